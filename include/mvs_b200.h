@@ -1,0 +1,128 @@
+/*
+ * mvs_b200.h -- C ABI of the B200-native random-projection sketching path.
+ *
+ * This is the drop-in boundary for the hot path of
+ * RolandFaure/metagenome_vector_sketches:
+ *
+ *   VectorXi transform_set_into_vector(const std::unordered_set<unsigned long>&, int d)
+ *       reference: include/random_projection.h:11, src/random_projection.cpp:9-26
+ *   the sample loop, int16 saturation and norm pass of sketch()
+ *       reference: src/project_everything.cpp:287-298, 327-353
+ *
+ * The reference has no FFI layer for this path (its pybind module, src/bindings.cpp,
+ * binds the query side only), so the entry points below are what a cgo / ctypes /
+ * C++ caller of that path binds instead; INTEGRATION.md shows the C++ shim with the
+ * reference's exact signature and the ctypes stub.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; the caller owns every buffer;
+ *   - every function returns 0 (MVS_OK) or a negative mvs_status; mvs_strerror()
+ *     gives the text, mvs_last_cuda_error() the underlying cudaError_t;
+ *   - a batch is CSR: sample s owns hashes[offsets[s] .. offsets[s+1]); offsets has
+ *     n_samples+1 entries, offsets[0] is the index of the first hash of sample 0;
+ *   - hashes inside one sample must be UNIQUE (the reference receives a set; a
+ *     duplicate would be counted twice).  mvs_sort_unique() is the helper the
+ *     drivers use;
+ *   - `seed` is additive: entry(h, j) uses splitmix64(h + 64*(j/64) + seed);
+ *     seed 0 is bit-identical to the reference (which has no seed);
+ *   - a context is bound to ONE GPU (one process / host thread per GPU); it is not
+ *     thread-safe, use one context per host thread;
+ *   - there is NO CPU fallback: without a usable sm_100 device mvs_create() fails.
+ */
+#ifndef MVS_B200_H
+#define MVS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mvs_ctx mvs_ctx;
+
+typedef enum mvs_status {
+    MVS_OK = 0,
+    MVS_ERR_INVALID_ARG = -1,   /* null pointer, d <= 0, negative sizes, offsets not monotone */
+    MVS_ERR_NO_DEVICE = -2,     /* no CUDA device / device is not sm_100 */
+    MVS_ERR_CUDA = -3,          /* a CUDA call failed: see mvs_last_cuda_error() */
+    MVS_ERR_OOM = -4,           /* host or device allocation failed */
+    MVS_ERR_TOO_LARGE = -5,     /* a sample has >= 2^31 hashes (int32 accumulator, as the reference) */
+    MVS_ERR_IO = -6             /* file could not be opened / written (driver helpers) */
+} mvs_status;
+
+/* ---- lifetime --------------------------------------------------------------------- */
+int mvs_create(mvs_ctx** ctx, int device);          /* binds to cuda:<device> */
+void mvs_destroy(mvs_ctx* ctx);
+const char* mvs_strerror(int status);
+int mvs_last_cuda_error(const mvs_ctx* ctx);        /* cudaError_t of the last failure, 0 if none */
+int mvs_abi_version(void);                          /* bumps when a signature changes */
+
+/* ---- the hot path ----------------------------------------------------------------- */
+
+/* One set -> one vector.  Replaces transform_set_into_vector
+ * (reference src/random_projection.cpp:9).  hashes/out are HOST pointers. */
+int mvs_transform_set(mvs_ctx* ctx, const uint64_t* hashes, int64_t n_hashes, int d,
+                      uint64_t seed, int32_t* out);
+
+/* A CSR batch of sets -> n_samples x d int32 row-major.  Replaces the OpenMP sample
+ * loop of sketch() (reference src/project_everything.cpp:289-298).  All pointers are
+ * HOST memory (pinned memory from mvs_host_alloc / mvs_host_register makes the copies
+ * asynchronous); the call streams slices of the batch through the GPU on several CUDA
+ * streams (H2D, kernel, D2H overlapped) and returns when `out` is complete. */
+int mvs_project_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offsets,
+                      int64_t n_samples, int d, uint64_t seed, int32_t* out);
+
+/* Same computation with the hash array and the output already resident in HBM.
+ * d_hashes / d_out are DEVICE pointers on the context's GPU, h_offsets is a HOST array
+ * (n_samples+1 entries indexing d_hashes).  `stream` is a cudaStream_t (NULL = the
+ * context's own stream).  Asynchronous w.r.t. the host unless `stream` is NULL.      */
+int mvs_project_device(mvs_ctx* ctx, const uint64_t* d_hashes, const uint64_t* h_offsets,
+                       int64_t n_samples, int d, uint64_t seed, int32_t* d_out, void* stream);
+
+/* Epilogue of sketch() on device-resident vectors (reference
+ * src/project_everything.cpp:327-347): per row the exact integer sum of squares
+ * (norm = sqrt(sumsq / d)) and, if d_out16 != NULL, the int16-saturated copy.
+ * d_vec, d_sumsq (n_samples uint64) and d_out16 (n_samples*d int16) are DEVICE pointers. */
+int mvs_finalize_device(mvs_ctx* ctx, const int32_t* d_vec, int64_t n_samples, int d,
+                        uint64_t* d_sumsq, int16_t* d_out16, void* stream);
+
+/* Host-pointer convenience wrapper of the above (copies in and out). */
+int mvs_finalize(mvs_ctx* ctx, const int32_t* vec, int64_t n_samples, int d,
+                 uint64_t* sumsq, int16_t* out16);
+
+/* ---- helpers ---------------------------------------------------------------------- */
+/* In-place sort + unique of one sample's hashes (set semantics of the reference's
+ * unordered_set).  Returns the new count (>= 0). */
+int64_t mvs_sort_unique(uint64_t* hashes, int64_t n);
+
+void* mvs_host_alloc(size_t bytes);                 /* pinned host memory, NULL on failure */
+void mvs_host_free(void* p);
+int mvs_host_register(void* p, size_t bytes);       /* pin caller-owned memory */
+int mvs_host_unregister(void* p);
+
+/* ---- measurement ------------------------------------------------------------------ */
+typedef struct mvs_timing {
+    float kernel_ms;       /* CUDA-event time of the projection (+ partial-reduce) kernels of
+                              the last mvs_project_device call, measured on its stream */
+    float reduce_ms;       /* the partial-reduce kernel alone */
+    uint64_t launches;     /* kernels launched by this context since creation */
+    uint64_t warp_tasks;   /* warp tasks of the last projection call */
+    uint64_t partial_rows; /* partial rows of the last projection call */
+    uint64_t h2d_bytes;    /* bytes copied host->device by the last mvs_project_batch */
+    uint64_t d2h_bytes;    /* bytes copied device->host by the last mvs_project_batch */
+} mvs_timing;
+int mvs_get_timing(mvs_ctx* ctx, mvs_timing* t);    /* synchronises the context's streams */
+
+/* Integer issue-rate microbenchmark used as the roofline denominator.
+ * which: 0 = LOP3 (ALU pipe), 1 = IMAD (FMA pipe), 2 = LOP3+IMAD interleaved 1:1,
+ *        3 = IADD3, 4 = SHF.  Writes 32-bit lane-operations per second. */
+int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second);
+
+/* Kernel tuning knobs for experiments (0 = default).  Unknown keys are ignored. */
+int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MVS_B200_H */

@@ -1,0 +1,634 @@
+// mvs_capi.cu -- host side of the C ABI declared in include/mvs_b200.h.
+//
+// Replaces, for the GPU, the sample loop of sketch()
+// (reference src/project_everything.cpp:287-298) and transform_set_into_vector
+// (reference src/random_projection.cpp:9-26).  Planning (splitting samples into warp
+// tasks), slice streaming (H2D / kernels / D2H on several streams) and the partial
+// reduce live here; the device code is in mvs_kernels.cuh.
+//
+// There is deliberately no CPU implementation of the projection in this file: if the
+// device is missing or a launch fails the call returns an error.
+#include "../../include/mvs_b200.h"
+#include "mvs_kernels.cuh"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+namespace {
+
+using mvs::ReduceItem;
+using mvs::WarpTask;
+
+constexpr int kSlots = 3;                        // slices in flight in mvs_project_batch
+constexpr int kAbiVersion = 1;
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;                  // everything queued on this slot has finished
+    cudaEvent_t uploaded = nullptr;              // the pinned plan buffers have been read by the copy engine
+    bool busy = false;
+    bool upload_busy = false;
+    DevBuf hashes, out, partials, tasks, reduce;
+    PinBuf h_tasks, h_reduce;
+};
+
+struct Geometry {
+    int d = 0;
+    int nb = 0;                                  // 64-column blocks
+    int lph_log2 = 5;
+    int S = 1;                                   // hash slots per warp
+    int passes = 1;                              // 32-block column passes
+    uint64_t cap = 0;                            // max hashes per warp task
+    uint32_t quantum = 16;                       // 16 * S
+};
+
+}  // namespace
+
+struct mvs_ctx {
+    int device = 0;
+    int sm_count = 0;
+    int last_cuda = 0;
+    Slot slots[kSlots];
+    cudaEvent_t ev_start = nullptr, ev_mid = nullptr, ev_end = nullptr;
+    bool timing_valid = false;
+    mvs_timing timing{};
+    uint64_t launches = 0;
+    uint64_t slice_hashes = 16ull << 20;         // hashes per streamed slice (128 MB)
+    uint64_t slice_rows_bytes = 256ull << 20;    // output bytes per streamed slice
+    uint32_t* d_sink = nullptr;
+};
+
+namespace {
+
+#define MVS_CUDA(ctx, call)                                   \
+    do {                                                      \
+        cudaError_t e_ = (call);                              \
+        if (e_ != cudaSuccess) {                              \
+            (ctx)->last_cuda = static_cast<int>(e_);          \
+            cudaGetLastError();                               \
+            return e_ == cudaErrorMemoryAllocation ? MVS_ERR_OOM : MVS_ERR_CUDA; \
+        }                                                     \
+    } while (0)
+
+int ensure_dev(mvs_ctx* ctx, DevBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap) return MVS_OK;
+    if (b.p) {
+        MVS_CUDA(ctx, cudaFree(b.p));
+        b.p = nullptr;
+        b.cap = 0;
+    }
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&b.p, want);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        want = bytes;
+        MVS_CUDA(ctx, cudaMalloc(&b.p, want));
+    }
+    b.cap = want;
+    return MVS_OK;
+}
+
+int ensure_pin(mvs_ctx* ctx, PinBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap) return MVS_OK;
+    if (b.p) {
+        MVS_CUDA(ctx, cudaFreeHost(b.p));
+        b.p = nullptr;
+        b.cap = 0;
+    }
+    const size_t want = bytes + bytes / 4 + 4096;
+    MVS_CUDA(ctx, cudaMallocHost(&b.p, want));
+    b.cap = want;
+    return MVS_OK;
+}
+
+Geometry make_geometry(int d)
+{
+    Geometry g;
+    g.d = d;
+    g.nb = (d + 63) / 64;
+    if (g.nb >= 32) {
+        g.lph_log2 = 5;
+        g.passes = (g.nb + 31) / 32;
+    } else {
+        int l = 0;
+        while ((1 << l) < g.nb) ++l;
+        g.lph_log2 = l;
+        g.passes = 1;
+    }
+    g.S = 32 >> g.lph_log2;
+    g.quantum = 16u * static_cast<uint32_t>(g.S);
+    g.cap = static_cast<uint64_t>(mvs::kMaxRounds) * static_cast<uint64_t>(g.S);
+    return g;
+}
+
+struct PlanCounts {
+    uint64_t tasks = 0, reduce = 0, prows = 0;
+};
+
+// First pass: how many tasks / reduce items / partial rows does [s0, s1) need?
+int count_plan(const uint64_t* offsets, int64_t s0, int64_t s1, const Geometry& g, PlanCounts& pc)
+{
+    pc = PlanCounts{};
+    for (int64_t s = s0; s < s1; ++s) {
+        if (offsets[s + 1] < offsets[s]) return MVS_ERR_INVALID_ARG;
+        const uint64_t n = offsets[s + 1] - offsets[s];
+        if (n >= (1ull << 31)) return MVS_ERR_TOO_LARGE;
+        uint64_t nchunks = 1;
+        if (n > g.cap) {
+            uint64_t k = (n + g.cap - 1) / g.cap;
+            uint64_t per = (n + k - 1) / k;
+            per = (per + g.quantum - 1) / g.quantum * g.quantum;
+            nchunks = (n + per - 1) / per;
+        }
+        pc.tasks += nchunks * static_cast<uint64_t>(g.passes);
+        if (nchunks > 1) {
+            pc.reduce += 1;
+            pc.prows += nchunks;
+        }
+    }
+    if (pc.tasks >= 0xFFFFFFF0ull || pc.prows >= 0xFFFFFFF0ull) return MVS_ERR_TOO_LARGE;
+    return MVS_OK;
+}
+
+// Second pass: emit.  `hash_base` is subtracted from the CSR offsets (index of the first
+// hash present in the device array), `row_base` from the sample index (first output row).
+void emit_plan(const uint64_t* offsets, int64_t s0, int64_t s1, uint64_t hash_base, int64_t row_base,
+               const Geometry& g, WarpTask* tasks, ReduceItem* reduce)
+{
+    uint64_t ti = 0, ri = 0, prow = 0;
+    for (int64_t s = s0; s < s1; ++s) {
+        const uint64_t n = offsets[s + 1] - offsets[s];
+        const uint64_t b0 = offsets[s] - hash_base;
+        uint64_t nchunks = 1, per = n;
+        if (n > g.cap) {
+            uint64_t k = (n + g.cap - 1) / g.cap;
+            per = (n + k - 1) / k;
+            per = (per + g.quantum - 1) / g.quantum * g.quantum;
+            nchunks = (n + per - 1) / per;
+        }
+        const uint32_t row = static_cast<uint32_t>(s - row_base);
+        for (uint64_t c = 0; c < nchunks; ++c) {
+            const uint64_t cb = c * per;
+            const uint64_t cn = std::min<uint64_t>(per, n - cb);
+            for (int p = 0; p < g.passes; ++p) {
+                WarpTask& t = tasks[ti++];
+                t.begin = b0 + cb;
+                t.count = static_cast<uint32_t>(cn);
+                t.sample = row;
+                t.pass = static_cast<uint32_t>(p);
+                t.prow = nchunks > 1 ? static_cast<uint32_t>(prow + c) : mvs::kDirect;
+                t.pad0 = 0;
+                t.pad1 = 0;
+            }
+        }
+        if (nchunks > 1) {
+            ReduceItem& r = reduce[ri++];
+            r.sample = row;
+            r.prow = static_cast<uint32_t>(prow);
+            r.nchunks = static_cast<uint32_t>(nchunks);
+            r.n = static_cast<uint32_t>(n);
+            prow += nchunks;
+        }
+    }
+}
+
+template <int L>
+cudaError_t launch_project_t(cudaStream_t st, uint32_t ntasks, const uint64_t* d_hashes, const WarpTask* d_tasks,
+                             int d, uint64_t seed, int32_t* d_out, int32_t* d_partials, int vec4)
+{
+    const uint32_t grid = (ntasks + mvs::kWarpsPerCta - 1) / mvs::kWarpsPerCta;
+    const size_t smem = static_cast<size_t>(mvs::kWarpsPerCta) * mvs::kStages * mvs::kTileHashes * sizeof(uint64_t);
+    mvs::project_kernel<L><<<grid, mvs::kWarpsPerCta * 32, smem, st>>>(d_hashes, d_tasks, ntasks, d,
+                                                                     seed + mvs::kGolden, d_out, d_partials, vec4);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_project(const Geometry& g, cudaStream_t st, uint32_t ntasks, const uint64_t* d_hashes,
+                           const WarpTask* d_tasks, uint64_t seed, int32_t* d_out, int32_t* d_partials)
+{
+    const int vec4 = ((g.d & 3) == 0) && ((reinterpret_cast<uintptr_t>(d_out) & 15) == 0) &&
+                     ((reinterpret_cast<uintptr_t>(d_partials) & 15) == 0);
+    switch (g.lph_log2) {
+        case 0: return launch_project_t<0>(st, ntasks, d_hashes, d_tasks, g.d, seed, d_out, d_partials, vec4);
+        case 1: return launch_project_t<1>(st, ntasks, d_hashes, d_tasks, g.d, seed, d_out, d_partials, vec4);
+        case 2: return launch_project_t<2>(st, ntasks, d_hashes, d_tasks, g.d, seed, d_out, d_partials, vec4);
+        case 3: return launch_project_t<3>(st, ntasks, d_hashes, d_tasks, g.d, seed, d_out, d_partials, vec4);
+        case 4: return launch_project_t<4>(st, ntasks, d_hashes, d_tasks, g.d, seed, d_out, d_partials, vec4);
+        default: return launch_project_t<5>(st, ntasks, d_hashes, d_tasks, g.d, seed, d_out, d_partials, vec4);
+    }
+}
+
+// Plan [s0, s1) into the slot's pinned buffers, upload, launch projection (+ reduce).
+// d_hashes holds the hashes from index `hash_base` on; d_out row 0 = sample `s0`
+// when rows_local, else sample 0.
+int run_range(mvs_ctx* ctx, Slot& sl, const uint64_t* d_hashes, const uint64_t* offsets, int64_t s0, int64_t s1,
+              uint64_t hash_base, int64_t row_base, const Geometry& g, uint64_t seed, int32_t* d_out,
+              cudaStream_t st, bool record_timing)
+{
+    PlanCounts pc;
+    int rc = count_plan(offsets, s0, s1, g, pc);
+    if (rc != MVS_OK) return rc;
+    if (pc.tasks == 0) return MVS_OK;
+    if ((rc = ensure_pin(ctx, sl.h_tasks, pc.tasks * sizeof(WarpTask))) != MVS_OK) return rc;
+    if ((rc = ensure_pin(ctx, sl.h_reduce, (pc.reduce + 1) * sizeof(ReduceItem))) != MVS_OK) return rc;
+    if ((rc = ensure_dev(ctx, sl.tasks, pc.tasks * sizeof(WarpTask))) != MVS_OK) return rc;
+    if ((rc = ensure_dev(ctx, sl.reduce, (pc.reduce + 1) * sizeof(ReduceItem))) != MVS_OK) return rc;
+    if ((rc = ensure_dev(ctx, sl.partials, (pc.prows + 1) * static_cast<size_t>(g.d) * sizeof(int32_t))) != MVS_OK)
+        return rc;
+    emit_plan(offsets, s0, s1, hash_base, row_base, g, static_cast<WarpTask*>(sl.h_tasks.p),
+              static_cast<ReduceItem*>(sl.h_reduce.p));
+    MVS_CUDA(ctx, cudaMemcpyAsync(sl.tasks.p, sl.h_tasks.p, pc.tasks * sizeof(WarpTask), cudaMemcpyHostToDevice, st));
+    if (pc.reduce)
+        MVS_CUDA(ctx, cudaMemcpyAsync(sl.reduce.p, sl.h_reduce.p, pc.reduce * sizeof(ReduceItem),
+                                      cudaMemcpyHostToDevice, st));
+    MVS_CUDA(ctx, cudaEventRecord(sl.uploaded, st));
+    sl.upload_busy = true;
+    if (record_timing) MVS_CUDA(ctx, cudaEventRecord(ctx->ev_start, st));
+    MVS_CUDA(ctx, launch_project(g, st, static_cast<uint32_t>(pc.tasks), d_hashes,
+                                 static_cast<const WarpTask*>(sl.tasks.p), seed, d_out,
+                                 static_cast<int32_t*>(sl.partials.p)));
+    ctx->launches += 1;
+    if (record_timing) MVS_CUDA(ctx, cudaEventRecord(ctx->ev_mid, st));
+    if (pc.reduce) {
+        const unsigned gy = static_cast<unsigned>(std::min<int64_t>((g.d + 255) / 256, 65535));
+        dim3 grid(static_cast<unsigned>(pc.reduce), gy);
+        mvs::reduce_partials_kernel<<<grid, 256, 0, st>>>(static_cast<const ReduceItem*>(sl.reduce.p),
+                                                        static_cast<uint32_t>(pc.reduce), g.d,
+                                                        static_cast<const int32_t*>(sl.partials.p), d_out);
+        MVS_CUDA(ctx, cudaGetLastError());
+        ctx->launches += 1;
+    }
+    if (record_timing) {
+        MVS_CUDA(ctx, cudaEventRecord(ctx->ev_end, st));
+        ctx->timing_valid = true;
+    }
+    ctx->timing.warp_tasks = pc.tasks;
+    ctx->timing.partial_rows = pc.prows;
+    return MVS_OK;
+}
+
+int wait_slot(mvs_ctx* ctx, Slot& sl)
+{
+    if (sl.busy) {
+        MVS_CUDA(ctx, cudaEventSynchronize(sl.done));
+        sl.busy = false;
+        sl.upload_busy = false;
+    }
+    return MVS_OK;
+}
+
+int wait_upload(mvs_ctx* ctx, Slot& sl)
+{
+    if (sl.upload_busy) {
+        MVS_CUDA(ctx, cudaEventSynchronize(sl.uploaded));
+        sl.upload_busy = false;
+    }
+    return MVS_OK;
+}
+
+}  // namespace
+
+// ======================================================================================
+extern "C" {
+
+int mvs_abi_version(void) { return kAbiVersion; }
+
+const char* mvs_strerror(int status)
+{
+    switch (status) {
+        case MVS_OK: return "ok";
+        case MVS_ERR_INVALID_ARG: return "invalid argument";
+        case MVS_ERR_NO_DEVICE: return "no usable sm_100 CUDA device (there is no CPU fallback)";
+        case MVS_ERR_CUDA: return "CUDA call failed";
+        case MVS_ERR_OOM: return "out of memory";
+        case MVS_ERR_TOO_LARGE: return "sample or batch too large (>= 2^31 hashes in one sample, or >= 2^32 tasks)";
+        case MVS_ERR_IO: return "I/O error";
+        default: return "unknown mvs status";
+    }
+}
+
+int mvs_last_cuda_error(const mvs_ctx* ctx) { return ctx ? ctx->last_cuda : 0; }
+
+int mvs_create(mvs_ctx** out, int device)
+{
+    if (!out) return MVS_ERR_INVALID_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) {
+        cudaGetLastError();
+        return MVS_ERR_NO_DEVICE;
+    }
+    cudaDeviceProp prop{};
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+        cudaGetLastError();
+        return MVS_ERR_NO_DEVICE;
+    }
+    if (prop.major != 10) return MVS_ERR_NO_DEVICE;          // sm_100a cubin only
+    mvs_ctx* ctx = new (std::nothrow) mvs_ctx();
+    if (!ctx) return MVS_ERR_OOM;
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    int rc = MVS_OK;
+    auto chk = [&](cudaError_t e) {
+        if (e != cudaSuccess && rc == MVS_OK) {
+            ctx->last_cuda = static_cast<int>(e);
+            rc = MVS_ERR_CUDA;
+        }
+    };
+    chk(cudaSetDevice(device));
+    for (auto& sl : ctx->slots) {
+        chk(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking));
+        chk(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+        chk(cudaEventCreateWithFlags(&sl.uploaded, cudaEventDisableTiming));
+    }
+    chk(cudaEventCreate(&ctx->ev_start));
+    chk(cudaEventCreate(&ctx->ev_mid));
+    chk(cudaEventCreate(&ctx->ev_end));
+    chk(cudaMalloc(reinterpret_cast<void**>(&ctx->d_sink), 256));
+    if (rc != MVS_OK) {
+        mvs_destroy(ctx);
+        return rc;
+    }
+    *out = ctx;
+    return MVS_OK;
+}
+
+void mvs_destroy(mvs_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    for (auto& sl : ctx->slots) {
+        if (sl.stream) cudaStreamSynchronize(sl.stream);
+        for (DevBuf* b : {&sl.hashes, &sl.out, &sl.partials, &sl.tasks, &sl.reduce})
+            if (b->p) cudaFree(b->p);
+        for (PinBuf* b : {&sl.h_tasks, &sl.h_reduce})
+            if (b->p) cudaFreeHost(b->p);
+        if (sl.done) cudaEventDestroy(sl.done);
+        if (sl.uploaded) cudaEventDestroy(sl.uploaded);
+        if (sl.stream) cudaStreamDestroy(sl.stream);
+    }
+    if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
+    if (ctx->ev_mid) cudaEventDestroy(ctx->ev_mid);
+    if (ctx->ev_end) cudaEventDestroy(ctx->ev_end);
+    if (ctx->d_sink) cudaFree(ctx->d_sink);
+    cudaGetLastError();
+    delete ctx;
+}
+
+int mvs_project_device(mvs_ctx* ctx, const uint64_t* d_hashes, const uint64_t* h_offsets, int64_t n_samples, int d,
+                       uint64_t seed, int32_t* d_out, void* stream)
+{
+    if (!ctx || !h_offsets || n_samples < 0 || d <= 0 || (!d_out && n_samples > 0)) return MVS_ERR_INVALID_ARG;
+    if (n_samples == 0) return MVS_OK;
+    if (n_samples >= 0xFFFFFFF0ll) return MVS_ERR_TOO_LARGE;
+    if (!d_hashes && h_offsets[n_samples] > h_offsets[0]) return MVS_ERR_INVALID_ARG;
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    Slot& sl = ctx->slots[0];
+    // Only the pinned plan buffers must be free again; device buffers are protected by
+    // stream order (callers use one stream per context) and cudaFree synchronises.
+    int rc = stream ? wait_upload(ctx, sl) : wait_slot(ctx, sl);
+    if (rc != MVS_OK) return rc;
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : sl.stream;
+    const Geometry g = make_geometry(d);
+    rc = run_range(ctx, sl, d_hashes, h_offsets, 0, n_samples, 0, 0, g, seed, d_out, st, true);
+    if (rc != MVS_OK) return rc;
+    MVS_CUDA(ctx, cudaEventRecord(sl.done, st));
+    sl.busy = true;
+    if (!stream) MVS_CUDA(ctx, cudaStreamSynchronize(st));
+    return MVS_OK;
+}
+
+int mvs_project_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offsets, int64_t n_samples, int d,
+                      uint64_t seed, int32_t* out)
+{
+    if (!ctx || !offsets || n_samples < 0 || d <= 0 || (!out && n_samples > 0)) return MVS_ERR_INVALID_ARG;
+    if (n_samples == 0) return MVS_OK;
+    if (n_samples >= 0xFFFFFFF0ll) return MVS_ERR_TOO_LARGE;
+    if (!hashes && offsets[n_samples] > offsets[0]) return MVS_ERR_INVALID_ARG;
+    for (int64_t s = 0; s < n_samples; ++s)
+        if (offsets[s + 1] < offsets[s]) return MVS_ERR_INVALID_ARG;
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    const Geometry g = make_geometry(d);
+    const uint64_t row_bytes = static_cast<uint64_t>(d) * sizeof(int32_t);
+    const int64_t max_rows = std::max<int64_t>(1, static_cast<int64_t>(ctx->slice_rows_bytes / row_bytes));
+    ctx->timing.h2d_bytes = 0;
+    ctx->timing.d2h_bytes = 0;
+    ctx->timing_valid = false;
+
+    int rc = MVS_OK;
+    int64_t s0 = 0;
+    int turn = 0;
+    while (s0 < n_samples && rc == MVS_OK) {
+        int64_t s1 = s0 + 1;
+        while (s1 < n_samples && s1 - s0 < max_rows && offsets[s1 + 1] - offsets[s0] <= ctx->slice_hashes) ++s1;
+        const uint64_t h0 = offsets[s0];
+        const uint64_t nh = offsets[s1] - h0;
+        const int64_t rows = s1 - s0;
+        Slot& sl = ctx->slots[turn % kSlots];
+        ++turn;
+        if ((rc = wait_slot(ctx, sl)) != MVS_OK) break;
+        if ((rc = ensure_dev(ctx, sl.hashes, (nh + 2) * sizeof(uint64_t))) != MVS_OK) break;
+        if ((rc = ensure_dev(ctx, sl.out, static_cast<size_t>(rows) * row_bytes)) != MVS_OK) break;
+        if (nh) {
+            cudaError_t e = cudaMemcpyAsync(sl.hashes.p, hashes + h0, nh * sizeof(uint64_t), cudaMemcpyHostToDevice,
+                                            sl.stream);
+            if (e != cudaSuccess) { ctx->last_cuda = e; cudaGetLastError(); rc = MVS_ERR_CUDA; break; }
+            ctx->timing.h2d_bytes += nh * sizeof(uint64_t);
+        }
+        rc = run_range(ctx, sl, static_cast<const uint64_t*>(sl.hashes.p), offsets, s0, s1, h0, s0, g, seed,
+                       static_cast<int32_t*>(sl.out.p), sl.stream, false);
+        if (rc != MVS_OK) break;
+        ctx->timing.h2d_bytes += ctx->timing.warp_tasks * sizeof(WarpTask);
+        cudaError_t e = cudaMemcpyAsync(out + static_cast<size_t>(s0) * static_cast<size_t>(d), sl.out.p,
+                                        static_cast<size_t>(rows) * row_bytes, cudaMemcpyDeviceToHost, sl.stream);
+        if (e == cudaSuccess) e = cudaEventRecord(sl.done, sl.stream);
+        if (e != cudaSuccess) { ctx->last_cuda = e; cudaGetLastError(); rc = MVS_ERR_CUDA; break; }
+        ctx->timing.d2h_bytes += static_cast<uint64_t>(rows) * row_bytes;
+        sl.busy = true;
+        s0 = s1;
+    }
+    for (auto& sl : ctx->slots) {
+        const int r2 = wait_slot(ctx, sl);
+        if (rc == MVS_OK) rc = r2;
+    }
+    return rc;
+}
+
+int mvs_transform_set(mvs_ctx* ctx, const uint64_t* hashes, int64_t n_hashes, int d, uint64_t seed, int32_t* out)
+{
+    if (n_hashes < 0) return MVS_ERR_INVALID_ARG;
+    const uint64_t offs[2] = {0, static_cast<uint64_t>(n_hashes)};
+    return mvs_project_batch(ctx, hashes, offs, 1, d, seed, out);
+}
+
+int mvs_finalize_device(mvs_ctx* ctx, const int32_t* d_vec, int64_t n_samples, int d, uint64_t* d_sumsq,
+                        int16_t* d_out16, void* stream)
+{
+    if (!ctx || n_samples < 0 || d <= 0 || (!d_vec && n_samples > 0)) return MVS_ERR_INVALID_ARG;
+    if (n_samples == 0) return MVS_OK;
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->slots[0].stream;
+    const int64_t rows_per_cta = 8;
+    const int64_t grid = (n_samples + rows_per_cta - 1) / rows_per_cta;
+    if (grid > 0x7FFFFFFFll) return MVS_ERR_TOO_LARGE;
+    mvs::finalize_kernel<<<static_cast<unsigned>(grid), 256, 0, st>>>(
+        d_vec, n_samples, d, reinterpret_cast<unsigned long long*>(d_sumsq), d_out16);
+    MVS_CUDA(ctx, cudaGetLastError());
+    ctx->launches += 1;
+    if (!stream) MVS_CUDA(ctx, cudaStreamSynchronize(st));
+    return MVS_OK;
+}
+
+int mvs_finalize(mvs_ctx* ctx, const int32_t* vec, int64_t n_samples, int d, uint64_t* sumsq, int16_t* out16)
+{
+    if (!ctx || n_samples < 0 || d <= 0 || (!vec && n_samples > 0)) return MVS_ERR_INVALID_ARG;
+    if (n_samples == 0) return MVS_OK;
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    Slot& sl = ctx->slots[0];
+    int rc = wait_slot(ctx, sl);
+    if (rc != MVS_OK) return rc;
+    const size_t n = static_cast<size_t>(n_samples) * static_cast<size_t>(d);
+    // layout in sl.out: [vec int32 n][sumsq u64 n_samples][out16 int16 n]
+    const size_t off_ss = (n * sizeof(int32_t) + 255) / 256 * 256;
+    const size_t off_16 = off_ss + (static_cast<size_t>(n_samples) * sizeof(uint64_t) + 255) / 256 * 256;
+    const size_t total = off_16 + n * sizeof(int16_t);
+    if ((rc = ensure_dev(ctx, sl.out, total)) != MVS_OK) return rc;
+    char* base = static_cast<char*>(sl.out.p);
+    MVS_CUDA(ctx, cudaMemcpyAsync(base, vec, n * sizeof(int32_t), cudaMemcpyHostToDevice, sl.stream));
+    rc = mvs_finalize_device(ctx, reinterpret_cast<int32_t*>(base), n_samples, d,
+                             reinterpret_cast<uint64_t*>(base + off_ss),
+                             out16 ? reinterpret_cast<int16_t*>(base + off_16) : nullptr, sl.stream);
+    if (rc != MVS_OK) return rc;
+    if (sumsq)
+        MVS_CUDA(ctx, cudaMemcpyAsync(sumsq, base + off_ss, static_cast<size_t>(n_samples) * sizeof(uint64_t),
+                                      cudaMemcpyDeviceToHost, sl.stream));
+    if (out16)
+        MVS_CUDA(ctx, cudaMemcpyAsync(out16, base + off_16, n * sizeof(int16_t), cudaMemcpyDeviceToHost, sl.stream));
+    MVS_CUDA(ctx, cudaStreamSynchronize(sl.stream));
+    return MVS_OK;
+}
+
+int64_t mvs_sort_unique(uint64_t* hashes, int64_t n)
+{
+    if (!hashes || n <= 0) return 0;
+    std::sort(hashes, hashes + n);
+    return static_cast<int64_t>(std::unique(hashes, hashes + n) - hashes);
+}
+
+void* mvs_host_alloc(size_t bytes)
+{
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+void mvs_host_free(void* p)
+{
+    if (p) cudaFreeHost(p);
+}
+int mvs_host_register(void* p, size_t bytes)
+{
+    if (!p) return MVS_ERR_INVALID_ARG;
+    if (cudaHostRegister(p, bytes, cudaHostRegisterDefault) != cudaSuccess) {
+        cudaGetLastError();
+        return MVS_ERR_CUDA;
+    }
+    return MVS_OK;
+}
+int mvs_host_unregister(void* p)
+{
+    if (!p) return MVS_ERR_INVALID_ARG;
+    if (cudaHostUnregister(p) != cudaSuccess) {
+        cudaGetLastError();
+        return MVS_ERR_CUDA;
+    }
+    return MVS_OK;
+}
+
+int mvs_get_timing(mvs_ctx* ctx, mvs_timing* t)
+{
+    if (!ctx || !t) return MVS_ERR_INVALID_ARG;
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ctx->timing_valid) {
+        MVS_CUDA(ctx, cudaEventSynchronize(ctx->ev_end));
+        float a = 0.f, b = 0.f;
+        MVS_CUDA(ctx, cudaEventElapsedTime(&a, ctx->ev_start, ctx->ev_end));
+        MVS_CUDA(ctx, cudaEventElapsedTime(&b, ctx->ev_mid, ctx->ev_end));
+        ctx->timing.kernel_ms = a;
+        ctx->timing.reduce_ms = b;
+    } else {
+        ctx->timing.kernel_ms = 0.f;
+        ctx->timing.reduce_ms = 0.f;
+    }
+    ctx->timing.launches = ctx->launches;
+    *t = ctx->timing;
+    return MVS_OK;
+}
+
+int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second)
+{
+    if (!ctx || !ops_per_second || which < 0 || which > 4) return MVS_ERR_INVALID_ARG;
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->slots[0].stream;
+    const int iters = 4096;
+    const unsigned grid = static_cast<unsigned>(ctx->sm_count) * 8u;
+    cudaEvent_t e0, e1;
+    MVS_CUDA(ctx, cudaEventCreate(&e0));
+    MVS_CUDA(ctx, cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+        cudaEventRecord(e0, st);
+        switch (which) {
+            case 0: mvs::issue_bench_kernel<0><<<grid, 256, 0, st>>>(ctx->d_sink, iters, 0x9e3779b9u, 0x85ebca6bu); break;
+            case 1: mvs::issue_bench_kernel<1><<<grid, 256, 0, st>>>(ctx->d_sink, iters, 0x9e3779b9u, 0x85ebca6bu); break;
+            case 2: mvs::issue_bench_kernel<2><<<grid, 256, 0, st>>>(ctx->d_sink, iters, 0x9e3779b9u, 0x85ebca6bu); break;
+            case 3: mvs::issue_bench_kernel<3><<<grid, 256, 0, st>>>(ctx->d_sink, iters, 0x9e3779b9u, 0x85ebca6bu); break;
+            default: mvs::issue_bench_kernel<4><<<grid, 256, 0, st>>>(ctx->d_sink, iters, 0x9e3779b9u, 0x85ebca6bu); break;
+        }
+        cudaEventRecord(e1, st);
+        cudaError_t e = cudaEventSynchronize(e1);
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) {
+            ctx->last_cuda = e;
+            cudaEventDestroy(e0);
+            cudaEventDestroy(e1);
+            return MVS_ERR_CUDA;
+        }
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (rep > 0) best = std::min(best, ms);
+        ctx->launches += 1;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    const double ops = static_cast<double>(grid) * 256.0 * static_cast<double>(iters) * 32.0;
+    *ops_per_second = ops / (static_cast<double>(best) * 1e-3);
+    return MVS_OK;
+}
+
+int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value)
+{
+    if (!ctx || !key) return MVS_ERR_INVALID_ARG;
+    if (!std::strcmp(key, "slice_hashes") && value > 0) ctx->slice_hashes = static_cast<uint64_t>(value);
+    else if (!std::strcmp(key, "slice_rows_bytes") && value > 0) ctx->slice_rows_bytes = static_cast<uint64_t>(value);
+    return MVS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,352 @@
+// mvs_kernels.cuh -- sm_100a device code of the random-projection sketching path.
+//
+// What is computed (reference src/random_projection.cpp:9-26):
+//     vec[j] = sum over hashes h of ( 1 - 2 * bit_{j%64}( splitmix64(h + 64*(j/64)) ) )
+//            = |H| - 2*C[j],   C[j] = number of hashes whose bit is 1.
+//
+// How: a *bit-sliced positional popcount*.  A lane owns one 64-column block b of one
+// hash stream.  For every hash it evaluates the 64-bit mixer once (two 32-bit words =
+// 64 columns) and feeds the two words into a Harley-Seal carry-save-adder tree whose
+// bit planes (weights 1,2,4,...,2^11) live in registers; one CSA is two LOP3.  No
+// per-column add is ever issued in the loop; the planes are expanded into int32
+// columns once per warp task (<= 4080 hashes per lane).  No matrix is materialised,
+// no atomics are used, integer adds make every partition order bit-exact.
+//
+// Work decomposition: a *warp task* = (sample, contiguous hash range, 32-block column
+// pass).  Lanes of a warp = LPH blocks x S hash slots (LPH*S = 32): d = 2048 gives
+// LPH = 32, S = 1 (one hash broadcast to 32 blocks); d = 256 gives LPH = 4, S = 8.
+// Hashes are staged global -> shared with cp.async (LDGSTS, zero-filled past the end
+// of the range) in a two-stage ring private to the warp and read back as broadcast
+// LDS.  Padding zeros are processed like real hashes and their known contribution
+// (splitmix64(0 + c) per lane) is subtracted at the flush, so the inner loop has no
+// masking at all.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace mvs {
+
+constexpr int kWarpsPerCta = 4;
+constexpr int kTileHashes = 512;                 // hashes per staging tile (4 KB) per warp
+constexpr int kStages = 2;
+constexpr int kPlanes = 12;                      // bit planes: counts up to 4095 per lane
+constexpr uint32_t kMaxRounds = 4080;            // hashes per lane per task (255 groups of 16)
+constexpr uint32_t kDirect = 0xFFFFFFFFu;
+constexpr uint64_t kGolden = 0x9e3779b97f4a7c15ULL;
+
+struct __align__(16) WarpTask {                  // 32 bytes
+    uint64_t begin;                              // first hash (index into the batch array)
+    uint32_t count;                              // hashes of this chunk
+    uint32_t sample;                             // output row
+    uint32_t pass;                               // column pass: blocks [32*pass, 32*pass+32)
+    uint32_t prow;                               // partial row, or kDirect
+    uint32_t pad0, pad1;
+};
+
+struct __align__(16) ReduceItem {                // 16 bytes
+    uint32_t sample;
+    uint32_t prow;                               // first partial row
+    uint32_t nchunks;
+    uint32_t n;                                  // |H_s|
+};
+
+// ---- splitmix64 finaliser (reference src/random_projection.cpp:14-17) --------------
+__device__ __forceinline__ void mix64(uint64_t x, uint32_t& lo, uint32_t& hi)
+{
+    x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ULL;
+    x = (x ^ (x >> 27)) * 0x94d049bb133111ebULL;
+    x = x ^ (x >> 31);
+    lo = static_cast<uint32_t>(x);
+    hi = static_cast<uint32_t>(x >> 32);
+}
+
+// carry-save adder on 32 bit columns at once: s = a^b^c, c = maj(a,b,c)
+__device__ __forceinline__ void csa(uint32_t& carry, uint32_t& sum, uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t s, m;
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(s) : "r"(a), "r"(b), "r"(c));
+    asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(m) : "r"(a), "r"(b), "r"(c));
+    sum = s;
+    carry = m;
+}
+
+// add the one-bit-per-column word c (weight 2^L) into planes L..kPlanes-1
+template <int L>
+__device__ __forceinline__ void ripple(uint32_t (&P)[kPlanes], uint32_t c)
+{
+#pragma unroll
+    for (int p = L; p < kPlanes; ++p) {
+        uint32_t t = P[p] & c;
+        P[p] ^= c;
+        c = t;
+    }
+}
+
+// 4 weight-1 words into (ones, twos) -> one weight-4 carry
+__device__ __forceinline__ uint32_t hs4(uint32_t (&P)[kPlanes], uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+{
+    uint32_t tA, tB, f;
+    csa(tA, P[0], P[0], a, b);
+    csa(tB, P[0], P[0], c, d);
+    csa(f, P[1], P[1], tA, tB);
+    return f;
+}
+
+// One Harley-Seal group: 16 hashes of this lane's stream -> planes 0..3 + a weight-16
+// carry per word.  sp points at the lane's first hash of the group in shared memory;
+// consecutive hashes of the lane are S entries apart.
+template <int S>
+__device__ __forceinline__ void group16(const uint64_t* __restrict__ sp, uint64_t cval,
+                                        uint32_t (&Plo)[kPlanes], uint32_t (&Phi)[kPlanes],
+                                        uint32_t& c16lo, uint32_t& c16hi)
+{
+    uint32_t lo[16], hi[16];
+    if constexpr (S == 1) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const ulonglong2 h2 = *reinterpret_cast<const ulonglong2*>(sp + 2 * i);   // LDS.128 broadcast
+            mix64(h2.x + cval, lo[2 * i], hi[2 * i]);
+            mix64(h2.y + cval, lo[2 * i + 1], hi[2 * i + 1]);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) mix64(sp[i * S] + cval, lo[i], hi[i]);
+    }
+    uint32_t fl[4], fh[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        fl[q] = hs4(Plo, lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+        fh[q] = hs4(Phi, hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+    }
+    uint32_t eA, eB;
+    csa(eA, Plo[2], Plo[2], fl[0], fl[1]);
+    csa(eB, Plo[2], Plo[2], fl[2], fl[3]);
+    csa(c16lo, Plo[3], Plo[3], eA, eB);
+    csa(eA, Phi[2], Phi[2], fh[0], fh[1]);
+    csa(eB, Phi[2], Phi[2], fh[2], fh[3]);
+    csa(c16hi, Phi[3], Phi[3], eA, eB);
+}
+
+__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc, uint32_t src_bytes)
+{
+    const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// ------------------------------------------------------------------------------------
+// The projection kernel.  One warp = one WarpTask.  LPH_LOG2 = log2(lanes per hash).
+// ------------------------------------------------------------------------------------
+template <int LPH_LOG2>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__ tasks, uint32_t ntasks,
+               int d, uint64_t seed_golden, int32_t* __restrict__ out, int32_t* __restrict__ partials,
+               int vec4_ok)
+{
+    constexpr int LPH = 1 << LPH_LOG2;
+    constexpr int S = 32 >> LPH_LOG2;
+    constexpr int kGroupsPerTile = kTileHashes / (16 * S);
+
+    extern __shared__ __align__(16) uint64_t smem[];
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t wid = blockIdx.x * kWarpsPerCta + warp;
+    if (wid >= ntasks) return;                   // warps are independent: no CTA-wide barrier below
+
+    const WarpTask task = tasks[wid];
+    uint64_t* ring = smem + warp * (kStages * kTileHashes);
+    const uint64_t* src = hashes + task.begin;
+    const uint32_t count = task.count;
+
+    const int slot = lane >> LPH_LOG2;
+    const int blk = static_cast<int>(task.pass) * 32 + (lane & (LPH - 1));
+    const uint64_t cval = seed_golden + (static_cast<uint64_t>(static_cast<uint32_t>(blk)) << 6);
+
+    uint32_t Plo[kPlanes], Phi[kPlanes];
+#pragma unroll
+    for (int p = 0; p < kPlanes; ++p) { Plo[p] = 0u; Phi[p] = 0u; }
+    uint32_t pend16lo = 0, pend16hi = 0, pend32lo = 0, pend32hi = 0;
+    uint32_t g = 0;                              // groups done (warp-uniform)
+
+    const uint32_t ntiles = (count + kTileHashes - 1) / kTileHashes;
+
+    auto issue_tile = [&](uint32_t t) {
+        uint64_t* st = ring + (t & (kStages - 1)) * kTileHashes;
+        const uint32_t base = t * kTileHashes;
+#pragma unroll
+        for (int i = 0; i < kTileHashes / 32; ++i) {
+            const uint32_t pos = base + i * 32 + lane;
+            const bool ok = pos < count;
+            cp_async8(st + i * 32 + lane, src + (ok ? pos : 0u), ok ? 8u : 0u);   // zero-fill past the end
+        }
+    };
+
+    if (ntiles) issue_tile(0);
+    cp_async_commit();
+    for (uint32_t t = 0; t < ntiles; ++t) {
+        if (t + 1 < ntiles) issue_tile(t + 1);
+        cp_async_commit();
+        cp_async_wait<1>();
+        __syncwarp();
+        const uint64_t* st = ring + (t & (kStages - 1)) * kTileHashes;
+        const uint32_t valid = min(count - t * kTileHashes, static_cast<uint32_t>(kTileHashes));
+        const uint32_t rounds = (valid + S - 1) / S;
+        const uint32_t ngroups = (rounds + 15) >> 4;           // <= kGroupsPerTile
+        for (uint32_t gi = 0; gi < ngroups; ++gi, ++g) {
+            uint32_t c16lo, c16hi;
+            group16<S>(st + gi * (16 * S) + slot, cval, Plo, Phi, c16lo, c16hi);
+            if ((g & 1u) == 0u) {
+                pend16lo = c16lo; pend16hi = c16hi;
+            } else {
+                uint32_t c32lo, c32hi;
+                csa(c32lo, Plo[4], Plo[4], pend16lo, c16lo);
+                csa(c32hi, Phi[4], Phi[4], pend16hi, c16hi);
+                if ((g & 2u) == 0u) {
+                    pend32lo = c32lo; pend32hi = c32hi;
+                } else {
+                    uint32_t c64lo, c64hi;
+                    csa(c64lo, Plo[5], Plo[5], pend32lo, c32lo);
+                    csa(c64hi, Phi[5], Phi[5], pend32hi, c32hi);
+                    ripple<6>(Plo, c64lo);
+                    ripple<6>(Phi, c64hi);
+                }
+            }
+        }
+        __syncwarp();                            // stage may be overwritten by the next issue
+    }
+    (void)kGroupsPerTile;
+    // fold the pending carries (g = number of groups done)
+    if (g & 1u) { ripple<4>(Plo, pend16lo); ripple<4>(Phi, pend16hi); }
+    if (g & 2u) { ripple<5>(Plo, pend32lo); ripple<5>(Phi, pend32hi); }
+
+    // padding correction: this lane consumed 16*g hashes of which `mine` were real; the
+    // others were zeros whose mixer output is the per-lane constant z.
+    const uint32_t mine = (count > static_cast<uint32_t>(slot)) ? (count - slot + S - 1) / S : 0u;
+    const uint32_t npad = 16u * g - mine;
+    uint32_t zlo, zhi;
+    mix64(cval, zlo, zhi);
+
+    // ---- flush: expand planes into int32 columns, fold hash slots, store -------------
+    const int nb = (d + 63) >> 6;
+    const bool writer = (slot == 0) && (blk < nb);
+    const bool direct = (task.prow == kDirect);
+    int32_t* row = direct ? out + static_cast<size_t>(task.sample) * static_cast<size_t>(d)
+                          : partials + static_cast<size_t>(task.prow) * static_cast<size_t>(d);
+    const int32_t n_total = static_cast<int32_t>(count);
+    const bool vec4 = vec4_ok != 0;             // d % 4 == 0 and 16-byte aligned rows (host-checked)
+
+#pragma unroll
+    for (int w = 0; w < 2; ++w) {
+#pragma unroll
+        for (int jq = 0; jq < 8; ++jq) {
+            int32_t v[4];
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) {
+                const int j = jq * 4 + jj;
+                uint32_t val = 0;
+#pragma unroll
+                for (int p = 0; p < kPlanes; ++p) {
+                    const uint32_t plane = w ? Phi[p] : Plo[p];
+                    val |= ((plane >> j) & 1u) << p;
+                }
+                const uint32_t zbit = ((w ? zhi : zlo) >> j) & 1u;
+                val -= npad * zbit;
+#pragma unroll
+                for (int m = LPH; m < 32; m <<= 1) val += __shfl_xor_sync(0xffffffffu, val, m);
+                v[jj] = direct ? (n_total - 2 * static_cast<int32_t>(val)) : static_cast<int32_t>(val);
+            }
+            if (writer) {
+                const int col = blk * 64 + w * 32 + jq * 4;
+                if (vec4) {
+                    if (col < d) *reinterpret_cast<int4*>(row + col) = make_int4(v[0], v[1], v[2], v[3]);
+                } else {
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj)
+                        if (col + jj < d) row[col + jj] = v[jj];
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// Partial reduce: samples split over several warp tasks.  Fixed chunk order, no atomics.
+//   out[s][j] = |H_s| - 2 * sum_c partial[prow + c][j]
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+reduce_partials_kernel(const ReduceItem* __restrict__ items, uint32_t nitems, int d,
+                       const int32_t* __restrict__ partials, int32_t* __restrict__ out)
+{
+    const uint32_t it = blockIdx.y;
+    if (it >= nitems) return;
+    const ReduceItem r = items[it];
+    const int32_t* p = partials + static_cast<size_t>(r.prow) * static_cast<size_t>(d);
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < d; j += gridDim.x * blockDim.x) {
+        int32_t acc = 0;
+        for (uint32_t c = 0; c < r.nchunks; ++c) acc += p[static_cast<size_t>(c) * d + j];
+        out[static_cast<size_t>(r.sample) * d + j] = static_cast<int32_t>(r.n) - 2 * acc;
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// Epilogue of sketch() (reference src/project_everything.cpp:327-347): per row the exact
+// sum of squares and the int16-saturated copy.  One warp per row.
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+finalize_kernel(const int32_t* __restrict__ vec, int64_t n_rows, int d,
+                unsigned long long* __restrict__ sumsq, int16_t* __restrict__ out16)
+{
+    const int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= n_rows) return;
+    const int lane = threadIdx.x & 31;
+    const int32_t* v = vec + row * d;
+    unsigned long long ss = 0;
+    for (int j = lane; j < d; j += 32) {
+        const int32_t x = v[j];
+        ss += static_cast<unsigned long long>(static_cast<long long>(x) * static_cast<long long>(x));
+        if (out16) out16[row * d + j] = static_cast<int16_t>(max(-32768, min(32767, x)));
+    }
+#pragma unroll
+    for (int m = 16; m; m >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, m);
+    if (lane == 0 && sumsq) sumsq[row] = ss;
+}
+
+// ------------------------------------------------------------------------------------
+// Integer issue-rate microbenchmarks (roofline denominator).
+// ------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(256)
+issue_bench_kernel(uint32_t* sink, int iters, uint32_t k0, uint32_t k1)
+{
+    uint32_t a[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = threadIdx.x * 2654435761u + i * k0 + blockIdx.x;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (MODE == 0) {
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(k0), "r"(k1));
+                } else if (MODE == 1) {
+                    asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(k0), "r"(k1));
+                } else if (MODE == 2) {
+                    if (i & 1) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(k0), "r"(k1));
+                    else       asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(k0), "r"(k1));
+                } else if (MODE == 3) {
+                    asm volatile("add.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(k0));
+                } else {
+                    asm volatile("shf.r.wrap.b32 %0, %0, %1, 7;" : "+r"(a[i]) : "r"(k1));
+                }
+            }
+        }
+    }
+    uint32_t x = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x ^= a[i];
+    if (x == 0x12345u) sink[0] = x;              // practically never; keeps the chains alive
+}
+
+}  // namespace mvs

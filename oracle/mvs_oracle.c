@@ -1,0 +1,98 @@
+/*
+ * mvs_oracle.c -- CPU ORACLE for the random-projection sketching path.
+ *
+ * THIS IS TEST INFRASTRUCTURE, NOT PRODUCT CODE.  Only tests/, bench.py's
+ * cpu_baseline / --impl reference legs and __graft_entry__.smoke() may load
+ * it.  The shipped path (metagenome_vector_sketches_b200/csrc) never links
+ * or calls anything in this directory.
+ *
+ * It restates, loop for loop, the reference algorithm
+ *   transform_set_into_vector   /root/reference/src/random_projection.cpp:9-26
+ * and the two host-side post-passes of the batch driver
+ *   int16 saturation            /root/reference/src/project_everything.cpp:332-347
+ *   norm = ||v / sqrt(d)||      /root/reference/src/project_everything.cpp:327-330
+ *
+ * Parity pin: oracle/_ref (the unmodified reference sources compiled where
+ * they lie, see oracle/Makefile) is compared with this file on the golden
+ * vectors in tests/golden (KAT-1..3 of SURVEY.md section 8c) and on seeded
+ * random sets by tests/test_oracle.py.
+ */
+#include <stdint.h>
+#include <stddef.h>
+#include <string.h>
+#include <math.h>
+
+/* random_projection.cpp:13-17 -- the splitmix64 finaliser applied to
+ * (hash + i), i = first column of the 64-wide block.  `seed` is the additive
+ * extension of SURVEY.md D2: seed 0 is the reference. */
+static inline uint64_t oracle_mix(uint64_t hash, uint64_t i, uint64_t seed)
+{
+    uint64_t x = hash + i + seed;
+    x += 0x9e3779b97f4a7c15ULL;
+    x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ULL;
+    x = (x ^ (x >> 27)) * 0x94d049bb133111ebULL;
+    x = x ^ (x >> 31);
+    return x;
+}
+
+uint64_t oracle_splitmix64(uint64_t hash, uint64_t i, uint64_t seed)
+{
+    return oracle_mix(hash, i, seed);
+}
+
+/* random_projection.cpp:9-26.  `hashes` must already be a set (unique values),
+ * as the reference receives an unordered_set.  out[d] is overwritten. */
+void oracle_transform_set(const uint64_t *hashes, int64_t n, int d,
+                          uint64_t seed, int32_t *out)
+{
+    if (d <= 0) return;
+    memset(out, 0, (size_t)d * sizeof(int32_t));
+    for (int64_t k = 0; k < n; ++k) {                       /* :11 */
+        for (int i = 0; i < d; i += 64) {                   /* :12 */
+            uint64_t x = oracle_mix(hashes[k], (uint64_t)i, seed);
+            for (int b = 0; b < 64 && (i + b) < d; ++b) {   /* :19 */
+                int projected = 1 - 2 * (int)((x >> b) & 1);/* :20 */
+                out[i + b] += projected;                    /* :21 */
+            }
+        }
+    }
+}
+
+/* The sample loop of sketch(), project_everything.cpp:289-298, over a CSR
+ * batch: sample s owns hashes[offsets[s] .. offsets[s+1]).  OpenMP dynamic
+ * schedule as in the reference when compiled with -fopenmp. */
+void oracle_project_csr(const uint64_t *hashes, const uint64_t *offsets,
+                        int64_t n_samples, int d, uint64_t seed, int32_t *out)
+{
+#pragma omp parallel for schedule(dynamic)
+    for (int64_t s = 0; s < n_samples; ++s)
+        oracle_transform_set(hashes + offsets[s],
+                             (int64_t)(offsets[s + 1] - offsets[s]), d, seed,
+                             out + (size_t)s * (size_t)d);
+}
+
+/* project_everything.cpp:332-347 */
+void oracle_saturate_int16(const int32_t *v, int64_t n, int16_t *out)
+{
+    for (int64_t i = 0; i < n; ++i) {
+        int32_t x = v[i];
+        out[i] = (int16_t)(x > 32767 ? 32767 : (x < -32768 ? -32768 : x));
+    }
+}
+
+/* Exact value the reference's float expression approximates:
+ * sqrt(sum v^2 / d).  (project_everything.cpp:327-329 evaluates it in float32
+ * through Eigen; the printed text has 6 significant digits.) */
+double oracle_norm_exact(const int32_t *v, int d)
+{
+    uint64_t ss = 0;
+    for (int i = 0; i < d; ++i) ss += (uint64_t)((int64_t)v[i] * (int64_t)v[i]);
+    return sqrt((double)ss / (double)d);
+}
+
+uint64_t oracle_sumsq(const int32_t *v, int d)
+{
+    uint64_t ss = 0;
+    for (int i = 0; i < d; ++i) ss += (uint64_t)((int64_t)v[i] * (int64_t)v[i]);
+    return ss;
+}

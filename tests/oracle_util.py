@@ -1,0 +1,131 @@
+"""Loader for the CPU oracle (oracle/liboracle.so) and, when prebuilt, the compiled
+reference (oracle/_ref/<variant>/libref_projection.so).  TEST INFRASTRUCTURE ONLY."""
+import ctypes as C
+import json
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+_oracle = None
+_ref = None
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        so = os.path.join(ORACLE_DIR, "liboracle.so")
+        if not os.path.exists(so):
+            subprocess.run(["make", "-C", ORACLE_DIR, "oracle"], check=True, stdout=subprocess.DEVNULL)
+        lib = C.CDLL(so)
+        lib.oracle_transform_set.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_uint64, C.c_void_p]
+        lib.oracle_project_csr.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64, C.c_void_p]
+        lib.oracle_saturate_int16.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
+        lib.oracle_norm_exact.argtypes = [C.c_void_p, C.c_int]
+        lib.oracle_norm_exact.restype = C.c_double
+        lib.oracle_sumsq.argtypes = [C.c_void_p, C.c_int]
+        lib.oracle_sumsq.restype = C.c_uint64
+        lib.oracle_splitmix64.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64]
+        lib.oracle_splitmix64.restype = C.c_uint64
+        _oracle = lib
+    return _oracle
+
+
+def ref_dir():
+    """Directory of a reference build that runs on this host (native first, then v3), or None."""
+    for variant in ("native", "v3"):
+        d = os.path.join(ORACLE_DIR, "_ref", variant)
+        exe = os.path.join(d, "standalone_projection")
+        if not os.path.exists(exe):
+            continue
+        try:
+            r = subprocess.run([exe], capture_output=True, timeout=20)
+            if r.returncode == 1:          # usage + exit 1 (standalone_projection.cpp:12-15)
+                return d
+        except Exception:
+            pass
+    return None
+
+
+def ref_lib():
+    global _ref
+    if _ref is None:
+        d = ref_dir()
+        if d is None:
+            return None
+        lib = C.CDLL(os.path.join(d, "libref_projection.so"))
+        lib.ref_transform_set.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_void_p]
+        lib.ref_project_csr.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p,
+                                        C.POINTER(C.c_double)]
+        _ref = lib
+    return _ref
+
+
+def oracle_set(hashes, d, seed=0):
+    h = np.ascontiguousarray(hashes, dtype=np.uint64)
+    out = np.empty(d, dtype=np.int32)
+    oracle().oracle_transform_set(h.ctypes.data, len(h), d, C.c_uint64(seed), out.ctypes.data)
+    return out
+
+
+def oracle_csr(hashes, offsets, d, seed=0):
+    h = np.ascontiguousarray(hashes, dtype=np.uint64)
+    o = np.ascontiguousarray(offsets, dtype=np.uint64)
+    n = len(o) - 1
+    out = np.empty((n, d), dtype=np.int32)
+    oracle().oracle_project_csr(h.ctypes.data, o.ctypes.data, n, d, C.c_uint64(seed), out.ctypes.data)
+    return out
+
+
+def ref_set(hashes, d):
+    h = np.ascontiguousarray(hashes, dtype=np.uint64)
+    out = np.empty(d, dtype=np.int32)
+    ref_lib().ref_transform_set(h.ctypes.data, len(h), d, out.ctypes.data)
+    return out
+
+
+def load_toy():
+    z = np.load(os.path.join(GOLDEN, "toy_hashes.npz"))
+    return [str(n) for n in z["names"]], z["offsets"].astype(np.uint64), z["hashes"].astype(np.uint64)
+
+
+def load_toy_ref(tag):
+    z = np.load(os.path.join(GOLDEN, "toy_ref_%s.npz" % tag))
+    return {k: (z[k] if z[k].shape else z[k].item()) for k in z.files}
+
+
+def load_kat():
+    return json.load(open(os.path.join(GOLDEN, "kat.json")))
+
+
+def parse_line_like_reference(text):
+    """istringstream >> unsigned long semantics of the reference parsers
+    (project_everything.cpp:275-279, standalone_projection.cpp:30-34): whitespace-separated
+    tokens; optional sign; a token that is not a number, or overflows 2^64-1, ends the line
+    (nothing inserted for it); '-N' wraps modulo 2^64.  Small-case oracle for the parser tests."""
+    out = []
+    for tok in text.split():
+        t = tok
+        neg = False
+        if t[:1] in "+-":
+            neg = t[0] == "-"
+            t = t[1:]
+        digits = ""
+        for ch in t:
+            if ch.isdigit() and ch.isascii():
+                digits += ch
+            else:
+                break
+        if not digits:
+            break
+        v = int(digits)
+        if v > 0xFFFFFFFFFFFFFFFF:
+            break
+        out.append((-v) & 0xFFFFFFFFFFFFFFFF if neg else v)
+        if len(digits) != len(t):          # trailing garbage: number is consumed, next >> fails
+            break
+    return out

@@ -1,0 +1,72 @@
+"""CPU tests of the drop-in boundary: the library loads without a GPU, exports every
+symbol include/mvs_b200.h declares, and fails loudly (no CPU fallback) when asked to compute."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import metagenome_vector_sketches_b200 as mvs
+from metagenome_vector_sketches_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "mvs_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(mvs_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_exported_and_bound():
+    lib = mvs.load_library()
+    names = _declared_symbols()
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(lib, n), "libmvs_b200.so does not export %s" % n
+        assert n in _lib.SIGNATURES, "ctypes binding misses %s" % n
+    assert sorted(_lib.SIGNATURES) == names
+    assert lib.mvs_abi_version() >= 1
+
+
+def test_strerror_and_argument_checks_need_no_gpu():
+    lib = mvs.load_library()
+    assert lib.mvs_strerror(0) == b"ok"
+    assert b"no CPU fallback" in lib.mvs_strerror(-2)
+    assert lib.mvs_create(None, 0) == -1
+    a = np.array([5, 3, 5, 1, 3], dtype=np.uint64)
+    n = lib.mvs_sort_unique(a.ctypes.data, len(a))
+    assert n == 3 and a[:3].tolist() == [1, 3, 5]
+
+
+def test_no_cpu_fallback_without_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(mvs.MvsError) as e:
+        mvs.Sketcher(0)
+    assert e.value.status == -2          # MVS_ERR_NO_DEVICE
+    with pytest.raises(mvs.MvsError):
+        mvs.transform_set_into_vector([1, 2, 3], 64)
+
+
+def test_product_does_not_reference_oracle():
+    pkg = os.path.join(ROOT, "metagenome_vector_sketches_b200")
+    for dp, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", "Makefile")):
+                txt = open(os.path.join(dp, f), errors="ignore").read()
+                assert "oracle/" not in txt and "liboracle" not in txt and "oracle_util" not in txt, f
+
+
+def test_synthetic_generator_is_injective_and_in_range():
+    h, off = mvs.synthetic.uniform_batch(64, 1000, seed=0)
+    assert len(np.unique(h)) == len(h) and int(h.max()) < 2 ** 54
+    h2, _ = mvs.synthetic.uniform_batch(64, 1000, seed=1)
+    assert not np.array_equal(h, h2)
+    sizes = mvs.synthetic.lognormal_sizes(2000, seed=0)
+    assert sizes.min() >= 1000 and sizes.max() <= 10 ** 7 and 1e4 < np.median(sizes) < 4e4
+    hr, offr = mvs.synthetic.ragged_batch([3, 0, 5], seed=0, first_sample=10)
+    assert offr.tolist() == [0, 3, 3, 8] and len(np.unique(hr)) == 8
+    assert np.array_equal(hr[:3], mvs.synthetic.synth_hashes([10, 10, 10], [0, 1, 2], 0))

@@ -1,0 +1,159 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through the C ABI,
+against the CPU oracle (bit-exact: integer work), the committed golden vectors from the
+reference, and size-independent properties at BASELINE sizes."""
+import hashlib
+
+import numpy as np
+import pytest
+
+import metagenome_vector_sketches_b200 as mvs
+from oracle_util import (oracle, oracle_set, oracle_csr, ref_lib, ref_set, load_toy, load_toy_ref, load_kat,
+                         parse_line_like_reference)
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def sk():
+    s = mvs.Sketcher(0)
+    yield s
+    s.close()
+
+
+def test_kats_standalone(sk):
+    for case in load_kat()["standalone"]:
+        d = case["d"]
+        for line, ref_out in zip(case["lines"], case["stdout"].split("\n")[:-1]):
+            vec = sk.transform_set(parse_line_like_reference(line), d)
+            assert " ".join("%g" % float(v) for v in vec) == ref_out
+
+
+@pytest.mark.parametrize("tag,d", [("d2048", 2048), ("d100", 100)])
+def test_toy_golden_bit_exact(sk, tag, d):
+    names, offsets, hashes = load_toy()
+    ref = load_toy_ref(tag)
+    got = sk.project_csr(hashes, offsets, d)
+    assert np.array_equal(got, ref["vectors"].astype(np.int32))
+    assert hashlib.sha256(got.tobytes()).hexdigest() == ref["vectors_sha256"]
+
+
+def test_toy_epilogue_int16_and_norms(sk):
+    names, offsets, hashes = load_toy()
+    ref16 = load_toy_ref("d2048_i16")
+    got = sk.project_csr(hashes, offsets, 2048)
+    sumsq, out16 = sk.finalize(got, want_int16=True)
+    assert np.array_equal(out16, ref16["vectors"])
+    assert hashlib.sha256(out16.tobytes()).hexdigest() == ref16["vectors_sha256"]
+    for row, ss, line in zip(got, sumsq, ref16["norms_txt"].split("\n")[:-1]):
+        assert int(ss) == int(oracle().oracle_sumsq(row.ctypes.data, 2048))
+        printed = float(line.rsplit(" ", 1)[1])
+        exact = mvs.norm_from_sumsq(ss, 2048)
+        ulp6 = 10.0 ** (np.floor(np.log10(exact)) - 5) if exact > 0 else 0.0
+        assert abs(printed - exact) <= 0.5 * ulp6 + 2e-6 * exact     # stated tolerance: print precision + f32
+
+
+def test_int16_saturation_edges(sk):
+    v = np.array([[40000, -40000, 32767, -32768, 32768, -32769, 0, 1]], dtype=np.int32)
+    sumsq, o16 = sk.finalize(v, want_int16=True)
+    assert o16.tolist() == [[32767, -32768, 32767, -32768, 32767, -32768, 0, 1]]
+    assert int(sumsq[0]) == int((v.astype(np.int64) ** 2).sum())
+
+
+@pytest.mark.parametrize("d", [1, 7, 63, 64, 65, 100, 128, 192, 256, 320, 512, 1000, 1024, 1536, 2048,
+                               2049, 2112, 4096, 4160, 5000])
+def test_random_sets_all_dimensions(sk, d):
+    rng = np.random.default_rng(1000 + d)
+    sizes = [0, 1, 2, 15, 16, 17, 31, 33, 100, 511, 512, 513, 1025, 4079, 4080, 4081, 9000]
+    if d <= 256:
+        sizes += [4080 * (32 // max(1, 1 << int(np.ceil(np.log2(max(1, (d + 63) // 64)))))) + 5, 70000]
+    sets = [np.unique(rng.integers(0, 2 ** 64 - 1, n, dtype=np.uint64)) for n in sizes]
+    offsets = np.zeros(len(sets) + 1, dtype=np.uint64)
+    offsets[1:] = np.cumsum([len(s) for s in sets])
+    hashes = np.concatenate(sets)
+    got = sk.project_csr(hashes, offsets, d)
+    want = oracle_csr(hashes, offsets, d)
+    assert np.array_equal(got, want)
+
+
+def test_seed_is_additive_and_zero_is_reference(sk):
+    rng = np.random.default_rng(5)
+    h = np.unique(rng.integers(0, 2 ** 63, 3000, dtype=np.uint64))
+    for seed in (0, 1, 12345, 2 ** 64 - 1):
+        assert np.array_equal(sk.transform_set(h, 2048, seed=seed), oracle_set(h, 2048, seed=seed))
+    with np.errstate(over="ignore"):
+        assert np.array_equal(sk.transform_set(h, 512, seed=77), sk.transform_set(h + np.uint64(77), 512))
+
+
+def test_large_sample_split_across_warp_tasks(sk):
+    # one sample >> task capacity: partial rows + fixed-order reduce
+    h, off = mvs.synthetic.uniform_batch(1, 300000, seed=3)
+    got = sk.project_csr(h, off, 2048)
+    assert np.array_equal(got, oracle_csr(h, off, 2048))
+    t = sk.timing()
+    assert t["partial_rows"] >= 300000 // 4080
+
+
+def test_many_slices_and_empty_samples(sk):
+    sk.set_option("slice_hashes", 50000)
+    try:
+        sizes = [0, 7000, 0, 0, 120000, 3, 49999, 50001, 0, 16, 80000, 1]
+        h, off = mvs.synthetic.ragged_batch(sizes, seed=9)
+        got = sk.project_csr(h, off, 1024)
+        assert np.array_equal(got, oracle_csr(h, off, 1024))
+        assert not got[0].any() and not got[2].any()
+    finally:
+        sk.set_option("slice_hashes", 16 << 20)
+
+
+def test_properties_at_scale(sk):
+    """Size-independent properties on a batch too big for the scalar oracle (1.6e7 hashes)."""
+    n, per, d = 320, 50000, 2048
+    h, off = mvs.synthetic.uniform_batch(n, per, seed=0)
+    full = sk.project_csr(h, off, d)
+    # (1) linearity: halves of every sample projected separately add up
+    off2 = np.arange(2 * n + 1, dtype=np.uint64) * np.uint64(per // 2)
+    halves = sk.project_csr(h, off2, d)
+    assert np.array_equal(halves[0::2] + halves[1::2], full)
+    # (2) prefix property: d' = 512 equals the first 512 columns
+    assert np.array_equal(sk.project_csr(h, off, 512), full[:, :512])
+    # (3) parity of every entry equals parity of |H| (sum of +-1), and |v| <= |H|
+    assert np.all((full & 1) == (per & 1)) and np.abs(full).max() <= per
+    # (4) spot-check rows against the oracle
+    for s in (0, 151, n - 1):
+        assert np.array_equal(full[s], oracle_set(h[int(off[s]):int(off[s + 1])], d))
+    # (5) one merged sample = sum of all rows (split across many tasks + reduce)
+    merged = sk.project_csr(h, np.array([0, len(h)], dtype=np.uint64), d)
+    assert np.array_equal(merged[0], full.sum(axis=0, dtype=np.int64).astype(np.int32))
+
+
+def test_device_resident_entry_point(sk):
+    import torch
+    h, off = mvs.synthetic.uniform_batch(64, 20000, seed=2)
+    dh = torch.from_numpy(h.view(np.int64)).cuda()
+    dout = torch.empty((64, 2048), dtype=torch.int32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    sk.project_device(dh.data_ptr(), off, 2048, dout.data_ptr(), stream=st)
+    torch.cuda.synchronize()
+    assert np.array_equal(dout.cpu().numpy(), oracle_csr(h, off, 2048))
+    t = sk.timing()
+    assert t["kernel_ms"] > 0 and t["launches"] > 0
+
+
+def test_live_reference_if_built(sk):
+    if ref_lib() is None:
+        pytest.skip("oracle/_ref not present on this host")
+    rng = np.random.default_rng(21)
+    for n, d in [(1, 64), (999, 2048), (5000, 300)]:
+        h = np.unique(rng.integers(0, 2 ** 64 - 1, n, dtype=np.uint64))
+        assert np.array_equal(sk.transform_set(h, d), ref_set(h, d))
+
+
+def test_error_paths(sk):
+    lib = mvs.load_library()
+    out = np.zeros(64, dtype=np.int32)
+    bad_off = np.array([5, 3], dtype=np.uint64)
+    h = np.arange(8, dtype=np.uint64)
+    assert lib.mvs_project_batch(sk._h, h.ctypes.data, bad_off.ctypes.data, 1, 64, 0, out.ctypes.data) == -1
+    assert lib.mvs_project_batch(sk._h, h.ctypes.data, bad_off.ctypes.data, 1, 0, 0, out.ctypes.data) == -1
+    assert lib.mvs_project_batch(sk._h, None, None, 1, 64, 0, out.ctypes.data) == -1
+    assert lib.mvs_project_batch(sk._h, h.ctypes.data, bad_off.ctypes.data, 0, 64, 0, None) == 0

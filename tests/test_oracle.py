@@ -1,0 +1,104 @@
+"""CPU tests: pin the oracle (oracle/mvs_oracle.c) against the reference's own outputs.
+
+Golden fixtures in tests/golden were produced by the unmodified reference binaries
+(tests/golden/make_golden.py); when oracle/_ref is prebuilt it is also called live."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from oracle_util import (oracle, oracle_set, oracle_csr, ref_lib, ref_set, load_toy, load_toy_ref, load_kat,
+                         parse_line_like_reference)
+
+
+def test_splitmix_kat1():
+    # splitmix64(0) = 0xE220A8397B1DCDAF
+    assert oracle().oracle_splitmix64(0, 0, 0) == 0xE220A8397B1DCDAF
+
+
+def test_standalone_kats():
+    kat = load_kat()
+    for case in kat["standalone"]:
+        d = case["d"]
+        got_lines = case["stdout"].split("\n")[:-1]
+        assert len(got_lines) == len(case["lines"])
+        for line, ref_out in zip(case["lines"], got_lines):
+            hs = sorted(set(parse_line_like_reference(line)))
+            vec = oracle_set(np.array(hs, dtype=np.uint64), d)
+            # standalone_projection prints static_cast<float>(v) with default ostream formatting
+            assert " ".join("%g" % float(v) for v in vec) == ref_out
+
+
+def test_sketch_parser_kat():
+    kat = load_kat()["sketch_parser"]
+    d = kat["d"]
+    rows = []
+    for line in kat["text"].split("\n"):
+        if ":" not in line:
+            continue
+        rest = line[line.index(":") + 1:]
+        hs = sorted(set(parse_line_like_reference(rest)))
+        rows.append(oracle_set(np.array(hs, dtype=np.uint64), d))
+    assert np.array_equal(np.concatenate(rows), np.array(kat["vectors"], dtype=np.int32))
+
+
+@pytest.mark.parametrize("tag,d", [("d2048", 2048), ("d100", 100)])
+def test_toy_golden(tag, d):
+    names, offsets, hashes = load_toy()
+    ref = load_toy_ref(tag)
+    got = oracle_csr(hashes, offsets, d)
+    assert np.array_equal(got, ref["vectors"].astype(np.int32))
+    assert hashlib.sha256(got.tobytes()).hexdigest() == ref["vectors_sha256"]
+    if d == 2048:
+        assert ref["vectors_sha256"] == "93fb4358e2774ad31cd50fe8f00a1eb6a97aa0ad029f166654bbf3385df74cb8"
+        assert got[0, :8].tolist() == [88, -118, 22, 30, -10, -22, 56, -72]
+
+
+def test_toy_norms_within_print_precision():
+    names, offsets, hashes = load_toy()
+    ref = load_toy_ref("d2048")
+    got = oracle_csr(hashes, offsets, 2048)
+    lines = ref["norms_txt"].split("\n")[:-1]
+    assert [l.rsplit(" ", 1)[0] for l in lines] == names
+    for row, line in zip(got, lines):
+        exact = oracle().oracle_norm_exact(row.ctypes.data, 2048)
+        printed = float(line.rsplit(" ", 1)[1])
+        # reference prints a float32 Eigen norm with 6 significant digits
+        # half a unit of the 6th significant digit + 2e-6 relative for the float32 evaluation
+        ulp6 = 10.0 ** (np.floor(np.log10(exact)) - 5) if exact > 0 else 0.0
+        assert abs(printed - exact) <= 0.5 * ulp6 + 2e-6 * exact
+
+
+def test_int16_golden_matches_saturation():
+    ref32 = load_toy_ref("d2048")["vectors"].astype(np.int32)
+    ref16 = load_toy_ref("d2048_i16")["vectors"]
+    out = np.empty(ref32.size, dtype=np.int16)
+    oracle().oracle_saturate_int16(ref32.ctypes.data, ref32.size, out.ctypes.data)
+    assert np.array_equal(out.reshape(ref32.shape), ref16)
+    big = np.array([40000, -40000, 32767, -32768, 32768, -32769, 0], dtype=np.int32)
+    o = np.empty(big.size, dtype=np.int16)
+    oracle().oracle_saturate_int16(big.ctypes.data, big.size, o.ctypes.data)
+    assert o.tolist() == [32767, -32768, 32767, -32768, 32767, -32768, 0]
+
+
+def test_properties():
+    rng = np.random.default_rng(7)
+    a = np.unique(rng.integers(0, 2 ** 63, 300, dtype=np.uint64))
+    b = np.unique(rng.integers(2 ** 63, 2 ** 64 - 1, 200, dtype=np.uint64))
+    d = 200
+    va, vb = oracle_set(a, d), oracle_set(b, d)
+    assert np.array_equal(oracle_set(np.concatenate([a, b]), d), va + vb)        # linearity over disjoint unions
+    assert np.array_equal(oracle_set(a, 2048)[:d], va)                           # prefix property
+    one = np.array([123456789], dtype=np.uint64)
+    assert np.array_equal(oracle_set(one, 256)[64:128], oracle_set(one + np.uint64(64), 64))   # block shift
+    assert not oracle_set(np.zeros(0, dtype=np.uint64), 77).any()                # empty set
+    assert np.array_equal(oracle_set(a, d, seed=5), oracle_set(a + np.uint64(5), d))           # additive seed
+
+
+def test_live_reference_if_built():
+    if ref_lib() is None:
+        pytest.skip("oracle/_ref not built on this host")
+    rng = np.random.default_rng(11)
+    for n, d in [(0, 64), (1, 1), (17, 63), (500, 2048), (1000, 130), (3, 4160)]:
+        h = np.unique(rng.integers(0, 2 ** 64 - 1, n, dtype=np.uint64))
+        assert np.array_equal(ref_set(h, d), oracle_set(h, d))
