@@ -103,9 +103,12 @@ int mvs_host_unregister(void* p);
 
 /* ---- measurement ------------------------------------------------------------------ */
 typedef struct mvs_timing {
-    float kernel_ms;       /* CUDA-event time of the projection (+ partial-reduce) kernels of
-                              the last mvs_project_device call, measured on its stream */
-    float reduce_ms;       /* the partial-reduce kernel alone */
+    float kernel_ms;       /* mean CUDA-event time (on the launching stream) of the projection +
+                              partial-reduce kernels over the mvs_project_device calls made since
+                              the previous mvs_get_timing (at most the last 64) */
+    float reduce_ms;       /* the partial-reduce kernel alone, same averaging */
+    uint32_t calls;        /* number of calls averaged */
+    uint32_t reserved;
     uint64_t launches;     /* kernels launched by this context since creation */
     uint64_t warp_tasks;   /* warp tasks of the last projection call */
     uint64_t partial_rows; /* partial rows of the last projection call */

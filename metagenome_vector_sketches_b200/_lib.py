@@ -24,6 +24,7 @@ class MvsError(RuntimeError):
 
 class Timing(C.Structure):
     _fields_ = [("kernel_ms", C.c_float), ("reduce_ms", C.c_float),
+                ("calls", C.c_uint32), ("reserved", C.c_uint32),
                 ("launches", C.c_uint64), ("warp_tasks", C.c_uint64),
                 ("partial_rows", C.c_uint64), ("h2d_bytes", C.c_uint64),
                 ("d2h_bytes", C.c_uint64)]

@@ -25,6 +25,7 @@ using mvs::WarpTask;
 
 constexpr int kSlots = 3;                        // slices in flight in mvs_project_batch
 constexpr int kAbiVersion = 1;
+constexpr int kTimingRing = 64;
 
 struct DevBuf {
     void* p = nullptr;
@@ -62,8 +63,11 @@ struct mvs_ctx {
     int sm_count = 0;
     int last_cuda = 0;
     Slot slots[kSlots];
-    cudaEvent_t ev_start = nullptr, ev_mid = nullptr, ev_end = nullptr;
-    bool timing_valid = false;
+    // ring of CUDA-event triples (start, after projection, after reduce), one per
+    // mvs_project_device call; mvs_get_timing averages the calls since the last query
+    cudaEvent_t ev[kTimingRing][3] = {};
+    uint64_t timing_calls = 0;                   // device-path calls recorded so far
+    uint64_t timing_read = 0;                    // calls already consumed by mvs_get_timing
     mvs_timing timing{};
     uint64_t launches = 0;
     uint64_t slice_hashes = 16ull << 20;         // hashes per streamed slice (128 MB)
@@ -258,12 +262,13 @@ int run_range(mvs_ctx* ctx, Slot& sl, const uint64_t* d_hashes, const uint64_t* 
                                       cudaMemcpyHostToDevice, st));
     MVS_CUDA(ctx, cudaEventRecord(sl.uploaded, st));
     sl.upload_busy = true;
-    if (record_timing) MVS_CUDA(ctx, cudaEventRecord(ctx->ev_start, st));
+    cudaEvent_t* ev = ctx->ev[ctx->timing_calls % kTimingRing];
+    if (record_timing) MVS_CUDA(ctx, cudaEventRecord(ev[0], st));
     MVS_CUDA(ctx, launch_project(g, st, static_cast<uint32_t>(pc.tasks), d_hashes,
                                  static_cast<const WarpTask*>(sl.tasks.p), seed, d_out,
                                  static_cast<int32_t*>(sl.partials.p)));
     ctx->launches += 1;
-    if (record_timing) MVS_CUDA(ctx, cudaEventRecord(ctx->ev_mid, st));
+    if (record_timing) MVS_CUDA(ctx, cudaEventRecord(ev[1], st));
     if (pc.reduce) {
         const unsigned gy = static_cast<unsigned>(std::min<int64_t>((g.d + 255) / 256, 65535));
         dim3 grid(static_cast<unsigned>(pc.reduce), gy);
@@ -274,8 +279,8 @@ int run_range(mvs_ctx* ctx, Slot& sl, const uint64_t* d_hashes, const uint64_t* 
         ctx->launches += 1;
     }
     if (record_timing) {
-        MVS_CUDA(ctx, cudaEventRecord(ctx->ev_end, st));
-        ctx->timing_valid = true;
+        MVS_CUDA(ctx, cudaEventRecord(ev[2], st));
+        ctx->timing_calls += 1;
     }
     ctx->timing.warp_tasks = pc.tasks;
     ctx->timing.partial_rows = pc.prows;
@@ -356,9 +361,8 @@ int mvs_create(mvs_ctx** out, int device)
         chk(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
         chk(cudaEventCreateWithFlags(&sl.uploaded, cudaEventDisableTiming));
     }
-    chk(cudaEventCreate(&ctx->ev_start));
-    chk(cudaEventCreate(&ctx->ev_mid));
-    chk(cudaEventCreate(&ctx->ev_end));
+    for (auto& e3 : ctx->ev)
+        for (auto& e : e3) chk(cudaEventCreate(&e));
     chk(cudaMalloc(reinterpret_cast<void**>(&ctx->d_sink), 256));
     if (rc != MVS_OK) {
         mvs_destroy(ctx);
@@ -382,9 +386,9 @@ void mvs_destroy(mvs_ctx* ctx)
         if (sl.uploaded) cudaEventDestroy(sl.uploaded);
         if (sl.stream) cudaStreamDestroy(sl.stream);
     }
-    if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
-    if (ctx->ev_mid) cudaEventDestroy(ctx->ev_mid);
-    if (ctx->ev_end) cudaEventDestroy(ctx->ev_end);
+    for (auto& e3 : ctx->ev)
+        for (auto& e : e3)
+            if (e) cudaEventDestroy(e);
     if (ctx->d_sink) cudaFree(ctx->d_sink);
     cudaGetLastError();
     delete ctx;
@@ -428,7 +432,6 @@ int mvs_project_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offs
     const int64_t max_rows = std::max<int64_t>(1, static_cast<int64_t>(ctx->slice_rows_bytes / row_bytes));
     ctx->timing.h2d_bytes = 0;
     ctx->timing.d2h_bytes = 0;
-    ctx->timing_valid = false;
 
     int rc = MVS_OK;
     int64_t s0 = 0;
@@ -566,17 +569,24 @@ int mvs_get_timing(mvs_ctx* ctx, mvs_timing* t)
 {
     if (!ctx || !t) return MVS_ERR_INVALID_ARG;
     MVS_CUDA(ctx, cudaSetDevice(ctx->device));
-    if (ctx->timing_valid) {
-        MVS_CUDA(ctx, cudaEventSynchronize(ctx->ev_end));
+    // mean over the device-path calls since the previous query (at most the ring size)
+    uint64_t first = ctx->timing_read;
+    if (ctx->timing_calls - first > static_cast<uint64_t>(kTimingRing)) first = ctx->timing_calls - kTimingRing;
+    double sum_a = 0.0, sum_b = 0.0;
+    uint32_t n = 0;
+    for (uint64_t c = first; c < ctx->timing_calls; ++c, ++n) {
+        cudaEvent_t* ev = ctx->ev[c % kTimingRing];
+        MVS_CUDA(ctx, cudaEventSynchronize(ev[2]));
         float a = 0.f, b = 0.f;
-        MVS_CUDA(ctx, cudaEventElapsedTime(&a, ctx->ev_start, ctx->ev_end));
-        MVS_CUDA(ctx, cudaEventElapsedTime(&b, ctx->ev_mid, ctx->ev_end));
-        ctx->timing.kernel_ms = a;
-        ctx->timing.reduce_ms = b;
-    } else {
-        ctx->timing.kernel_ms = 0.f;
-        ctx->timing.reduce_ms = 0.f;
+        MVS_CUDA(ctx, cudaEventElapsedTime(&a, ev[0], ev[2]));
+        MVS_CUDA(ctx, cudaEventElapsedTime(&b, ev[1], ev[2]));
+        sum_a += a;
+        sum_b += b;
     }
+    ctx->timing_read = ctx->timing_calls;
+    ctx->timing.kernel_ms = n ? static_cast<float>(sum_a / n) : 0.f;
+    ctx->timing.reduce_ms = n ? static_cast<float>(sum_b / n) : 0.f;
+    ctx->timing.calls = n;
     ctx->timing.launches = ctx->launches;
     *t = ctx->timing;
     return MVS_OK;

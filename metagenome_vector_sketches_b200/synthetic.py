@@ -71,3 +71,33 @@ def ragged_batch(sizes, seed=0, first_sample=0):
     s = np.repeat(np.arange(first_sample, first_sample + len(sizes), dtype=np.uint64), sizes)
     k = np.arange(total, dtype=np.uint64) - np.repeat(offsets[:-1], sizes)
     return synth_hashes(s, k, seed), offsets
+
+
+def _s64(v):
+    """uint64 constant as the int64 with the same bits (torch has no uint64 arithmetic)."""
+    v &= 0xFFFFFFFFFFFFFFFF
+    return v - (1 << 64) if v >= (1 << 63) else v
+
+
+def uniform_batch_torch(n_samples, hashes_per_sample, device, seed=0, first_sample=0, chunk_samples=512):
+    """Same batch as uniform_batch(), generated on `device` with torch int64 ops (bit-identical:
+    products wrap modulo 2^64 and every intermediate is masked to 54 bits, so it stays >= 0).
+    Returns (int64 tensor holding the uint64 bit patterns, numpy uint64 offsets)."""
+    import torch
+    out = torch.empty(n_samples * hashes_per_sample, dtype=torch.int64, device=device)
+    k = torch.arange(hashes_per_sample, dtype=torch.int64, device=device)
+    sx = (seed * _M1) & MASK54
+    for s0 in range(0, n_samples, chunk_samples):
+        s1 = min(n_samples, s0 + chunk_samples)
+        s = torch.arange(first_sample + s0, first_sample + s1, dtype=torch.int64, device=device)
+        x = ((s << 24)[:, None] | k[None, :]).reshape(-1)
+        x = x ^ sx
+        x = (x * _s64(_M1)) & MASK54
+        x = x ^ (x >> 29)
+        x = (x * _s64(_M2)) & MASK54
+        x = x ^ (x >> 27)
+        x = (x * _s64(_M3)) & MASK54
+        x = x ^ (x >> 31)
+        out[s0 * hashes_per_sample:s1 * hashes_per_sample] = x
+    offsets = np.arange(n_samples + 1, dtype=np.uint64) * np.uint64(hashes_per_sample)
+    return out, offsets
