@@ -119,7 +119,9 @@ int mvs_get_timing(mvs_ctx* ctx, mvs_timing* t);    /* synchronises the context'
 
 /* Integer issue-rate microbenchmark used as the roofline denominator.
  * which: 0 = LOP3 (ALU pipe), 1 = IMAD (FMA pipe), 2 = LOP3+IMAD interleaved 1:1,
- *        3 = IADD3, 4 = SHF.  Writes 32-bit lane-operations per second. */
+ *        3 = IADD3, 4 = SHF, 5 = IMAD.WIDE, 6 = IMAD.HI, 7 = SHF funnel, 8 = LOP3:IMAD 2:1,
+ *        9 = LOP3:SHF 1:1.  Writes 32-bit lane-instructions per second (mode 5 issues one
+ *        IMAD.WIDE + one LOP3 per counted op). */
 int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second);
 
 /* Kernel tuning knobs for experiments (0 = default).  Unknown keys are ignored. */

@@ -594,7 +594,7 @@ int mvs_get_timing(mvs_ctx* ctx, mvs_timing* t)
 
 int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second)
 {
-    if (!ctx || !ops_per_second || which < 0 || which > 4) return MVS_ERR_INVALID_ARG;
+    if (!ctx || !ops_per_second || which < 0 || which > 9) return MVS_ERR_INVALID_ARG;
     MVS_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->slots[0].stream;
     const int iters = 4096;
@@ -605,13 +605,14 @@ int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second)
     float best = 1e30f;
     for (int rep = 0; rep < 4; ++rep) {
         cudaEventRecord(e0, st);
+#define MVS_BENCH_CASE(M) \
+    case M: mvs::issue_bench_kernel<M><<<grid, 256, 0, st>>>(ctx->d_sink, iters, 0x9e3779b9u, 0x85ebca6bu); break;
         switch (which) {
-            case 0: mvs::issue_bench_kernel<0><<<grid, 256, 0, st>>>(ctx->d_sink, iters, 0x9e3779b9u, 0x85ebca6bu); break;
-            case 1: mvs::issue_bench_kernel<1><<<grid, 256, 0, st>>>(ctx->d_sink, iters, 0x9e3779b9u, 0x85ebca6bu); break;
-            case 2: mvs::issue_bench_kernel<2><<<grid, 256, 0, st>>>(ctx->d_sink, iters, 0x9e3779b9u, 0x85ebca6bu); break;
-            case 3: mvs::issue_bench_kernel<3><<<grid, 256, 0, st>>>(ctx->d_sink, iters, 0x9e3779b9u, 0x85ebca6bu); break;
-            default: mvs::issue_bench_kernel<4><<<grid, 256, 0, st>>>(ctx->d_sink, iters, 0x9e3779b9u, 0x85ebca6bu); break;
+            MVS_BENCH_CASE(0) MVS_BENCH_CASE(1) MVS_BENCH_CASE(2) MVS_BENCH_CASE(3) MVS_BENCH_CASE(4)
+            MVS_BENCH_CASE(5) MVS_BENCH_CASE(6) MVS_BENCH_CASE(7) MVS_BENCH_CASE(8) MVS_BENCH_CASE(9)
+            default: break;
         }
+#undef MVS_BENCH_CASE
         cudaEventRecord(e1, st);
         cudaError_t e = cudaEventSynchronize(e1);
         if (e == cudaSuccess) e = cudaGetLastError();

@@ -279,11 +279,11 @@ __global__ void __launch_bounds__(256)
 reduce_partials_kernel(const ReduceItem* __restrict__ items, uint32_t nitems, int d,
                        const int32_t* __restrict__ partials, int32_t* __restrict__ out)
 {
-    const uint32_t it = blockIdx.y;
+    const uint32_t it = blockIdx.x;              // grid = (items, column blocks)
     if (it >= nitems) return;
     const ReduceItem r = items[it];
     const int32_t* p = partials + static_cast<size_t>(r.prow) * static_cast<size_t>(d);
-    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < d; j += gridDim.x * blockDim.x) {
+    for (int j = blockIdx.y * blockDim.x + threadIdx.x; j < d; j += gridDim.y * blockDim.x) {
         int32_t acc = 0;
         for (uint32_t c = 0; c < r.nchunks; ++c) acc += p[static_cast<size_t>(c) * d + j];
         out[static_cast<size_t>(r.sample) * d + j] = static_cast<int32_t>(r.n) - 2 * acc;
@@ -336,9 +336,23 @@ issue_bench_kernel(uint32_t* sink, int iters, uint32_t k0, uint32_t k1)
                     if (i & 1) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(k0), "r"(k1));
                     else       asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(k0), "r"(k1));
                 } else if (MODE == 3) {
-                    asm volatile("add.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(k0));
-                } else {
+                    asm volatile("add.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(a[(i + 3) & 7]));   // not foldable
+                } else if (MODE == 4) {
                     asm volatile("shf.r.wrap.b32 %0, %0, %1, 7;" : "+r"(a[i]) : "r"(k1));
+                } else if (MODE == 5) {          // IMAD.WIDE.U32 (64-bit result, low word fed back)
+                    unsigned long long w;
+                    asm volatile("mul.wide.u32 %0, %1, %2;" : "=l"(w) : "r"(a[i]), "r"(k0));
+                    a[i] = static_cast<uint32_t>(w) ^ static_cast<uint32_t>(w >> 32);
+                } else if (MODE == 6) {          // IMAD.HI.U32
+                    asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(k0), "r"(k1));
+                } else if (MODE == 7) {          // 64-bit funnel shift SHF.R.U64 + LOP3 pairs
+                    asm volatile("shf.r.clamp.b32 %0, %0, %1, 27;" : "+r"(a[i]) : "r"(a[(i + 1) & 7]));
+                } else if (MODE == 8) {          // LOP3 : IMAD = 2 : 1
+                    if ((i % 3) == 2) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(k0), "r"(k1));
+                    else              asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(k0), "r"(k1));
+                } else {                         // LOP3 : SHF = 1 : 1 (both ALU pipe?)
+                    if (i & 1) asm volatile("shf.r.wrap.b32 %0, %0, %1, 7;" : "+r"(a[i]) : "r"(k1));
+                    else       asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(k0), "r"(k1));
                 }
             }
         }
