@@ -73,6 +73,15 @@ int mvs_transform_set(mvs_ctx* ctx, const uint64_t* hashes, int64_t n_hashes, in
 int mvs_project_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offsets,
                       int64_t n_samples, int d, uint64_t seed, int32_t* out);
 
+/* mvs_project_batch fused with the epilogue of sketch() (reference
+ * src/project_everything.cpp:327-347): any of the three HOST outputs may be NULL.
+ *   out    n_samples*d int32   (vectors.bin, int32 mode)
+ *   out16  n_samples*d int16   (vectors.bin, --int16 mode: saturated to [-32768, 32767])
+ *   sumsq  n_samples uint64    (exact sum of squares; norm = sqrt(sumsq / d)) */
+int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offsets,
+                     int64_t n_samples, int d, uint64_t seed, int32_t* out, int16_t* out16,
+                     uint64_t* sumsq);
+
 /* Same computation with the hash array and the output already resident in HBM.
  * d_hashes / d_out are DEVICE pointers on the context's GPU, h_offsets is a HOST array
  * (n_samples+1 entries indexing d_hashes).  `stream` is a cudaStream_t (NULL = the
@@ -90,6 +99,47 @@ int mvs_finalize_device(mvs_ctx* ctx, const int32_t* d_vec, int64_t n_samples, i
 /* Host-pointer convenience wrapper of the above (copies in and out). */
 int mvs_finalize(mvs_ctx* ctx, const int32_t* vec, int64_t n_samples, int d,
                  uint64_t* sumsq, int16_t* out16);
+
+/* ---- drivers: the reference's two CLIs as library calls ------------------------------ */
+typedef struct mvs_hash_batch {
+    int64_t n_samples;
+    uint64_t n_hashes;
+    uint64_t* hashes;        /* CSR payload, sorted + unique inside each sample (pinned if possible) */
+    uint64_t* offsets;       /* n_samples + 1 */
+    char** names;            /* n_samples C strings (text before the first ':'); NULL if !named */
+    int hashes_pinned;
+} mvs_hash_batch;
+
+/* Parser of sketch() (named = 1: "<name>: h1 h2 ...", lines without ':' skipped; reference
+ * src/project_everything.cpp:264-282) and of standalone_projection (named = 0: one set per
+ * line, empty line = empty set; reference src/standalone_projection.cpp:27-34).  Token
+ * semantics are those of `istringstream >> unsigned long`.  Needs no GPU. */
+int mvs_parse_hash_file(const char* path, int named, mvs_hash_batch** out);
+void mvs_free_hash_batch(mvs_hash_batch* b);
+
+/* db/ writer of sketch() (reference src/project_everything.cpp:306-361): vectors.bin (int32
+ * rows, or int16 if vec16 != NULL), vector_norms.txt ("<name> <sqrt(sumsq/d)>", %g),
+ * dimension.txt, dtype.txt.  Needs no GPU. */
+int mvs_write_db(const char* index_folder, int64_t n_samples, int d, const char* const* names,
+                 const uint64_t* sumsq, const int32_t* vec32, const int16_t* vec16);
+
+/* Contiguous size-balanced static partition of a CSR batch over n_parts GPUs; writes
+ * n_parts + 1 sample bounds.  No collective is needed afterwards: samples are independent. */
+void mvs_partition_samples(const uint64_t* offsets, int64_t n_samples, int n_parts, int64_t* bounds);
+
+/* sketch() end to end (reference src/project_everything.cpp:238-362): wipes/creates
+ * index_folder, parses, projects on n_ctx GPUs (one context + host thread each), writes db/. */
+int mvs_sketch_file(mvs_ctx* const* ctxs, int n_ctx, const char* hash_file, const char* index_folder,
+                    int d, int use_int16, uint64_t seed, int verbose);
+
+/* standalone_projection main (reference src/standalone_projection.cpp:11-46): one vector per
+ * input line printed as floats separated by ' '.  out_path NULL = stdout. */
+int mvs_standalone_file(mvs_ctx* ctx, const char* hashes_file, int d, uint64_t seed, const char* out_path);
+
+/* `project_everything convert` (reference src/project_everything.cpp:181-235) in process:
+ * every *.sig.zip of the folder -> one "<name>: h1 h2 ..." line (k=31 `mins`), files in sorted
+ * order, zip/gzip read with zlib instead of system("unzip"/"gunzip").  Needs no GPU. */
+int mvs_convert_signatures(const char* signature_folder, const char* hash_file, int threads, int verbose);
 
 /* ---- helpers ---------------------------------------------------------------------- */
 /* In-place sort + unique of one sample's hashes (set semantics of the reference's

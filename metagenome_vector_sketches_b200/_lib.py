@@ -30,6 +30,11 @@ class Timing(C.Structure):
                 ("d2h_bytes", C.c_uint64)]
 
 
+class HashBatch(C.Structure):
+    _fields_ = [("n_samples", C.c_int64), ("n_hashes", C.c_uint64), ("hashes", C.POINTER(C.c_uint64)),
+                ("offsets", C.POINTER(C.c_uint64)), ("names", C.POINTER(C.c_char_p)), ("hashes_pinned", C.c_int)]
+
+
 # name -> (restype, argtypes); must list every symbol of include/mvs_b200.h
 SIGNATURES = {
     "mvs_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
@@ -39,10 +44,21 @@ SIGNATURES = {
     "mvs_abi_version": (C.c_int, []),
     "mvs_transform_set": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64, C.c_void_p]),
     "mvs_project_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64, C.c_void_p]),
+    "mvs_sketch_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64, C.c_void_p,
+                                   C.c_void_p, C.c_void_p]),
     "mvs_project_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64,
                                      C.c_void_p, C.c_void_p]),
     "mvs_finalize_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "mvs_finalize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]),
+    "mvs_parse_hash_file": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.POINTER(HashBatch))]),
+    "mvs_free_hash_batch": (None, [C.POINTER(HashBatch)]),
+    "mvs_write_db": (C.c_int, [C.c_char_p, C.c_int64, C.c_int, C.POINTER(C.c_char_p), C.c_void_p, C.c_void_p,
+                               C.c_void_p]),
+    "mvs_partition_samples": (None, [C.c_void_p, C.c_int64, C.c_int, C.c_void_p]),
+    "mvs_sketch_file": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_char_p, C.c_char_p, C.c_int, C.c_int,
+                                  C.c_uint64, C.c_int]),
+    "mvs_standalone_file": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_uint64, C.c_char_p]),
+    "mvs_convert_signatures": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int, C.c_int]),
     "mvs_sort_unique": (C.c_int64, [C.c_void_p, C.c_int64]),
     "mvs_host_alloc": (C.c_void_p, [C.c_size_t]),
     "mvs_host_free": (None, [C.c_void_p]),

@@ -42,7 +42,7 @@ struct Slot {
     cudaEvent_t uploaded = nullptr;              // the pinned plan buffers have been read by the copy engine
     bool busy = false;
     bool upload_busy = false;
-    DevBuf hashes, out, partials, tasks, reduce;
+    DevBuf hashes, out, partials, tasks, reduce, sumsq, out16;
     PinBuf h_tasks, h_reduce;
 };
 
@@ -378,7 +378,7 @@ void mvs_destroy(mvs_ctx* ctx)
     cudaSetDevice(ctx->device);
     for (auto& sl : ctx->slots) {
         if (sl.stream) cudaStreamSynchronize(sl.stream);
-        for (DevBuf* b : {&sl.hashes, &sl.out, &sl.partials, &sl.tasks, &sl.reduce})
+        for (DevBuf* b : {&sl.hashes, &sl.out, &sl.partials, &sl.tasks, &sl.reduce, &sl.sumsq, &sl.out16})
             if (b->p) cudaFree(b->p);
         for (PinBuf* b : {&sl.h_tasks, &sl.h_reduce})
             if (b->p) cudaFreeHost(b->p);
@@ -417,10 +417,11 @@ int mvs_project_device(mvs_ctx* ctx, const uint64_t* d_hashes, const uint64_t* h
     return MVS_OK;
 }
 
-int mvs_project_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offsets, int64_t n_samples, int d,
-                      uint64_t seed, int32_t* out)
+int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offsets, int64_t n_samples, int d,
+                     uint64_t seed, int32_t* out, int16_t* out16, uint64_t* sumsq)
 {
-    if (!ctx || !offsets || n_samples < 0 || d <= 0 || (!out && n_samples > 0)) return MVS_ERR_INVALID_ARG;
+    if (!ctx || !offsets || n_samples < 0 || d <= 0 || (!out && !out16 && !sumsq && n_samples > 0))
+        return MVS_ERR_INVALID_ARG;
     if (n_samples == 0) return MVS_OK;
     if (n_samples >= 0xFFFFFFF0ll) return MVS_ERR_TOO_LARGE;
     if (!hashes && offsets[n_samples] > offsets[0]) return MVS_ERR_INVALID_ARG;
@@ -447,6 +448,8 @@ int mvs_project_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offs
         if ((rc = wait_slot(ctx, sl)) != MVS_OK) break;
         if ((rc = ensure_dev(ctx, sl.hashes, (nh + 2) * sizeof(uint64_t))) != MVS_OK) break;
         if ((rc = ensure_dev(ctx, sl.out, static_cast<size_t>(rows) * row_bytes)) != MVS_OK) break;
+        if (sumsq && (rc = ensure_dev(ctx, sl.sumsq, static_cast<size_t>(rows) * sizeof(uint64_t))) != MVS_OK) break;
+        if (out16 && (rc = ensure_dev(ctx, sl.out16, static_cast<size_t>(rows) * row_bytes / 2)) != MVS_OK) break;
         if (nh) {
             cudaError_t e = cudaMemcpyAsync(sl.hashes.p, hashes + h0, nh * sizeof(uint64_t), cudaMemcpyHostToDevice,
                                             sl.stream);
@@ -457,11 +460,30 @@ int mvs_project_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offs
                        static_cast<int32_t*>(sl.out.p), sl.stream, false);
         if (rc != MVS_OK) break;
         ctx->timing.h2d_bytes += ctx->timing.warp_tasks * sizeof(WarpTask);
-        cudaError_t e = cudaMemcpyAsync(out + static_cast<size_t>(s0) * static_cast<size_t>(d), sl.out.p,
-                                        static_cast<size_t>(rows) * row_bytes, cudaMemcpyDeviceToHost, sl.stream);
+        cudaError_t e = cudaSuccess;
+        if (out16 || sumsq) {                    // fused epilogue of sketch(): sum of squares + int16 saturation
+            rc = mvs_finalize_device(ctx, static_cast<const int32_t*>(sl.out.p), rows, d,
+                                     sumsq ? static_cast<uint64_t*>(sl.sumsq.p) : nullptr,
+                                     out16 ? static_cast<int16_t*>(sl.out16.p) : nullptr, sl.stream);
+            if (rc != MVS_OK) break;
+        }
+        if (out) {
+            e = cudaMemcpyAsync(out + static_cast<size_t>(s0) * static_cast<size_t>(d), sl.out.p,
+                                static_cast<size_t>(rows) * row_bytes, cudaMemcpyDeviceToHost, sl.stream);
+            ctx->timing.d2h_bytes += static_cast<uint64_t>(rows) * row_bytes;
+        }
+        if (out16 && e == cudaSuccess) {
+            e = cudaMemcpyAsync(out16 + static_cast<size_t>(s0) * static_cast<size_t>(d), sl.out16.p,
+                                static_cast<size_t>(rows) * row_bytes / 2, cudaMemcpyDeviceToHost, sl.stream);
+            ctx->timing.d2h_bytes += static_cast<uint64_t>(rows) * row_bytes / 2;
+        }
+        if (sumsq && e == cudaSuccess) {
+            e = cudaMemcpyAsync(sumsq + s0, sl.sumsq.p, static_cast<size_t>(rows) * sizeof(uint64_t),
+                                cudaMemcpyDeviceToHost, sl.stream);
+            ctx->timing.d2h_bytes += static_cast<uint64_t>(rows) * sizeof(uint64_t);
+        }
         if (e == cudaSuccess) e = cudaEventRecord(sl.done, sl.stream);
         if (e != cudaSuccess) { ctx->last_cuda = e; cudaGetLastError(); rc = MVS_ERR_CUDA; break; }
-        ctx->timing.d2h_bytes += static_cast<uint64_t>(rows) * row_bytes;
         sl.busy = true;
         s0 = s1;
     }
@@ -470,6 +492,13 @@ int mvs_project_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offs
         if (rc == MVS_OK) rc = r2;
     }
     return rc;
+}
+
+int mvs_project_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offsets, int64_t n_samples, int d,
+                      uint64_t seed, int32_t* out)
+{
+    if (!out && n_samples > 0) return MVS_ERR_INVALID_ARG;
+    return mvs_sketch_batch(ctx, hashes, offsets, n_samples, d, seed, out, nullptr, nullptr);
 }
 
 int mvs_transform_set(mvs_ctx* ctx, const uint64_t* hashes, int64_t n_hashes, int d, uint64_t seed, int32_t* out)

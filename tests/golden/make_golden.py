@@ -152,7 +152,9 @@ def main():
     # parser edge cases of sketch() (project_everything.cpp:264-282)
     text = ("a: 1 2 3\n" "no colon line 5 6\n" "c: 5 x 6\n" "neg: -1\n"
             "big: 7 99999999999999999999999 8\n" "empty:\n" "sp ace: 10 10 11\n"
-            "two:colons: 4\n" "tab:\t12\t13  14 \n" "plus: +15 016\n")
+            "two:colons: 4\n" "tab:\t12\t13  14 \n" "plus: +15 016\n"
+            "glued: 5-3 7+8\n" "hex: 0x10 3\n" "exp: 1e5 2\n" "cr: 21 22\r\n" "max: 18446744073709551615 18446744073709551616 9\n"
+            "negbig: -18446744073709551615 -18446744073709551616 4\n" "last: 31 32")
     with tempfile.TemporaryDirectory() as td:
         hf = os.path.join(td, "edge.txt")
         open(hf, "w").write(text)

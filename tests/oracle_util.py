@@ -103,29 +103,31 @@ def load_kat():
 
 
 def parse_line_like_reference(text):
-    """istringstream >> unsigned long semantics of the reference parsers
-    (project_everything.cpp:275-279, standalone_projection.cpp:30-34): whitespace-separated
-    tokens; optional sign; a token that is not a number, or overflows 2^64-1, ends the line
-    (nothing inserted for it); '-N' wraps modulo 2^64.  Small-case oracle for the parser tests."""
+    """`while (iss >> hash)` for unsigned long (project_everything.cpp:275-279,
+    standalone_projection.cpp:30-34), character by character: skip whitespace, optional sign, at
+    least one digit (else the loop ends), magnitude > 2^64-1 ends the loop without inserting,
+    '-N' wraps modulo 2^64; the next extraction starts right after the last digit, so "5x" gives
+    [5] and "5-3" gives [5, 2^64-3].  Small-case oracle for the parser tests, pinned by kat.json."""
     out = []
-    for tok in text.split():
-        t = tok
-        neg = False
-        if t[:1] in "+-":
-            neg = t[0] == "-"
-            t = t[1:]
-        digits = ""
-        for ch in t:
-            if ch.isdigit() and ch.isascii():
-                digits += ch
-            else:
-                break
-        if not digits:
+    i, n = 0, len(text)
+    ws = " \t\n\v\f\r"
+    while True:
+        while i < n and text[i] in ws:
+            i += 1
+        if i >= n:
             break
-        v = int(digits)
+        neg = False
+        if text[i] in "+-":
+            neg = text[i] == "-"
+            i += 1
+        j = i
+        while j < n and text[j] in "0123456789":
+            j += 1
+        if j == i:
+            break
+        v = int(text[i:j])
+        i = j
         if v > 0xFFFFFFFFFFFFFFFF:
             break
         out.append((-v) & 0xFFFFFFFFFFFFFFFF if neg else v)
-        if len(digits) != len(t):          # trailing garbage: number is consumed, next >> fails
-            break
     return out
