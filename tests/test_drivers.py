@@ -1,0 +1,158 @@
+"""CPU tests of the host-side drivers (parser, db writer, convert, partition, CLI grammar).
+None of these needs a GPU: they exercise the C++ code above the projection call."""
+import ctypes as C
+import hashlib
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import metagenome_vector_sketches_b200 as mvs
+from metagenome_vector_sketches_b200 import _lib
+from oracle_util import load_kat, load_toy, load_toy_ref, parse_line_like_reference, oracle_set
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "metagenome_vector_sketches_b200", "bin")
+
+
+def parse_file(path, named):
+    lib = mvs.load_library()
+    hb = C.POINTER(_lib.HashBatch)()
+    rc = lib.mvs_parse_hash_file(path.encode(), int(named), C.byref(hb))
+    if rc != 0:
+        return rc, None, None
+    b = hb.contents
+    n = b.n_samples
+    off = np.ctypeslib.as_array(b.offsets, shape=(n + 1,)).copy()
+    hashes = np.ctypeslib.as_array(b.hashes, shape=(max(1, int(b.n_hashes)),))[: int(b.n_hashes)].copy()
+    names = [b.names[i].decode() for i in range(n)] if named else None
+    lib.mvs_free_hash_batch(hb)
+    return 0, names, [hashes[int(off[i]):int(off[i + 1])] for i in range(n)]
+
+
+def test_parser_matches_reference_edge_cases(tmp_path):
+    kat = load_kat()["sketch_parser"]
+    p = tmp_path / "edge.txt"
+    p.write_bytes(kat["text"].encode())
+    rc, names, sets = parse_file(str(p), True)
+    assert rc == 0
+    want_names, want_sets = [], []
+    for line in kat["text"].split("\n"):
+        if ":" not in line:
+            continue
+        want_names.append(line[: line.index(":")])
+        want_sets.append(sorted(set(parse_line_like_reference(line[line.index(":") + 1:]))))
+    assert names == want_names
+    assert [s.tolist() for s in sets] == want_sets
+    # ... and the sets reproduce the reference's vectors.bin for that file (golden, d=8)
+    got = np.concatenate([oracle_set(s, kat["d"]) for s in sets])
+    assert np.array_equal(got, np.array(kat["vectors"], dtype=np.int32))
+    # norms file of the reference lists the same names in the same order
+    assert [l.rsplit(" ", 1)[0] for l in kat["norms_txt"].split("\n")[:-1]] == want_names
+
+
+def test_parser_standalone_mode_lines(tmp_path):
+    p = tmp_path / "q.hashes"
+    p.write_text("1 2 3\n\n5 5 5\nx 9\n7")
+    rc, names, sets = parse_file(str(p), False)
+    assert rc == 0 and names is None
+    assert [s.tolist() for s in sets] == [[1, 2, 3], [], [5], [], [7]]
+    p.write_text("")
+    assert parse_file(str(p), False)[2] == []
+    assert parse_file(str(tmp_path / "missing"), True)[0] == -6      # MVS_ERR_IO
+
+
+def test_parser_toy_roundtrip(tmp_path):
+    names, offsets, hashes = load_toy()
+    p = tmp_path / "toy.txt"
+    with open(p, "w") as f:
+        for i, nme in enumerate(names):
+            f.write(nme + ":" + "".join(" %d" % int(h) for h in hashes[int(offsets[i]):int(offsets[i + 1])]) + "\n")
+    rc, got_names, sets = parse_file(str(p), True)
+    assert rc == 0 and got_names == names
+    for i, s in enumerate(sets):
+        assert np.array_equal(s, np.unique(hashes[int(offsets[i]):int(offsets[i + 1])]))
+
+
+@pytest.mark.parametrize("tag,i16", [("d2048", False), ("d2048_i16", True), ("d100", False)])
+def test_write_db_matches_reference_files(tmp_path, tag, i16):
+    lib = mvs.load_library()
+    names, _, _ = load_toy()
+    ref = load_toy_ref(tag)
+    vec = ref["vectors"]
+    n, d = vec.shape
+    v32 = vec.astype(np.int32)
+    sumsq = (v32.astype(np.int64) ** 2).sum(axis=1).astype(np.uint64)
+    arr = (C.c_char_p * n)(*[s.encode() for s in names])
+    v16 = np.ascontiguousarray(vec.astype(np.int16)) if i16 else None
+    out = tmp_path / "db"
+    out.mkdir()
+    rc = lib.mvs_write_db(str(out).encode(), n, d, arr, sumsq.ctypes.data,
+                          None if i16 else v32.ctypes.data, v16.ctypes.data if i16 else None)
+    assert rc == 0
+    raw = (out / "vectors.bin").read_bytes()
+    assert hashlib.sha256(raw).hexdigest() == ref["vectors_sha256"]          # byte-identical vectors.bin
+    assert (out / "dimension.txt").read_text() == ref["dimension_txt"]
+    assert (out / "dtype.txt").read_text() == ref["dtype_txt"]
+    mine = (out / "vector_norms.txt").read_text().split("\n")[:-1]
+    theirs = ref["norms_txt"].split("\n")[:-1]
+    assert len(mine) == len(theirs) == n
+    same = 0
+    for a, b in zip(mine, theirs):
+        na, va = a.rsplit(" ", 1)
+        nb, vb = b.rsplit(" ", 1)
+        assert na == nb
+        exact = float(va)
+        ulp6 = 10.0 ** (np.floor(np.log10(exact)) - 5) if exact > 0 else 0.0
+        assert abs(float(vb) - exact) <= 1.0 * ulp6 + 2e-6 * exact             # stated tolerance
+        same += a == b
+    assert same >= 0.8 * n                                                       # most lines are textually identical
+
+
+def test_convert_reads_toy_signatures(tmp_path):
+    toy = "/root/reference/test/toy"
+    if not os.path.isdir(toy):
+        pytest.skip("reference toy signatures not present on this host")
+    lib = mvs.load_library()
+    hf = tmp_path / "toy_hashes.txt"
+    assert lib.mvs_convert_signatures(toy.encode(), str(hf).encode(), 4, 0) == 0
+    rc, got_names, sets = parse_file(str(hf), True)
+    names, offsets, hashes = load_toy()
+    assert rc == 0 and got_names == names
+    for i, s in enumerate(sets):
+        assert np.array_equal(s, np.unique(hashes[int(offsets[i]):int(offsets[i + 1])]))
+
+
+def test_partition_is_contiguous_balanced_cover():
+    lib = mvs.load_library()
+    sizes = mvs.synthetic.lognormal_sizes(5000, seed=3)
+    off = np.zeros(len(sizes) + 1, dtype=np.uint64)
+    off[1:] = np.cumsum(sizes)
+    for parts in (1, 2, 4, 8):
+        b = np.zeros(parts + 1, dtype=np.int64)
+        lib.mvs_partition_samples(off.ctypes.data, len(sizes), parts, b.ctypes.data)
+        assert b[0] == 0 and b[-1] == len(sizes) and np.all(np.diff(b) >= 0)
+        loads = [int(off[b[k + 1]] - off[b[k]]) for k in range(parts)]
+        assert sum(loads) == int(off[-1])
+        assert max(loads) <= int(off[-1]) / parts + int(sizes.max()) + len(sizes)   # balanced within one sample
+    # empty samples only: still a cover
+    off0 = np.zeros(11, dtype=np.uint64)
+    b = np.zeros(5, dtype=np.int64)
+    lib.mvs_partition_samples(off0.ctypes.data, 10, 4, b.ctypes.data)
+    assert b[0] == 0 and b[-1] == 10 and np.all(np.diff(b) >= 0)
+
+
+def test_cli_grammar_and_exit_codes(tmp_path):
+    pe = os.path.join(BIN, "project_everything")
+    sp = os.path.join(BIN, "standalone_projection")
+    if not (os.path.exists(pe) and os.path.exists(sp)):
+        pytest.skip("CLI drivers not built")
+    for argv in ([pe], [pe, "sketch"], [pe, "sketch", "a"], [pe, "sketch", "a", "b", "--nope"],
+                 [pe, "sketch", "a", "b", "-d"], [pe, "bogus"], [pe, "convert", "a"]):
+        r = subprocess.run(argv, capture_output=True, text=True)
+        assert r.returncode == 1 and "Usage:" in r.stderr             # reference: usage + exit 1
+    r = subprocess.run([sp], capture_output=True, text=True)
+    assert r.returncode == 1 and "Usage:" in r.stderr and "<hashes_file> <dimension>" in r.stderr
+    r = subprocess.run([sp, "only_one"], capture_output=True, text=True)
+    assert r.returncode == 1
