@@ -113,3 +113,17 @@ def test_config5_topk_identical_through_reference_consumers(tmp_path, toy_hash_f
         assert r.returncode == 0
         assert (theirs / "vectors.bin").read_bytes() == (ours / "vectors.bin").read_bytes()
         assert pipeline(str(ours) + "/", "oursall", names) == pipeline(str(theirs) + "/", "refall", names)
+
+
+def test_reference_driver_linked_against_our_shim(tmp_path, toy_hash_file):
+    """INTEGRATION.md option 2: the reference's unmodified project_everything.cpp + our
+    transform_set_into_vector shim (prebuilt by oracle/Makefile) writes the reference's vectors.bin."""
+    exe = os.path.join(REFV3, "project_everything_b200shim")
+    if not os.path.exists(exe):
+        pytest.skip("shim-linked reference driver not prebuilt")
+    db = tmp_path / "db_shim"
+    r = run([exe, "sketch", toy_hash_file, str(db), "-d", "2048"], env=dict(os.environ, OMP_NUM_THREADS="4"))
+    assert r.returncode == 0, r.stderr
+    ref = load_toy_ref("d2048")
+    assert hashlib.sha256((db / "vectors.bin").read_bytes()).hexdigest() == ref["vectors_sha256"]
+    assert (db / "vector_norms.txt").read_text() == ref["norms_txt"] or ref_dir() != REFV3
