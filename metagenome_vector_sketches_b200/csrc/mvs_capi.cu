@@ -241,9 +241,20 @@ cudaError_t launch_project(const Geometry& g, cudaStream_t st, uint32_t ntasks, 
 // d_hashes holds the hashes from index `hash_base` on; d_out row 0 = sample `s0`
 // when rows_local, else sample 0.
 int run_range(mvs_ctx* ctx, Slot& sl, const uint64_t* d_hashes, const uint64_t* offsets, int64_t s0, int64_t s1,
-              uint64_t hash_base, int64_t row_base, const Geometry& g, uint64_t seed, int32_t* d_out,
+              uint64_t hash_base, int64_t row_base, const Geometry& g_in, uint64_t seed, int32_t* d_out,
               cudaStream_t st, bool record_timing)
 {
+    // Small batches: shrink the per-task hash cap so that the grid still fills the GPU for several
+    // waves (a warp task is the unit of parallelism); large batches keep the full 4080-round cap.
+    Geometry g = g_in;
+    {
+        const uint64_t total = offsets[s1] - offsets[s0];
+        const uint64_t target_tasks = static_cast<uint64_t>(ctx->sm_count) * 24ull * 4ull;    // ~4 waves of resident warps
+        const uint64_t min_cap = 2048ull * static_cast<uint64_t>(g.S);                         // keeps the flush under ~5 %
+        uint64_t want = (total * static_cast<uint64_t>(g.passes) + target_tasks - 1) / target_tasks;
+        want = (want + g.quantum - 1) / g.quantum * g.quantum;
+        g.cap = std::min<uint64_t>(g.cap, std::max<uint64_t>(min_cap, want));
+    }
     PlanCounts pc;
     int rc = count_plan(offsets, s0, s1, g, pc);
     if (rc != MVS_OK) return rc;

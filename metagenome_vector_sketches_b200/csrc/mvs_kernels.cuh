@@ -20,6 +20,13 @@
 // LDS.  Padding zeros are processed like real hashes and their known contribution
 // (splitmix64(0 + c) per lane) is subtracted at the flush, so the inner loop has no
 // masking at all.
+//
+// The 64-bit add `hash + c_lane` is hoisted out of the (hash, lane) loop: once a tile has
+// landed, the warp adds the task constant  base = golden + seed + 2048*pass  to every
+// staged hash in place (one add per HASH, not per hash and lane), so a lane only adds its
+// own  64*block < 2048  to the low word.  That add can carry into the high word only if
+// low32(hash + base) >= 2^32 - 2048, about one hash in two million; the tile pass votes on
+// it and a flagged tile (2.4e-4 of them) runs the same loop with the exact 64-bit add.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -33,6 +40,7 @@ constexpr int kPlanes = 12;                      // bit planes: counts up to 409
 constexpr uint32_t kMaxRounds = 4080;            // hashes per lane per task (255 groups of 16)
 constexpr uint32_t kDirect = 0xFFFFFFFFu;
 constexpr uint64_t kGolden = 0x9e3779b97f4a7c15ULL;
+constexpr uint32_t kCarryRisk = 0xFFFFF800u;     // low words >= 2^32 - 2048 may carry when 64*block is added
 
 struct __align__(16) WarpTask {                  // 32 bytes
     uint64_t begin;                              // first hash (index into the batch array)
@@ -58,6 +66,19 @@ __device__ __forceinline__ void mix64(uint64_t x, uint32_t& lo, uint32_t& hi)
     x = x ^ (x >> 31);
     lo = static_cast<uint32_t>(x);
     hi = static_cast<uint32_t>(x >> 32);
+}
+
+// hb = hash + base (already added in shared memory), off = 64*block of this lane (< 2048).
+// EXACT = false: the tile pass has proved that low32(hb) + off cannot carry.
+template <bool EXACT>
+__device__ __forceinline__ void mix_staged(uint64_t hb, uint32_t off, uint32_t& lo, uint32_t& hi)
+{
+    if constexpr (EXACT) {
+        mix64(hb + off, lo, hi);
+    } else {
+        const uint32_t xlo = static_cast<uint32_t>(hb) + off;
+        mix64((hb & 0xFFFFFFFF00000000ULL) | xlo, lo, hi);
+    }
 }
 
 // carry-save adder on 32 bit columns at once: s = a^b^c, c = maj(a,b,c)
@@ -93,10 +114,10 @@ __device__ __forceinline__ uint32_t hs4(uint32_t (&P)[kPlanes], uint32_t a, uint
 }
 
 // One Harley-Seal group: 16 hashes of this lane's stream -> planes 0..3 + a weight-16
-// carry per word.  sp points at the lane's first hash of the group in shared memory;
-// consecutive hashes of the lane are S entries apart.
-template <int S>
-__device__ __forceinline__ void group16(const uint64_t* __restrict__ sp, uint64_t cval,
+// carry per word.  sp points at the lane's first (pre-added) hash of the group in shared
+// memory; consecutive hashes of the lane are S entries apart.
+template <int S, bool EXACT>
+__device__ __forceinline__ void group16(const uint64_t* __restrict__ sp, uint32_t off,
                                         uint32_t (&Plo)[kPlanes], uint32_t (&Phi)[kPlanes],
                                         uint32_t& c16lo, uint32_t& c16hi)
 {
@@ -105,12 +126,12 @@ __device__ __forceinline__ void group16(const uint64_t* __restrict__ sp, uint64_
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const ulonglong2 h2 = *reinterpret_cast<const ulonglong2*>(sp + 2 * i);   // LDS.128 broadcast
-            mix64(h2.x + cval, lo[2 * i], hi[2 * i]);
-            mix64(h2.y + cval, lo[2 * i + 1], hi[2 * i + 1]);
+            mix_staged<EXACT>(h2.x, off, lo[2 * i], hi[2 * i]);
+            mix_staged<EXACT>(h2.y, off, lo[2 * i + 1], hi[2 * i + 1]);
         }
     } else {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) mix64(sp[i * S] + cval, lo[i], hi[i]);
+        for (int i = 0; i < 16; ++i) mix_staged<EXACT>(sp[i * S], off, lo[i], hi[i]);
     }
     uint32_t fl[4], fh[4];
 #pragma unroll
@@ -162,7 +183,9 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
 
     const int slot = lane >> LPH_LOG2;
     const int blk = static_cast<int>(task.pass) * 32 + (lane & (LPH - 1));
-    const uint64_t cval = seed_golden + (static_cast<uint64_t>(static_cast<uint32_t>(blk)) << 6);
+    const uint64_t base = seed_golden + (static_cast<uint64_t>(task.pass) << 11);   // added per hash in the tile pass
+    const uint32_t off = static_cast<uint32_t>(lane & (LPH - 1)) << 6;              // added per lane, < 2048
+    const uint64_t cval = base + off;                                               // == seed_golden + 64*blk
 
     uint32_t Plo[kPlanes], Phi[kPlanes];
 #pragma unroll
@@ -190,13 +213,24 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
         cp_async_commit();
         cp_async_wait<1>();
         __syncwarp();
-        const uint64_t* st = ring + (t & (kStages - 1)) * kTileHashes;
+        uint64_t* st = ring + (t & (kStages - 1)) * kTileHashes;
+        // tile pass: hash += base in place; vote whether any low word could carry under + off
+        bool risky = false;
+#pragma unroll
+        for (int i = 0; i < kTileHashes / 32; ++i) {
+            const uint64_t v = st[i * 32 + lane] + base;
+            risky |= static_cast<uint32_t>(v) >= kCarryRisk;
+            st[i * 32 + lane] = v;
+        }
+        const bool exact = __any_sync(0xffffffffu, risky);
+        __syncwarp();
         const uint32_t valid = min(count - t * kTileHashes, static_cast<uint32_t>(kTileHashes));
         const uint32_t rounds = (valid + S - 1) / S;
         const uint32_t ngroups = (rounds + 15) >> 4;           // <= kGroupsPerTile
         for (uint32_t gi = 0; gi < ngroups; ++gi, ++g) {
             uint32_t c16lo, c16hi;
-            group16<S>(st + gi * (16 * S) + slot, cval, Plo, Phi, c16lo, c16hi);
+            if (exact) group16<S, true>(st + gi * (16 * S) + slot, off, Plo, Phi, c16lo, c16hi);
+            else group16<S, false>(st + gi * (16 * S) + slot, off, Plo, Phi, c16lo, c16hi);
             if ((g & 1u) == 0u) {
                 pend16lo = c16lo; pend16hi = c16hi;
             } else {

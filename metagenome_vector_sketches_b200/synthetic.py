@@ -101,3 +101,41 @@ def uniform_batch_torch(n_samples, hashes_per_sample, device, seed=0, first_samp
         out[s0 * hashes_per_sample:s1 * hashes_per_sample] = x
     offsets = np.arange(n_samples + 1, dtype=np.uint64) * np.uint64(hashes_per_sample)
     return out, offsets
+
+
+def ragged_batch_torch(sizes, device, seed=0, first_sample=0, chunk_hashes=1 << 27):
+    """Same batch as ragged_batch(), generated on `device` in chunks of whole samples (a sample
+    larger than chunk_hashes forms its own chunk).  Returns (int64 tensor, numpy uint64 offsets)."""
+    import torch
+    sizes = np.asarray(sizes, dtype=np.int64)
+    offsets = np.zeros(len(sizes) + 1, dtype=np.uint64)
+    offsets[1:] = np.cumsum(sizes).astype(np.uint64)
+    total = int(offsets[-1])
+    out = torch.empty(total, dtype=torch.int64, device=device)
+    sx = (seed * _M1) & MASK54
+    s0 = 0
+    n = len(sizes)
+    while s0 < n:
+        s1 = s0 + 1
+        while s1 < n and int(offsets[s1 + 1] - offsets[s0]) <= chunk_hashes:
+            s1 += 1
+        h0, h1 = int(offsets[s0]), int(offsets[s1])
+        if h1 > h0:
+            cnt = torch.from_numpy(sizes[s0:s1]).to(device)
+            sid = torch.arange(first_sample + s0, first_sample + s1, dtype=torch.int64, device=device)
+            start = torch.from_numpy(offsets[s0:s1].astype(np.int64) - h0).to(device)
+            s = torch.repeat_interleave(sid, cnt)
+            k = torch.arange(h1 - h0, dtype=torch.int64, device=device) - torch.repeat_interleave(start, cnt)
+            x = (s << 24) | k
+            del s, k
+            x = x ^ sx
+            x = (x * _s64(_M1)) & MASK54
+            x = x ^ (x >> 29)
+            x = (x * _s64(_M2)) & MASK54
+            x = x ^ (x >> 27)
+            x = (x * _s64(_M3)) & MASK54
+            x = x ^ (x >> 31)
+            out[h0:h1] = x
+            del x
+        s0 = s1
+    return out, offsets

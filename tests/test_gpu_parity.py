@@ -84,6 +84,43 @@ def test_seed_is_additive_and_zero_is_reference(sk):
         assert np.array_equal(sk.transform_set(h, 512, seed=77), sk.transform_set(h + np.uint64(77), 512))
 
 
+def test_carry_window_of_the_hoisted_add(sk):
+    """The kernel adds base = golden + seed + 2048*pass once per hash and 64*block per lane on the
+    low word only; hashes whose low word lands in [2^32 - 2048, 2^32) after the base add must take
+    the exact path.  Build samples that sit in and around that window for every pass / seed."""
+    golden = 0x9E3779B97F4A7C15
+    rng = np.random.default_rng(77)
+    for d, seed in ((2048, 0), (2048, 12345), (4096, 0), (256, 0), (100, 2 ** 64 - 5), (5000, 7)):
+        passes = (((d + 63) // 64) + 31) // 32
+        sets = []
+        for p in range(passes):
+            base = (golden + seed + 2048 * p) % 2 ** 64
+            # low words of hash + base: the whole window, its two edges, and plain wrap-around values
+            lows = np.concatenate([np.arange(2 ** 32 - 2112, 2 ** 32, dtype=np.uint64),
+                                   np.arange(0, 64, dtype=np.uint64)])
+            highs = rng.integers(0, 2 ** 32, len(lows), dtype=np.uint64)
+            target = (highs << np.uint64(32)) | lows
+            with np.errstate(over="ignore"):
+                sets.append(np.unique(target - np.uint64(base)))
+            # a sparse mix: one risky hash hidden among ordinary ones (exercises exact and fast tiles)
+            plain = rng.integers(0, 2 ** 63, 6000, dtype=np.uint64)
+            plain[3333] = sets[-1][-7]
+            sets.append(np.unique(plain))
+        offsets = np.zeros(len(sets) + 1, dtype=np.uint64)
+        offsets[1:] = np.cumsum([len(x) for x in sets])
+        hashes = np.concatenate(sets)
+        got = sk.project_csr(hashes, offsets, d, seed=seed)
+        assert np.array_equal(got, oracle_csr(hashes, offsets, d, seed=seed)), (d, seed)
+
+
+def test_small_batches_are_split_finer_and_stay_exact(sk):
+    # few samples: the planner shrinks the task cap to fill the GPU; the result must not change
+    h, off = mvs.synthetic.uniform_batch(3, 40000, seed=11)
+    for d in (256, 2048):
+        assert np.array_equal(sk.project_csr(h, off, d), oracle_csr(h, off, d))
+    assert sk.timing()["warp_tasks"] >= 3 * (40000 // 2048)
+
+
 def test_large_sample_split_across_warp_tasks(sk):
     # one sample >> task capacity: partial rows + fixed-order reduce
     h, off = mvs.synthetic.uniform_batch(1, 300000, seed=3)
