@@ -218,7 +218,8 @@ cudaError_t launch_project_t(cudaStream_t st, uint32_t ntasks, const uint64_t* d
     const uint32_t grid = (ntasks + mvs::kWarpsPerCta - 1) / mvs::kWarpsPerCta;
     const size_t smem = static_cast<size_t>(mvs::kWarpsPerCta) * mvs::kStages * mvs::kTileHashes * sizeof(uint64_t);
     mvs::project_kernel<L><<<grid, mvs::kWarpsPerCta * 32, smem, st>>>(d_hashes, d_tasks, ntasks, d,
-                                                                     seed + mvs::kGolden, d_out, d_partials, vec4);
+                                                                     seed + mvs::kGolden, d_out, d_partials, vec4,
+                                                                     mvs::kFold);
     return cudaGetLastError();
 }
 

@@ -27,6 +27,17 @@
 // own  64*block < 2048  to the low word.  That add can carry into the high word only if
 // low32(hash + base) >= 2^32 - 2048, about one hash in two million; the tile pass votes on
 // it and a flagged tile (2.4e-4 of them) runs the same loop with the exact 64-bit add.
+//
+// The last mixer step  x ^= x >> 31  changes only bit 0 of the high word (bit0 ^= bit31), i.e.
+// one column (32) of the 64-column block, for two ALU-pipe instructions per (hash, lane).
+// The loop therefore feeds the carry-save tree with the high word BEFORE that step (all its
+// other 31 columns are already final) and counts column 32 on the side without the ALU pipe:
+// t = hi * 0x80000001 (IMAD) carries bit0 ^ bit31 in bit 31 above hi's bits 0..30, so
+// popc(t) = popc(hi & 0x7fffffff) + (bit0 ^ bit31)  (POPC runs on the XU pipe, the running sum
+// on the FMA pipe), and the first term summed over the hashes equals the sum of the plane
+// counts of slots 0..30, known exactly at the flush.  Measured on B200 (tools/kexp): the ALU
+// pipe is the binding unit (IMAD.WIDE / IMAD.HI also take an ALU issue slot), 42.7 -> 38.6
+// clocks per (hash, warp) with both hoists.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -40,6 +51,7 @@ constexpr int kPlanes = 12;                      // bit planes: counts up to 409
 constexpr uint32_t kMaxRounds = 4080;            // hashes per lane per task (255 groups of 16)
 constexpr uint32_t kDirect = 0xFFFFFFFFu;
 constexpr uint64_t kGolden = 0x9e3779b97f4a7c15ULL;
+constexpr uint32_t kFold = 0x80000001u;          // passed as a kernel argument so that the multiply stays an IMAD
 constexpr uint32_t kCarryRisk = 0xFFFFF800u;     // low words >= 2^32 - 2048 may carry when 64*block is added
 
 struct __align__(16) WarpTask {                  // 32 bytes
@@ -70,15 +82,28 @@ __device__ __forceinline__ void mix64(uint64_t x, uint32_t& lo, uint32_t& hi)
 
 // hb = hash + base (already added in shared memory), off = 64*block of this lane (< 2048).
 // EXACT = false: the tile pass has proved that low32(hb) + off cannot carry.
+// Outputs: lo = final low word; hi = high word BEFORE the last xor-shift (columns 33..63 are
+// final, slot 0 holds the raw bit 0); eacc += popc(hi * fold), fold = 0x80000001 (see header).
 template <bool EXACT>
-__device__ __forceinline__ void mix_staged(uint64_t hb, uint32_t off, uint32_t& lo, uint32_t& hi)
+__device__ __forceinline__ void mix_staged(uint64_t hb, uint32_t off, uint32_t fold, uint32_t& lo, uint32_t& hi,
+                                           uint32_t& eacc)
 {
+    uint64_t x;
     if constexpr (EXACT) {
-        mix64(hb + off, lo, hi);
+        x = hb + off;
     } else {
         const uint32_t xlo = static_cast<uint32_t>(hb) + off;
-        mix64((hb & 0xFFFFFFFF00000000ULL) | xlo, lo, hi);
+        x = (hb & 0xFFFFFFFF00000000ULL) | xlo;
     }
+    x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ULL;
+    x = (x ^ (x >> 27)) * 0x94d049bb133111ebULL;
+    const uint32_t xl = static_cast<uint32_t>(x);
+    const uint32_t xh = static_cast<uint32_t>(x >> 32);
+    lo = xl ^ __funnelshift_r(xl, xh, 31);
+    hi = xh;
+    uint32_t t;
+    asm("mul.lo.u32 %0, %1, %2;" : "=r"(t) : "r"(xh), "r"(fold));
+    eacc += static_cast<uint32_t>(__popc(t));
 }
 
 // carry-save adder on 32 bit columns at once: s = a^b^c, c = maj(a,b,c)
@@ -117,21 +142,21 @@ __device__ __forceinline__ uint32_t hs4(uint32_t (&P)[kPlanes], uint32_t a, uint
 // carry per word.  sp points at the lane's first (pre-added) hash of the group in shared
 // memory; consecutive hashes of the lane are S entries apart.
 template <int S, bool EXACT>
-__device__ __forceinline__ void group16(const uint64_t* __restrict__ sp, uint32_t off,
+__device__ __forceinline__ void group16(const uint64_t* __restrict__ sp, uint32_t off, uint32_t fold,
                                         uint32_t (&Plo)[kPlanes], uint32_t (&Phi)[kPlanes],
-                                        uint32_t& c16lo, uint32_t& c16hi)
+                                        uint32_t& c16lo, uint32_t& c16hi, uint32_t& eacc)
 {
     uint32_t lo[16], hi[16];
     if constexpr (S == 1) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const ulonglong2 h2 = *reinterpret_cast<const ulonglong2*>(sp + 2 * i);   // LDS.128 broadcast
-            mix_staged<EXACT>(h2.x, off, lo[2 * i], hi[2 * i]);
-            mix_staged<EXACT>(h2.y, off, lo[2 * i + 1], hi[2 * i + 1]);
+            mix_staged<EXACT>(h2.x, off, fold, lo[2 * i], hi[2 * i], eacc);
+            mix_staged<EXACT>(h2.y, off, fold, lo[2 * i + 1], hi[2 * i + 1], eacc);
         }
     } else {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) mix_staged<EXACT>(sp[i * S], off, lo[i], hi[i]);
+        for (int i = 0; i < 16; ++i) mix_staged<EXACT>(sp[i * S], off, fold, lo[i], hi[i], eacc);
     }
     uint32_t fl[4], fh[4];
 #pragma unroll
@@ -164,7 +189,7 @@ template <int LPH_LOG2>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__ tasks, uint32_t ntasks,
                int d, uint64_t seed_golden, int32_t* __restrict__ out, int32_t* __restrict__ partials,
-               int vec4_ok)
+               int vec4_ok, uint32_t fold)
 {
     constexpr int LPH = 1 << LPH_LOG2;
     constexpr int S = 32 >> LPH_LOG2;
@@ -192,6 +217,7 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
     for (int p = 0; p < kPlanes; ++p) { Plo[p] = 0u; Phi[p] = 0u; }
     uint32_t pend16lo = 0, pend16hi = 0, pend32lo = 0, pend32hi = 0;
     uint32_t g = 0;                              // groups done (warp-uniform)
+    uint32_t eacc = 0;                           // sum of popc(hi * fold) over this lane's hashes
 
     const uint32_t ntiles = (count + kTileHashes - 1) / kTileHashes;
 
@@ -229,8 +255,8 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
         const uint32_t ngroups = (rounds + 15) >> 4;           // <= kGroupsPerTile
         for (uint32_t gi = 0; gi < ngroups; ++gi, ++g) {
             uint32_t c16lo, c16hi;
-            if (exact) group16<S, true>(st + gi * (16 * S) + slot, off, Plo, Phi, c16lo, c16hi);
-            else group16<S, false>(st + gi * (16 * S) + slot, off, Plo, Phi, c16lo, c16hi);
+            if (exact) group16<S, true>(st + gi * (16 * S) + slot, off, fold, Plo, Phi, c16lo, c16hi, eacc);
+            else group16<S, false>(st + gi * (16 * S) + slot, off, fold, Plo, Phi, c16lo, c16hi, eacc);
             if ((g & 1u) == 0u) {
                 pend16lo = c16lo; pend16hi = c16hi;
             } else {
@@ -271,6 +297,13 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
     const int32_t n_total = static_cast<int32_t>(count);
     const bool vec4 = vec4_ok != 0;             // d % 4 == 0 and 16-byte aligned rows (host-checked)
 
+    // column 32 (bit0 ^ bit31 of the high word): eacc minus the hashes' popc(hi & 0x7fffffff),
+    // which is sum_p 2^p * popc(plane_p & 0x7fffffff).  Padding zeros are included on both sides
+    // and removed below like in every other column (zhi is the true final word of the padding).
+    uint32_t col32 = eacc;
+#pragma unroll
+    for (int p = 0; p < kPlanes; ++p) col32 -= static_cast<uint32_t>(__popc(Phi[p] & 0x7FFFFFFFu)) << p;
+
 #pragma unroll
     for (int w = 0; w < 2; ++w) {
 #pragma unroll
@@ -285,6 +318,7 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
                     const uint32_t plane = w ? Phi[p] : Plo[p];
                     val |= ((plane >> j) & 1u) << p;
                 }
+                if (w == 1 && j == 0) val = col32;
                 const uint32_t zbit = ((w ? zhi : zlo) >> j) & 1u;
                 val -= npad * zbit;
 #pragma unroll

@@ -66,7 +66,7 @@ __device__ __forceinline__ void mul64(uint32_t ylo, uint32_t yhi, uint32_t mlo, 
 }
 
 template <int V>
-__device__ __forceinline__ void mix64(uint64_t h, uint64_t cval, const Consts& kc, uint32_t& olo, uint32_t& ohi)
+__device__ __forceinline__ void mix64(uint64_t h, uint64_t cval, const Consts& kc, uint32_t& olo, uint32_t& ohi, uint32_t& eacc)
 {
     uint32_t lo, hi;
     if constexpr (V & 16) {
@@ -90,7 +90,18 @@ __device__ __forceinline__ void mix64(uint64_t h, uint64_t cval, const Consts& k
     yhi = hi ^ shr_hi<V>(hi, 27, kc.m32, 1);
     mul64<V>(ylo, yhi, 0x133111ebu, 0x94d049bbu, lo, hi);
     olo = lo ^ __funnelshift_r(lo, hi, 31);
-    ohi = hi ^ shr_hi<V>(hi, 31, kc.m2, 2);
+    if constexpr (V & 64) {
+        // column 32 of the block is bit0 ^ bit31 of hi: t = hi * 0x80000001 has that xor in bit 31 and
+        // hi's bits 0..30 below it, so popc(t) = popc(hi & 0x7fffffff) + (bit0 ^ bit31); the first term
+        // summed over the hashes is known from the plane counts at the flush.  IMAD + POPC + IMAD.IADD:
+        // no ALU-pipe instruction, instead of SHF + LOP3.
+        uint32_t t;
+        asm("mul.lo.u32 %0, %1, %2;" : "=r"(t) : "r"(hi), "r"(kc.m2 * 0x40000000u + 1u));
+        eacc += __popc(t);
+        ohi = hi;
+    } else {
+        ohi = hi ^ shr_hi<V>(hi, 31, kc.m2, 2);
+    }
 }
 
 __device__ __forceinline__ uint32_t hs4(uint32_t (&P)[kPlanes], uint32_t a, uint32_t b, uint32_t c, uint32_t d)
@@ -105,14 +116,14 @@ __device__ __forceinline__ uint32_t hs4(uint32_t (&P)[kPlanes], uint32_t a, uint
 template <int V>
 __device__ __forceinline__ void group16(const uint64_t* __restrict__ sp, uint64_t cval, const Consts& kc,
                                         uint32_t (&Plo)[kPlanes], uint32_t (&Phi)[kPlanes],
-                                        uint32_t& c16lo, uint32_t& c16hi)
+                                        uint32_t& c16lo, uint32_t& c16hi, uint32_t& eacc)
 {
     uint32_t lo[16], hi[16];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         const ulonglong2 h2 = *reinterpret_cast<const ulonglong2*>(sp + 2 * i);
-        mix64<V>(h2.x, cval, kc, lo[2 * i], hi[2 * i]);
-        mix64<V>(h2.y, cval, kc, lo[2 * i + 1], hi[2 * i + 1]);
+        mix64<V>(h2.x, cval, kc, lo[2 * i], hi[2 * i], eacc);
+        mix64<V>(h2.y, cval, kc, lo[2 * i + 1], hi[2 * i + 1], eacc);
     }
     uint32_t fl[4], fh[4];
 #pragma unroll
@@ -162,7 +173,7 @@ kexp_kernel(const uint64_t* __restrict__ hashes, uint32_t ntasks, uint32_t per, 
 #pragma unroll
     for (int p = 0; p < kPlanes; ++p) { Plo[p] = 0u; Phi[p] = 0u; }
     uint32_t pend16lo = 0, pend16hi = 0, pend32lo = 0, pend32hi = 0, pend64lo = 0, pend64hi = 0;
-    uint32_t g = 0;
+    uint32_t g = 0, eacc = 0;
     const uint32_t ntiles = (per + TILE - 1) / TILE;
 
     auto issue_tile = [&](uint32_t t) {
@@ -199,8 +210,8 @@ kexp_kernel(const uint64_t* __restrict__ hashes, uint32_t ntasks, uint32_t per, 
         const uint32_t ngroups = (valid + 15) >> 4;
         for (uint32_t gi = 0; gi < ngroups; ++gi, ++g) {
             uint32_t c16lo, c16hi;
-            if ((V & 16) && tile_risky) group16<(V & ~16)>(st + gi * 16, cval, kc, Plo, Phi, c16lo, c16hi);
-            else group16<V>(st + gi * 16, cval, kc, Plo, Phi, c16lo, c16hi);
+            if ((V & 16) && tile_risky) group16<(V & ~16)>(st + gi * 16, cval, kc, Plo, Phi, c16lo, c16hi, eacc);
+            else group16<V>(st + gi * 16, cval, kc, Plo, Phi, c16lo, c16hi, eacc);
             if ((g & 1u) == 0u) {
                 pend16lo = c16lo; pend16hi = c16hi;
             } else {
@@ -237,6 +248,13 @@ kexp_kernel(const uint64_t* __restrict__ hashes, uint32_t ntasks, uint32_t per, 
     if ((V & 32) && (g & 4u)) { ripple<6>(Plo, pend64lo); ripple<6>(Phi, pend64hi); }
 
     int32_t* row = out + static_cast<size_t>(wid) * 2048;
+    uint32_t ecount = 0;
+    if constexpr (V & 64) {
+        uint32_t low31 = 0;                      // sum over hashes of popc(hi & 0x7fffffff) = sum_p 2^p * popc(plane_p & 0x7fffffff)
+#pragma unroll
+        for (int p = 0; p < kPlanes; ++p) low31 += static_cast<uint32_t>(__popc(Phi[p] & 0x7FFFFFFFu)) << p;
+        ecount = eacc - low31;
+    }
 #pragma unroll
     for (int w = 0; w < 2; ++w) {
 #pragma unroll
@@ -251,6 +269,7 @@ kexp_kernel(const uint64_t* __restrict__ hashes, uint32_t ntasks, uint32_t per, 
                     const uint32_t plane = w ? Phi[p] : Plo[p];
                     val |= ((plane >> j) & 1u) << p;
                 }
+                if ((V & 64) && w == 1 && j == 0) val = ecount;
                 v[jj] = static_cast<int32_t>(per) - 2 * static_cast<int32_t>(val);
             }
             *reinterpret_cast<int4*>(row + lane * 64 + w * 32 + jq * 4) = make_int4(v[0], v[1], v[2], v[3]);
