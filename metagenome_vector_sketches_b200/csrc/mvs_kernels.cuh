@@ -47,8 +47,8 @@ namespace mvs {
 constexpr int kWarpsPerCta = 4;
 constexpr int kTileHashes = 512;                 // hashes per staging tile (4 KB) per warp
 constexpr int kStages = 2;
-constexpr int kPlanes = 12;                      // bit planes: counts up to 4095 per lane
-constexpr uint32_t kMaxRounds = 4080;            // hashes per lane per task (255 groups of 16)
+constexpr int kPlanes = 14;                      // bit planes: counts up to 16383 per lane
+constexpr uint32_t kMaxRounds = 16368;           // hashes per lane per task (1023 groups of 16)
 constexpr uint32_t kDirect = 0xFFFFFFFFu;
 constexpr uint64_t kGolden = 0x9e3779b97f4a7c15ULL;
 constexpr uint32_t kFold = 0x80000001u;          // passed as a kernel argument so that the multiply stays an IMAD
