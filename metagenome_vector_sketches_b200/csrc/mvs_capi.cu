@@ -72,6 +72,7 @@ struct mvs_ctx {
     uint64_t launches = 0;
     uint64_t slice_hashes = 16ull << 20;         // hashes per streamed slice (128 MB)
     uint64_t slice_rows_bytes = 256ull << 20;    // output bytes per streamed slice
+    uint64_t task_cap = 0;                       // experiment knob: rounds per warp task (0 = planner's choice)
     uint32_t* d_sink = nullptr;
 };
 
@@ -255,6 +256,7 @@ int run_range(mvs_ctx* ctx, Slot& sl, const uint64_t* d_hashes, const uint64_t* 
         uint64_t want = (total * static_cast<uint64_t>(g.passes) + target_tasks - 1) / target_tasks;
         want = (want + g.quantum - 1) / g.quantum * g.quantum;
         g.cap = std::min<uint64_t>(g.cap, std::max<uint64_t>(min_cap, want));
+        if (ctx->task_cap) g.cap = std::min<uint64_t>(g_in.cap, (ctx->task_cap + 15) / 16 * 16 * static_cast<uint64_t>(g.S));
     }
     PlanCounts pc;
     int rc = count_plan(offsets, s0, s1, g, pc);
@@ -680,6 +682,7 @@ int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value)
     if (!ctx || !key) return MVS_ERR_INVALID_ARG;
     if (!std::strcmp(key, "slice_hashes") && value > 0) ctx->slice_hashes = static_cast<uint64_t>(value);
     else if (!std::strcmp(key, "slice_rows_bytes") && value > 0) ctx->slice_rows_bytes = static_cast<uint64_t>(value);
+    else if (!std::strcmp(key, "task_cap") && value >= 0) ctx->task_cap = static_cast<uint64_t>(value);
     return MVS_OK;
 }
 
