@@ -155,7 +155,7 @@ def run_reference_impl(args):
             "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
                              "sample": r["sample"]},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    _emit(line)
     return 0
 
 
@@ -260,7 +260,30 @@ def measured_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+_REAL_STDOUT = None
+
+
+def _quiet_stdout():
+    """Route fd 1 to stderr while the job runs (NCCL / the CUDA runtime print banners on stdout) and keep
+    the real stdout for the ONE JSON line."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def _emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    _quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -288,6 +311,21 @@ def main():
     achieved_ops = total * w / k_s
     hbm_peak, hbm_how = measured_peaks()
     alg_bytes = total * 8 + n * d * 4
+    # Issued-instruction view, the one that cannot exceed 1: per (hash, 32 blocks) round a warp issues
+    # ALU_EQUIV instructions that need an ALU-pipe slot (5 LOP3 + 5 SHF of the mixer, 4.3 LOP3 of the
+    # carry-save tree, 2 IMAD.WIDE which also take an ALU slot -- SASS + profiles/r01b_kexp_issue_mix_and_variants.txt);
+    # the 16-lane ALU pipe takes one warp instruction every 2 clocks (= the live LOP3 peak below).
+    nb = (d + 63) // 64
+    lph = 32 if nb >= 32 else 1 << max(0, (nb - 1).bit_length())
+    rounds = total * ((nb + 31) // 32) / (32 // lph)             # warp rounds of one launch
+    ALU_EQUIV = 16.3
+    alu_lane_ops = rounds * ALU_EQUIV * 32.0 / k_s
+    alu_view = {"bound": "alu-pipe issue", "unit": "Tlane-op/s", "achieved": alu_lane_ops / 1e12,
+                "peak": peaks["lop3"] / 1e12, "frac": alu_lane_ops / peaks["lop3"],
+                "alu_equiv_warp_instr_per_round": ALU_EQUIV,
+                "how": "ALU-slot instructions of the inner loop (static SASS count) x rounds / kernel time, against the "
+                       "live LOP3-only issue peak; ncu (profiles/r01b_project_kernel_ncu_full.txt): pipe_alu 79.4 % + "
+                       "IMAD.WIDE slots, fmaheavy 63.5 %, xu 20.3 %, issue 72.6 %"}
     roofline = {
         "bound": "int32-issue (ALU+FMA pipes); not hbm, not tensor -- see DESIGN.md",
         "achieved": achieved_ops / 1e12, "peak": p_int / 1e12, "unit": "Tint32op/s", "frac": achieved_ops / p_int,
@@ -297,6 +335,7 @@ def main():
         "issue_peaks_Top_s": {k: v / 1e12 for k, v in peaks.items()},
         "note": "algorithmic ops W(d)=d+20*ceil(d/64) per hash (SURVEY 8d); the bit-sliced kernel issues "
                 "fewer instructions than W, so frac may exceed 1; issued-instruction utilisation is in profiles/",
+        "alu_pipe": alu_view,
         "hbm": {"bound": "hbm", "achieved": alg_bytes / k_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
                 "frac": alg_bytes / k_s / 1e9 / hbm_peak, "peak_how": hbm_how,
                 "algorithmic_bytes_per_launch": alg_bytes},
@@ -330,7 +369,7 @@ def main():
             "cpu_baseline": cpu,
             "checksum": g["checksum_dev"],
         }
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
