@@ -16,6 +16,8 @@
 #include <fcntl.h>
 #include <unistd.h>
 
+#include <omp.h>
+
 #include <algorithm>
 #include <chrono>
 #include <cmath>
@@ -42,28 +44,146 @@ inline bool is_space(unsigned char c)            // isspace() in the "C" locale,
 //   * a magnitude above 2^64-1 sets failbit: nothing is inserted and the loop ends;
 //   * extraction stops at the first non-digit; the NEXT extraction starts right there, so "5x"
 //     yields 5 and then ends the line, while "5-3" yields 5 and 2^64-3.
-void parse_tokens(const char* p, const char* e, std::vector<uint64_t>& out)
+// Every token owns one maximal run of digits, so the number of digit runs of a line is an upper
+// bound of its token count (exact for well-formed lines): count_digit_runs() sizes the output.
+
+inline bool is_digit(unsigned char c) { return static_cast<unsigned>(c - '0') < 10u; }
+
+// eight ASCII digits at once (little endian: first character in the lowest byte)
+inline bool all_digits8(uint64_t w)
 {
+    return ((w & 0xF0F0F0F0F0F0F0F0ull) | (((w + 0x0606060606060606ull) & 0xF0F0F0F0F0F0F0F0ull) >> 4)) ==
+           0x3333333333333333ull;
+}
+inline uint64_t parse8(uint64_t w)
+{
+    w -= 0x3030303030303030ull;
+    w = (w * 10) + (w >> 8);
+    return (((w & 0x000000FF000000FFull) * (100ull + (1000000ull << 32))) +
+            (((w >> 16) & 0x000000FF000000FFull) * (1ull + (10000ull << 32)))) >> 32;
+}
+
+uint64_t count_digit_runs(const char* b, const char* e)
+{
+    if (b >= e) return 0;
+    uint64_t n = is_digit(static_cast<unsigned char>(*b)) ? 1 : 0;
+    const unsigned char* u = reinterpret_cast<const unsigned char*>(b);
+    const size_t len = static_cast<size_t>(e - b);
+    for (size_t i = 1; i < len; ++i) n += static_cast<uint64_t>(is_digit(u[i]) & !is_digit(u[i - 1]));
+    return n;
+}
+
+// Parses [p, e) into dst (room for count_digit_runs(p, e) values).  `safe_end` is the end of the
+// mapping: 8-byte loads are only issued while p + 8 <= safe_end.  Returns the token count;
+// *strictly_increasing tells whether the values came sorted and unique (then no dedupe is needed).
+size_t parse_tokens(const char* p, const char* e, const char* safe_end, uint64_t* dst, bool* strictly_increasing)
+{
+    size_t n = 0;
+    bool inc = true;
+    uint64_t prev = 0;
     for (;;) {
         while (p < e && is_space(static_cast<unsigned char>(*p))) ++p;
-        if (p >= e) return;
+        if (p >= e) break;
         bool neg = false;
         if (*p == '+' || *p == '-') {
             neg = (*p == '-');
             ++p;
         }
-        if (p >= e || *p < '0' || *p > '9') return;
+        if (p >= e || !is_digit(static_cast<unsigned char>(*p))) break;
         uint64_t v = 0;
+        int nd = 0;
+        // up to 16 digits in two 8-digit steps: no overflow possible below 19 digits
+        while (nd <= 8 && p + 8 <= e && p + 8 <= safe_end) {
+            uint64_t w;
+            std::memcpy(&w, p, 8);
+            if (!all_digits8(w)) break;
+            v = v * 100000000ull + parse8(w);
+            p += 8;
+            nd += 8;
+        }
         bool overflow = false;
-        while (p < e && *p >= '0' && *p <= '9') {
+        while (p < e && is_digit(static_cast<unsigned char>(*p))) {
             const uint64_t dgt = static_cast<uint64_t>(*p - '0');
-            if (v > (UINT64_MAX - dgt) / 10) overflow = true;
+            if (nd >= 19 && v > (UINT64_MAX - dgt) / 10) overflow = true;
             v = v * 10 + dgt;
             ++p;
+            ++nd;
         }
-        if (overflow) return;
-        out.push_back(neg ? (0 - v) : v);
+        if (overflow) break;
+        if (neg) v = 0 - v;
+        inc &= (n == 0) | (v > prev);
+        prev = v;
+        dst[n++] = v;
     }
+    *strictly_increasing = inc;
+    return n;
+}
+
+// One line -> a set (sorted + unique unless it already was strictly increasing).
+size_t parse_line_set(const char* b, const char* e, const char* safe_end, uint64_t* dst)
+{
+    bool inc = true;
+    size_t n = parse_tokens(b, e, safe_end, dst, &inc);
+    if (!inc) {                                                         // unordered_set semantics
+        std::sort(dst, dst + n);
+        n = static_cast<size_t>(std::unique(dst, dst + n) - dst);
+    }
+    return n;
+}
+
+struct LineRef {
+    const char* name_b;
+    const char* name_e;
+    const char* b;                               // token text
+    const char* e;
+    uint64_t bound;                              // upper bound of the token count
+};
+
+// Line index of a mapped hash file: std::getline semantics ('\n' separated, a last line without
+// '\n' is kept if non-empty), lines without ':' skipped in named mode (reference :267).  The
+// newline scan and the per-line digit-run count both run in parallel.
+void index_lines(const char* data, size_t size, int named, std::vector<LineRef>& lines)
+{
+    lines.clear();
+    if (size == 0) return;
+    int T = 1;
+#pragma omp parallel
+    {
+#pragma omp single
+        T = omp_get_num_threads();
+    }
+    const size_t piece = std::max<size_t>(1 << 20, (size + static_cast<size_t>(T) - 1) / static_cast<size_t>(T));
+    const size_t npieces = (size + piece - 1) / piece;
+    std::vector<std::vector<size_t>> nl(npieces);
+#pragma omp parallel for schedule(dynamic, 1)
+    for (size_t k = 0; k < npieces; ++k) {
+        const char* p = data + k * piece;
+        const char* pe = data + std::min(size, (k + 1) * piece);
+        while (p < pe) {
+            const char* q = static_cast<const char*>(std::memchr(p, '\n', static_cast<size_t>(pe - p)));
+            if (!q) break;
+            nl[k].push_back(static_cast<size_t>(q - data));
+            p = q + 1;
+        }
+    }
+    size_t pos = 0;
+    auto add_line = [&](const char* b, const char* e) {
+        if (named) {
+            const char* colon = static_cast<const char*>(std::memchr(b, ':', static_cast<size_t>(e - b)));
+            if (colon) lines.push_back({b, colon, colon + 1, e, 0});
+        } else {
+            lines.push_back({nullptr, nullptr, b, e, 0});
+        }
+    };
+    for (size_t k = 0; k < npieces; ++k)
+        for (size_t q : nl[k]) {
+            add_line(data + pos, data + q);
+            pos = q + 1;
+        }
+    if (pos < size) add_line(data + pos, data + size);
+    const int64_t n = static_cast<int64_t>(lines.size());
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t i = 0; i < n; ++i) lines[static_cast<size_t>(i)].bound = count_digit_runs(lines[i].b, lines[i].e);
 }
 
 struct Mapped {
@@ -142,62 +262,49 @@ int mvs_parse_hash_file(const char* path, int named, mvs_hash_batch** out)
     Mapped mf(path);
     if (!mf.ok) return MVS_ERR_IO;
 
-    // 1. line boundaries (std::getline semantics: '\n' separated, last line kept if non-empty)
-    struct Line { const char* name_b; const char* name_e; const char* b; const char* e; };
-    std::vector<Line> lines;
-    const char* p = mf.data;
-    const char* end = mf.data + mf.size;
-    while (p < end) {
-        const char* nl = static_cast<const char*>(std::memchr(p, '\n', static_cast<size_t>(end - p)));
-        const char* le = nl ? nl : end;
-        if (named) {
-            const char* colon = static_cast<const char*>(std::memchr(p, ':', static_cast<size_t>(le - p)));
-            if (colon) lines.push_back({p, colon, colon + 1, le});     // lines without ':' are skipped (:267)
-        } else {
-            lines.push_back({nullptr, nullptr, p, le});
-        }
-        if (!nl) break;
-        p = nl + 1;
-    }
-
-    // 2. parse + dedupe every line (parallel over lines)
+    // 1. line index + an upper bound of every line's token count (both parallel)
+    std::vector<LineRef> lines;
+    index_lines(mf.data, mf.size, named, lines);
     const int64_t n = static_cast<int64_t>(lines.size());
-    std::vector<std::vector<uint64_t>> sets(static_cast<size_t>(n));
-#pragma omp parallel for schedule(dynamic, 4)
-    for (int64_t i = 0; i < n; ++i) {
-        std::vector<uint64_t>& v = sets[static_cast<size_t>(i)];
-        const Line& ln = lines[static_cast<size_t>(i)];
-        v.reserve(static_cast<size_t>(ln.e - ln.b) / 16 + 4);
-        parse_tokens(ln.b, ln.e, v);
-        std::sort(v.begin(), v.end());                                  // unordered_set semantics
-        v.erase(std::unique(v.begin(), v.end()), v.end());
-    }
 
-    // 3. CSR in (pinned) host memory
     mvs_hash_batch* b = static_cast<mvs_hash_batch*>(std::calloc(1, sizeof(mvs_hash_batch)));
     if (!b) return MVS_ERR_OOM;
     b->n_samples = n;
     b->offsets = static_cast<uint64_t*>(std::malloc(sizeof(uint64_t) * static_cast<size_t>(n + 1)));
     if (!b->offsets) { mvs_free_hash_batch(b); return MVS_ERR_OOM; }
+    uint64_t bound_total = 0;
+    for (int64_t i = 0; i < n; ++i) {
+        b->offsets[i] = bound_total;                                    // tentative: start of the line's slot
+        bound_total += lines[static_cast<size_t>(i)].bound;
+    }
+    b->offsets[n] = bound_total;
+    b->hashes = static_cast<uint64_t*>(host_alloc_any(sizeof(uint64_t) * (bound_total + 2), &b->hashes_pinned));
+    if (!b->hashes) { mvs_free_hash_batch(b); return MVS_ERR_OOM; }
+
+    // 2. parse + dedupe every line straight into its slot of the (pinned) CSR payload
+    std::vector<uint64_t> count(static_cast<size_t>(n ? n : 1));
+    const char* safe_end = mf.data + mf.size;
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t i = 0; i < n; ++i) {
+        const LineRef& ln = lines[static_cast<size_t>(i)];
+        count[static_cast<size_t>(i)] = parse_line_set(ln.b, ln.e, safe_end, b->hashes + b->offsets[i]);
+    }
+
+    // 3. close the gaps left by malformed / duplicated tokens (none for well-formed files)
     uint64_t total = 0;
     for (int64_t i = 0; i < n; ++i) {
+        const uint64_t from = b->offsets[i], c = count[static_cast<size_t>(i)];
+        if (from != total && c) std::memmove(b->hashes + total, b->hashes + from, c * sizeof(uint64_t));
         b->offsets[i] = total;
-        total += sets[static_cast<size_t>(i)].size();
+        total += c;
     }
     b->offsets[n] = total;
     b->n_hashes = total;
-    b->hashes = static_cast<uint64_t*>(host_alloc_any(sizeof(uint64_t) * (total + 2), &b->hashes_pinned));
-    if (!b->hashes) { mvs_free_hash_batch(b); return MVS_ERR_OOM; }
-#pragma omp parallel for schedule(dynamic, 4)
-    for (int64_t i = 0; i < n; ++i) {
-        const auto& v = sets[static_cast<size_t>(i)];
-        if (!v.empty()) std::memcpy(b->hashes + b->offsets[i], v.data(), v.size() * sizeof(uint64_t));
-    }
     if (named) {
         b->names = static_cast<char**>(std::calloc(static_cast<size_t>(n ? n : 1), sizeof(char*)));
         if (!b->names) { mvs_free_hash_batch(b); return MVS_ERR_OOM; }
         for (int64_t i = 0; i < n; ++i) {
-            const Line& ln = lines[static_cast<size_t>(i)];
+            const LineRef& ln = lines[static_cast<size_t>(i)];
             const size_t len = static_cast<size_t>(ln.name_e - ln.name_b);
             b->names[i] = static_cast<char*>(std::malloc(len + 1));
             if (!b->names[i]) { mvs_free_hash_batch(b); return MVS_ERR_OOM; }

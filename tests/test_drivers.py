@@ -63,6 +63,46 @@ def test_parser_standalone_mode_lines(tmp_path):
     assert parse_file(str(tmp_path / "missing"), True)[0] == -6      # MVS_ERR_IO
 
 
+def test_parser_swar_fuzz_against_stream_semantics(tmp_path):
+    """The 8-digits-at-a-time path (mvs_driver.cpp parse_tokens) against the character-by-character
+    model of `iss >> unsigned long`: every digit count 1..22 (overflow at 20+), leading zeros, signs,
+    junk that ends a line, duplicates / unsorted lines, a last line without newline that ends exactly
+    at the end of the mapping (no 8-byte load may cross it)."""
+    rng = np.random.default_rng(7)
+    lines = []
+    for k in range(400):
+        toks = []
+        for _ in range(int(rng.integers(0, 40))):
+            nd = int(rng.integers(1, 23))
+            t = "".join(rng.choice(list("0123456789"), size=nd))
+            r = rng.random()
+            if r < 0.05:
+                t = "-" + t
+            elif r < 0.1:
+                t = "+" + t
+            elif r < 0.12:
+                t = t + "x"
+            elif r < 0.14:
+                t = "18446744073709551615"
+            elif r < 0.16:
+                t = "18446744073709551616"
+            elif r < 0.2 and toks:
+                t = toks[int(rng.integers(0, len(toks)))]               # duplicate
+            toks.append(t)
+        sep = [" ", "  ", "\t", " \r"][k % 4]
+        lines.append("s%d:" % k + sep.join([""] + toks))
+    for tail in ("\n", "", " 12345678", " 1234567", " 123456789012345678901"):
+        text = "\n".join(lines) + tail
+        p = tmp_path / "fuzz.txt"
+        p.write_bytes(text.encode())
+        rc, names, sets = parse_file(str(p), True)
+        assert rc == 0
+        want = [l for l in text.split("\n") if ":" in l]
+        assert names == [l[: l.index(":")] for l in want]
+        for l, s in zip(want, sets):
+            assert s.tolist() == sorted(set(parse_line_like_reference(l[l.index(":") + 1:]))), l
+
+
 def test_parser_toy_roundtrip(tmp_path):
     names, offsets, hashes = load_toy()
     p = tmp_path / "toy.txt"
