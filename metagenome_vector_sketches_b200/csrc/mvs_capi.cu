@@ -217,7 +217,14 @@ cudaError_t launch_project_t(cudaStream_t st, uint32_t ntasks, const uint64_t* d
                              int d, uint64_t seed, int32_t* d_out, int32_t* d_partials, int vec4)
 {
     const uint32_t grid = (ntasks + mvs::kWarpsPerCta - 1) / mvs::kWarpsPerCta;
-    const size_t smem = static_cast<size_t>(mvs::kWarpsPerCta) * mvs::kStages * mvs::kTileHashes * sizeof(uint64_t);
+    // per warp: kStages raw tiles (8 B per hash) + one cooked tile (16 B per hash) = 8 KB; 32 KB per CTA
+    const size_t smem = static_cast<size_t>(mvs::kWarpsPerCta) * mvs::tile_hashes(L) *
+                        (mvs::kStages * sizeof(uint64_t) + sizeof(ulonglong2));
+    if (smem > 48 * 1024) {                      // only L = 0 (d <= 64): 64 KB
+        cudaError_t e = cudaFuncSetAttribute(mvs::project_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             static_cast<int>(smem));
+        if (e != cudaSuccess) return e;
+    }
     mvs::project_kernel<L><<<grid, mvs::kWarpsPerCta * 32, smem, st>>>(d_hashes, d_tasks, ntasks, d,
                                                                      seed + mvs::kGolden, d_out, d_partials, vec4,
                                                                      mvs::kFold);

@@ -21,12 +21,19 @@
 // (splitmix64(0 + c) per lane) is subtracted at the flush, so the inner loop has no
 // masking at all.
 //
-// The 64-bit add `hash + c_lane` is hoisted out of the (hash, lane) loop: once a tile has
-// landed, the warp adds the task constant  base = golden + seed + 2048*pass  to every
-// staged hash in place (one add per HASH, not per hash and lane), so a lane only adds its
-// own  64*block < 2048  to the low word.  That add can carry into the high word only if
-// low32(hash + base) >= 2^32 - 2048, about one hash in two million; the tile pass votes on
-// it and a flagged tile (2.4e-4 of them) runs the same loop with the exact 64-bit add.
+// Everything of the mixer that does not depend on the lane is hoisted out of the (hash, lane) loop
+// into a per-tile pass ("cooking"): once a tile of raw hashes has landed, the warp computes for every
+// HASH, not per hash and lane,
+//     hb = hash + base,  base = golden + seed + 2048*pass            (the 64-bit add)
+//     F  = (lo32(hb) >> 30) | (hi32(hb) << 2)                         (low word of hb >> 30)
+//     M  = (hi32(hb) ^ (hi32(hb) >> 30)) * lo32(K1)                   (high-word term of the 1st multiply)
+// and stores the 16-byte record {hb, F, M}.  A lane then only adds its own  off = 64*block < 2048  to
+// the low word:  xl = lo32(hb) + off,  l1 = xl ^ F,  and the first multiply is
+// (hi32(l1*lo32(K1)) + l1*hi32(K1) + M, lo32(l1*lo32(K1))).  This is exact as long as the add neither
+// carries out of the low word nor changes its bits 30..31, i.e. unless
+// (lo32(hb) mod 2^30) >= 2^30 - 2048, about one hash in 5e5; the tile pass votes on it and a flagged
+// tile (5e-4 of them) runs the same loop with the plain 64-bit arithmetic on hb.  Per (hash, lane)
+// this removes 3 SHF/LOP3/IADD from the ALU pipe and 1 IMAD (tools/kexp: 38.5 -> 34.2 clocks).
 //
 // The last mixer step  x ^= x >> 31  changes only bit 0 of the high word (bit0 ^= bit31), i.e.
 // one column (32) of the 64-column block, for two ALU-pipe instructions per (hash, lane).
@@ -45,14 +52,17 @@
 namespace mvs {
 
 constexpr int kWarpsPerCta = 4;
-constexpr int kTileHashes = 512;                 // hashes per staging tile (4 KB) per warp
+// hashes per staging tile per warp: 256 (2 KB raw x 2 stages + 4 KB cooked), but at least one
+// Harley-Seal group of 16 rounds for all S hash slots (S = 32, i.e. d <= 64, needs 512)
+__host__ __device__ constexpr int tile_hashes(int lph_log2) { return (32 >> lph_log2) * 16 > 256 ? (32 >> lph_log2) * 16 : 256; }
 constexpr int kStages = 2;
 constexpr int kPlanes = 14;                      // bit planes: counts up to 16383 per lane
 constexpr uint32_t kMaxRounds = 16368;           // hashes per lane per task (1023 groups of 16)
 constexpr uint32_t kDirect = 0xFFFFFFFFu;
 constexpr uint64_t kGolden = 0x9e3779b97f4a7c15ULL;
 constexpr uint32_t kFold = 0x80000001u;          // passed as a kernel argument so that the multiply stays an IMAD
-constexpr uint32_t kCarryRisk = 0xFFFFF800u;     // low words >= 2^32 - 2048 may carry when 64*block is added
+constexpr uint32_t kCarryRisk = 0xFFFFF800u;     // (lo32(hb) | 0xC0000000) >= this: + 64*block may reach bit 30
+constexpr uint32_t kK1lo = 0x1ce4e5b9u, kK1hi = 0xbf58476du;   // 0xbf58476d1ce4e5b9
 
 struct __align__(16) WarpTask {                  // 32 bytes
     uint64_t begin;                              // first hash (index into the batch array)
@@ -80,22 +90,27 @@ __device__ __forceinline__ void mix64(uint64_t x, uint32_t& lo, uint32_t& hi)
     hi = static_cast<uint32_t>(x >> 32);
 }
 
-// hb = hash + base (already added in shared memory), off = 64*block of this lane (< 2048).
-// EXACT = false: the tile pass has proved that low32(hb) + off cannot carry.
+// c = cooked record of one hash: c.x = hb = hash + base, c.y = {F, M} (see header); off = 64*block of
+// this lane (< 2048).  EXACT = false: the tile pass has proved that lo32(hb) + off stays below bit 30.
 // Outputs: lo = final low word; hi = high word BEFORE the last xor-shift (columns 33..63 are
 // final, slot 0 holds the raw bit 0); eacc += popc(hi * fold), fold = 0x80000001 (see header).
 template <bool EXACT>
-__device__ __forceinline__ void mix_staged(uint64_t hb, uint32_t off, uint32_t fold, uint32_t& lo, uint32_t& hi,
+__device__ __forceinline__ void mix_staged(ulonglong2 c, uint32_t off, uint32_t fold, uint32_t& lo, uint32_t& hi,
                                            uint32_t& eacc)
 {
     uint64_t x;
     if constexpr (EXACT) {
-        x = hb + off;
+        x = c.x + off;
+        x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ULL;
     } else {
-        const uint32_t xlo = static_cast<uint32_t>(hb) + off;
-        x = (hb & 0xFFFFFFFF00000000ULL) | xlo;
+        const uint32_t xl = static_cast<uint32_t>(c.x) + off;
+        const uint32_t l1 = xl ^ static_cast<uint32_t>(c.y);
+        uint32_t t = static_cast<uint32_t>(c.y >> 32);
+        asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(t) : "r"(l1), "r"(kK1hi));
+        uint64_t w;
+        asm("mul.wide.u32 %0, %1, %2;" : "=l"(w) : "r"(l1), "r"(kK1lo));
+        x = (static_cast<uint64_t>(static_cast<uint32_t>(w >> 32) + t) << 32) | static_cast<uint32_t>(w);
     }
-    x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ULL;
     x = (x ^ (x >> 27)) * 0x94d049bb133111ebULL;
     const uint32_t xl = static_cast<uint32_t>(x);
     const uint32_t xh = static_cast<uint32_t>(x >> 32);
@@ -104,6 +119,18 @@ __device__ __forceinline__ void mix_staged(uint64_t hb, uint32_t off, uint32_t f
     uint32_t t;
     asm("mul.lo.u32 %0, %1, %2;" : "=r"(t) : "r"(xh), "r"(fold));
     eacc += static_cast<uint32_t>(__popc(t));
+}
+
+// tile pass: raw hash -> cooked record
+__device__ __forceinline__ ulonglong2 cook(uint64_t raw, uint64_t base, bool& risky)
+{
+    const uint64_t hb = raw + base;
+    const uint32_t xl = static_cast<uint32_t>(hb);
+    const uint32_t xh = static_cast<uint32_t>(hb >> 32);
+    risky |= (xl | 0xC0000000u) >= kCarryRisk;
+    const uint32_t f = (xl >> 30) | (xh << 2);
+    const uint32_t m = (xh ^ (xh >> 30)) * kK1lo;
+    return make_ulonglong2(hb, (static_cast<uint64_t>(m) << 32) | f);
 }
 
 // carry-save adder on 32 bit columns at once: s = a^b^c, c = maj(a,b,c)
@@ -139,25 +166,16 @@ __device__ __forceinline__ uint32_t hs4(uint32_t (&P)[kPlanes], uint32_t a, uint
 }
 
 // One Harley-Seal group: 16 hashes of this lane's stream -> planes 0..3 + a weight-16
-// carry per word.  sp points at the lane's first (pre-added) hash of the group in shared
-// memory; consecutive hashes of the lane are S entries apart.
+// carry per word.  sp points at the lane's first cooked record of the group in shared
+// memory; consecutive hashes of the lane are S records apart.
 template <int S, bool EXACT>
-__device__ __forceinline__ void group16(const uint64_t* __restrict__ sp, uint32_t off, uint32_t fold,
+__device__ __forceinline__ void group16(const ulonglong2* __restrict__ sp, uint32_t off, uint32_t fold,
                                         uint32_t (&Plo)[kPlanes], uint32_t (&Phi)[kPlanes],
                                         uint32_t& c16lo, uint32_t& c16hi, uint32_t& eacc)
 {
     uint32_t lo[16], hi[16];
-    if constexpr (S == 1) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const ulonglong2 h2 = *reinterpret_cast<const ulonglong2*>(sp + 2 * i);   // LDS.128 broadcast
-            mix_staged<EXACT>(h2.x, off, fold, lo[2 * i], hi[2 * i], eacc);
-            mix_staged<EXACT>(h2.y, off, fold, lo[2 * i + 1], hi[2 * i + 1], eacc);
-        }
-    } else {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) mix_staged<EXACT>(sp[i * S], off, fold, lo[i], hi[i], eacc);
-    }
+    for (int i = 0; i < 16; ++i) mix_staged<EXACT>(sp[i * S], off, fold, lo[i], hi[i], eacc);   // LDS.128 (broadcast if S == 1)
     uint32_t fl[4], fh[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
@@ -193,7 +211,9 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
 {
     constexpr int LPH = 1 << LPH_LOG2;
     constexpr int S = 32 >> LPH_LOG2;
+    constexpr int kTileHashes = tile_hashes(LPH_LOG2);
     constexpr int kGroupsPerTile = kTileHashes / (16 * S);
+    static_assert(kGroupsPerTile >= 1, "a tile holds at least one group");
 
     extern __shared__ __align__(16) uint64_t smem[];
     const int warp = threadIdx.x >> 5;
@@ -202,7 +222,8 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
     if (wid >= ntasks) return;                   // warps are independent: no CTA-wide barrier below
 
     const WarpTask task = tasks[wid];
-    uint64_t* ring = smem + warp * (kStages * kTileHashes);
+    uint64_t* ring = smem + warp * (kStages * kTileHashes);                                  // raw hashes, 2 stages
+    ulonglong2* cooked = reinterpret_cast<ulonglong2*>(smem + kWarpsPerCta * kStages * kTileHashes) + warp * kTileHashes;
     const uint64_t* src = hashes + task.begin;
     const uint32_t count = task.count;
 
@@ -239,15 +260,11 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
         cp_async_commit();
         cp_async_wait<1>();
         __syncwarp();
-        uint64_t* st = ring + (t & (kStages - 1)) * kTileHashes;
-        // tile pass: hash += base in place; vote whether any low word could carry under + off
+        const uint64_t* st = ring + (t & (kStages - 1)) * kTileHashes;
+        // tile pass: raw -> cooked records; vote whether any low word could reach bit 30 under + off
         bool risky = false;
 #pragma unroll
-        for (int i = 0; i < kTileHashes / 32; ++i) {
-            const uint64_t v = st[i * 32 + lane] + base;
-            risky |= static_cast<uint32_t>(v) >= kCarryRisk;
-            st[i * 32 + lane] = v;
-        }
+        for (int i = 0; i < kTileHashes / 32; ++i) cooked[i * 32 + lane] = cook(st[i * 32 + lane], base, risky);
         const bool exact = __any_sync(0xffffffffu, risky);
         __syncwarp();
         const uint32_t valid = min(count - t * kTileHashes, static_cast<uint32_t>(kTileHashes));
@@ -255,8 +272,8 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
         const uint32_t ngroups = (rounds + 15) >> 4;           // <= kGroupsPerTile
         for (uint32_t gi = 0; gi < ngroups; ++gi, ++g) {
             uint32_t c16lo, c16hi;
-            if (exact) group16<S, true>(st + gi * (16 * S) + slot, off, fold, Plo, Phi, c16lo, c16hi, eacc);
-            else group16<S, false>(st + gi * (16 * S) + slot, off, fold, Plo, Phi, c16lo, c16hi, eacc);
+            if (exact) group16<S, true>(cooked + gi * (16 * S) + slot, off, fold, Plo, Phi, c16lo, c16hi, eacc);
+            else group16<S, false>(cooked + gi * (16 * S) + slot, off, fold, Plo, Phi, c16lo, c16hi, eacc);
             if ((g & 1u) == 0u) {
                 pend16lo = c16lo; pend16hi = c16hi;
             } else {
@@ -274,7 +291,7 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
                 }
             }
         }
-        __syncwarp();                            // stage may be overwritten by the next issue
+        __syncwarp();                            // stage and cooked tile may be overwritten next
     }
     (void)kGroupsPerTile;
     // fold the pending carries (g = number of groups done)

@@ -88,7 +88,7 @@ def test_seed_is_additive_and_zero_is_reference(sk):
 
 def test_carry_window_of_the_hoisted_add(sk):
     """The kernel adds base = golden + seed + 2048*pass once per hash and 64*block per lane on the
-    low word only; hashes whose low word lands in [2^32 - 2048, 2^32) after the base add must take
+    low word only; hashes whose low word lands in [k*2^30 - 2048, k*2^30) after the base add must take
     the exact path.  Build samples that sit in and around that window for every pass / seed."""
     golden = 0x9E3779B97F4A7C15
     rng = np.random.default_rng(77)
@@ -98,8 +98,11 @@ def test_carry_window_of_the_hoisted_add(sk):
         for p in range(passes):
             base = (golden + seed + 2048 * p) % 2 ** 64
             # low words of hash + base: the whole window, its two edges, and plain wrap-around values
+            # ... and, since the cooked tile pass also fixes bits 30..31 of the low word per hash, the
+            # windows below every multiple of 2^30 (where + 64*block reaches bit 30) with both edges
             lows = np.concatenate([np.arange(2 ** 32 - 2112, 2 ** 32, dtype=np.uint64),
-                                   np.arange(0, 64, dtype=np.uint64)])
+                                   np.arange(0, 64, dtype=np.uint64)] +
+                                  [np.arange(k * 2 ** 30 - 2112, k * 2 ** 30 + 64, 3, dtype=np.uint64) for k in (1, 2, 3)])
             highs = rng.integers(0, 2 ** 32, len(lows), dtype=np.uint64)
             target = (highs << np.uint64(32)) | lows
             with np.errstate(over="ignore"):

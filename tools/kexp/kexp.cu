@@ -140,6 +140,69 @@ __device__ __forceinline__ void group16(const uint64_t* __restrict__ sp, uint64_
     csa(c16hi, Phi[3], Phi[3], eA, eB);
 }
 
+// ---- V & 128: "cooked" tiles -----------------------------------------------------------
+// The tile pass stores per hash 16 bytes {lo32(hb), hi32(hb), 0, M}, M = (xh ^ (xh >> 30)) * K1lo with
+// xh = hi32(hb): when lo32(hb) + 64*block cannot carry, the high word of x ^ (x >> 30) and its product
+// with the low word of the first multiplier are the same for all 32 lanes, so the lane skips one
+// SHF + one LOP3 (ALU pipe) and one IMAD, and {0, M} is the 64-bit addend of the IMAD.WIDE.
+// V & 8 here: lane add as IMAD (FMA pipe).  V & 4: second multiply as wide + 2 mad.lo.
+template <int V, bool EXACT>
+__device__ __forceinline__ void mix_cooked(ulonglong2 c, uint32_t off, const Consts& kc, uint32_t& olo, uint32_t& ohi,
+                                           uint32_t& eacc)
+{
+    uint32_t lo, hi;
+    if constexpr (EXACT) {
+        const uint64_t x = c.x + off;
+        const uint64_t y = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ULL;
+        lo = static_cast<uint32_t>(y);
+        hi = static_cast<uint32_t>(y >> 32);
+    } else {
+        uint32_t xl;
+        if constexpr (V & 8) asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(xl) : "r"(off), "r"(kc.m2 >> 1), "r"(static_cast<uint32_t>(c.x)));
+        else xl = static_cast<uint32_t>(c.x) + off;
+        // V & 256: the funnel word (xl >> 30) | (xh << 2) is per hash too unless + off reaches bit 30
+        const uint32_t l1 = (V & 256) ? (xl ^ static_cast<uint32_t>(c.y))
+                                      : (xl ^ __funnelshift_r(xl, static_cast<uint32_t>(c.x >> 32), 30));
+        uint32_t t = static_cast<uint32_t>(c.y >> 32);                  // M
+        asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(t) : "r"(l1), "r"(0xbf58476du));
+        uint64_t y;
+        asm("mul.wide.u32 %0, %1, %2;" : "=l"(y) : "r"(l1), "r"(0x1ce4e5b9u));
+        lo = static_cast<uint32_t>(y);
+        hi = static_cast<uint32_t>(y >> 32) + t;
+    }
+    const uint32_t ylo = lo ^ __funnelshift_r(lo, hi, 27);
+    const uint32_t yhi = hi ^ (hi >> 27);
+    mul64<V>(ylo, yhi, 0x133111ebu, 0x94d049bbu, lo, hi);
+    olo = lo ^ __funnelshift_r(lo, hi, 31);
+    uint32_t t;
+    asm("mul.lo.u32 %0, %1, %2;" : "=r"(t) : "r"(hi), "r"(kc.m2 * 0x40000000u + 1u));
+    eacc += __popc(t);
+    ohi = hi;
+}
+
+template <int V, bool EXACT>
+__device__ __forceinline__ void group16c(const ulonglong2* __restrict__ sp, uint32_t off, const Consts& kc,
+                                         uint32_t (&Plo)[kPlanes], uint32_t (&Phi)[kPlanes],
+                                         uint32_t& c16lo, uint32_t& c16hi, uint32_t& eacc)
+{
+    uint32_t lo[16], hi[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) mix_cooked<V, EXACT>(sp[i], off, kc, lo[i], hi[i], eacc);
+    uint32_t fl[4], fh[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        fl[q] = hs4(Plo, lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+        fh[q] = hs4(Phi, hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+    }
+    uint32_t eA, eB;
+    csa(eA, Plo[2], Plo[2], fl[0], fl[1]);
+    csa(eB, Plo[2], Plo[2], fl[2], fl[3]);
+    csa(c16lo, Plo[3], Plo[3], eA, eB);
+    csa(eA, Phi[2], Phi[2], fh[0], fh[1]);
+    csa(eB, Phi[2], Phi[2], fh[2], fh[3]);
+    csa(c16hi, Phi[3], Phi[3], eA, eB);
+}
+
 __device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc, uint32_t src_bytes)
 {
     const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
@@ -195,7 +258,22 @@ kexp_kernel(const uint64_t* __restrict__ hashes, uint32_t ntasks, uint32_t per, 
         __syncwarp();
         uint64_t* st = ring + (t & 1) * TILE;
         bool tile_risky = false;
-        if constexpr (V & 16) {
+        ulonglong2* cooked = reinterpret_cast<ulonglong2*>(smem + WARPS * 2 * TILE) + warp * TILE;
+        if constexpr (V & 128) {
+            bool risky = false;
+#pragma unroll
+            for (int i = 0; i < TILE / 32; ++i) {
+                const uint64_t v = st[i * 32 + lane] + kGolden;
+                const uint32_t xl0 = static_cast<uint32_t>(v);
+                risky |= (V & 256) ? ((xl0 | 0xC0000000u) >= 0xFFFFF800u) : (xl0 >= 0xFFFFF840u);
+                const uint32_t xh = static_cast<uint32_t>(v >> 32);
+                const uint32_t m = (xh ^ (xh >> 30)) * 0x1ce4e5b9u;
+                const uint32_t f = (xl0 >> 30) | (xh << 2);
+                cooked[i * 32 + lane] = make_ulonglong2(v, (static_cast<uint64_t>(m) << 32) | ((V & 256) ? f : 0u));
+            }
+            tile_risky = __any_sync(0xffffffffu, risky);
+            __syncwarp();
+        } else if constexpr (V & 16) {
             bool risky = false;
 #pragma unroll
             for (int i = 0; i < TILE / 32; ++i) {
@@ -210,6 +288,10 @@ kexp_kernel(const uint64_t* __restrict__ hashes, uint32_t ntasks, uint32_t per, 
         const uint32_t ngroups = (valid + 15) >> 4;
         for (uint32_t gi = 0; gi < ngroups; ++gi, ++g) {
             uint32_t c16lo, c16hi;
+            if constexpr (V & 128) {
+                if (tile_risky) group16c<V, true>(cooked + gi * 16, static_cast<uint32_t>(lane) << 6, kc, Plo, Phi, c16lo, c16hi, eacc);
+                else group16c<V, false>(cooked + gi * 16, static_cast<uint32_t>(lane) << 6, kc, Plo, Phi, c16lo, c16hi, eacc);
+            } else
             if ((V & 16) && tile_risky) group16<(V & ~16)>(st + gi * 16, cval, kc, Plo, Phi, c16lo, c16hi, eacc);
             else group16<V>(st + gi * 16, cval, kc, Plo, Phi, c16lo, c16hi, eacc);
             if ((g & 1u) == 0u) {
@@ -392,7 +474,7 @@ void run(const char* name)
 {
     const Consts kc{4u, 32u, 2u};
     const uint32_t grid = (g_ntasks + WARPS - 1) / WARPS;
-    const size_t smem = static_cast<size_t>(WARPS) * 2 * TILE * 8;
+    const size_t smem = static_cast<size_t>(WARPS) * 2 * TILE * 8 + ((V & 128) ? static_cast<size_t>(WARPS) * TILE * 16 : 0);
     CK(cudaFuncSetAttribute(kexp_kernel<V, WARPS, TILE>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
