@@ -37,6 +37,12 @@ UNIT = "hashes/s"
 WORKLOAD = "configs[1]: synthetic 10k samples x 50k hashes, d=2048, seed 0"
 
 
+# dram__bytes_read.sum (4.003425 GB) + dram__bytes_write.sum (317.2 MB) of one project_kernel launch of the default
+# workload, profiles/r01c_project_kernel_ncu_full.txt; algorithmic bytes are 4.08 GB, the rest are the partial rows
+# of samples split over 4 warp tasks (written once, read once by reduce_partials_kernel)
+NCU_TRAFFIC_BYTES = 4003425000 + 317199616
+
+
 def work_per_hash(d):
     """algorithmic int32 ops per hash, d sign-accumulates + 20 per splitmix64."""
     return d + 20 * ((d + 63) // 64)
@@ -312,24 +318,28 @@ def main():
     hbm_peak, hbm_how = measured_peaks()
     alg_bytes = total * 8 + n * d * 4
     # Issued-instruction view, the one that cannot exceed 1: per (hash, 32 blocks) round a warp issues
-    # ALU_EQUIV instructions that need an ALU-pipe slot (5 LOP3 + 5 SHF of the mixer, 4.3 LOP3 of the
-    # carry-save tree, 2 IMAD.WIDE which also take an ALU slot -- SASS + profiles/r01b_kexp_issue_mix_and_variants.txt);
-    # the 16-lane ALU pipe takes one warp instruction every 2 clocks (= the live LOP3 peak below).
+    # ALU_EQUIV instructions that need an ALU-pipe slot: 12.9 on the ALU pipe itself (8.6 LOP3, 3.2 SHF, 1.1 other:
+    # per-opcode counts of profiles/r01c_project_kernel_ncu_full.txt) + 2 IMAD.WIDE, which displace one ALU slot
+    # each (profiles/r01b_kexp_issue_mix_and_variants.txt); the 16-lane ALU pipe takes one warp instruction every
+    # 2 clocks (= the live LOP3 peak below).
     nb = (d + 63) // 64
     lph = 32 if nb >= 32 else 1 << max(0, (nb - 1).bit_length())
     rounds = total * ((nb + 31) // 32) / (32 // lph)             # warp rounds of one launch
-    ALU_EQUIV = 16.3
+    ALU_EQUIV = 14.9
     alu_lane_ops = rounds * ALU_EQUIV * 32.0 / k_s
     alu_view = {"bound": "alu-pipe issue", "unit": "Tlane-op/s", "achieved": alu_lane_ops / 1e12,
                 "peak": peaks["lop3"] / 1e12, "frac": alu_lane_ops / peaks["lop3"],
                 "alu_equiv_warp_instr_per_round": ALU_EQUIV,
                 "how": "ALU-slot instructions of the inner loop (static SASS count) x rounds / kernel time, against the "
-                       "live LOP3-only issue peak; ncu (profiles/r01b_project_kernel_ncu_full.txt): pipe_alu 79.4 % + "
-                       "IMAD.WIDE slots, fmaheavy 63.5 %, xu 20.3 %, issue 72.6 %"}
+                       "live LOP3-only issue peak; ncu (profiles/r01c_project_kernel_ncu_full.txt): pipe_alu 74.0 % + "
+                       "IMAD.WIDE slots, fmaheavy 68.0 %, xu 23.3 %, issue 73.8 %"}
+    # DRAM bytes of one project_kernel launch from the committed ncu --set full capture of THIS workload
+    # (profiles/r01c_project_kernel_ncu_full.txt: dram__bytes_read.sum + dram__bytes_write.sum); other shapes: null
+    traffic = NCU_TRAFFIC_BYTES if (n, per, d) == (10000, 50000, 2048) else None
     roofline = {
         "bound": "int32-issue (ALU+FMA pipes); not hbm, not tensor -- see DESIGN.md",
         "achieved": achieved_ops / 1e12, "peak": p_int / 1e12, "unit": "Tint32op/s", "frac": achieved_ops / p_int,
-        "traffic": None,
+        "traffic": traffic,
         "work_per_hash_ops": w, "kernel_ms": g["kernel_ms"], "kernel_hashes_per_s": total / k_s,
         "peak_how": "live microbenchmark mvs_int_issue_peak(2): LOP3 (ALU pipe) and IMAD (FMA pipe) interleaved 1:1",
         "issue_peaks_Top_s": {k: v / 1e12 for k, v in peaks.items()},

@@ -132,6 +132,12 @@ void mvs_partition_samples(const uint64_t* offsets, int64_t n_samples, int n_par
 int mvs_sketch_file(mvs_ctx* const* ctxs, int n_ctx, const char* hash_file, const char* index_folder,
                     int d, int use_int16, uint64_t seed, int verbose);
 
+/* The CLI's entry: mvs_sketch_file with the contexts of devices[0..n_dev) created on a second host
+ * thread while the hash file is parsed (CUDA start-up overlaps the parse); the contexts are
+ * destroyed before returning.  Same results, same printed lines. */
+int mvs_sketch_file_on_devices(const int* devices, int n_dev, const char* hash_file, const char* index_folder,
+                               int d, int use_int16, uint64_t seed, int verbose);
+
 /* standalone_projection main (reference src/standalone_projection.cpp:11-46): one vector per
  * input line printed as floats separated by ' '.  out_path NULL = stdout. */
 int mvs_standalone_file(mvs_ctx* ctx, const char* hashes_file, int d, uint64_t seed, const char* out_path);

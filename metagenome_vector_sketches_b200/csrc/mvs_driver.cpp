@@ -63,13 +63,33 @@ inline uint64_t parse8(uint64_t w)
             (((w >> 16) & 0x000000FF000000FFull) * (1ull + (10000ull << 32)))) >> 32;
 }
 
+// high bit of every byte that is an ASCII digit
+inline uint64_t digit_mask8(uint64_t w)
+{
+    const uint64_t x = w & 0x7F7F7F7F7F7F7F7Full;
+    const uint64_t ge30 = x + 0x5050505050505050ull;                    // bit 7 set iff low 7 bits >= 0x30
+    const uint64_t ge3a = x + 0x4646464646464646ull;                    // bit 7 set iff low 7 bits >= 0x3a
+    return ge30 & ~ge3a & ~w & 0x8080808080808080ull;
+}
+
 uint64_t count_digit_runs(const char* b, const char* e)
 {
-    if (b >= e) return 0;
-    uint64_t n = is_digit(static_cast<unsigned char>(*b)) ? 1 : 0;
-    const unsigned char* u = reinterpret_cast<const unsigned char*>(b);
-    const size_t len = static_cast<size_t>(e - b);
-    for (size_t i = 1; i < len; ++i) n += static_cast<uint64_t>(is_digit(u[i]) & !is_digit(u[i - 1]));
+    uint64_t n = 0;
+    uint64_t prev = 0;                                                  // was the byte before p a digit (bit 7)
+    const char* p = b;
+    for (; p + 8 <= e; p += 8) {
+        uint64_t w;
+        std::memcpy(&w, p, 8);
+        const uint64_t dm = digit_mask8(w);
+        n += static_cast<uint64_t>(__builtin_popcountll(dm & ~((dm << 8) | prev)));   // digit whose predecessor is none
+        prev = dm >> 56;
+    }
+    bool pd = prev != 0;
+    for (; p < e; ++p) {
+        const bool dg = is_digit(static_cast<unsigned char>(*p));
+        n += static_cast<uint64_t>(dg & !pd);
+        pd = dg;
+    }
     return n;
 }
 
@@ -119,15 +139,38 @@ size_t parse_tokens(const char* p, const char* e, const char* safe_end, uint64_t
     return n;
 }
 
-// One line -> a set (sorted + unique unless it already was strictly increasing).
+// Drops repeated values in place keeping the first occurrence of each (unordered_set semantics; the
+// order inside a set does not matter to the projection, a sum).  Open addressing in a per-thread
+// table of >= 2n slots, ~10x cheaper than sort + unique for the 5e4-hash lines of config 2.
+size_t dedupe_first_occurrence(uint64_t* v, size_t n)
+{
+    static thread_local std::vector<uint64_t> table;
+    int lg = 4;
+    while ((size_t{1} << lg) < 2 * n) ++lg;
+    const size_t cap = size_t{1} << lg;
+    table.assign(cap, 0);                                               // 0 = empty; the value 0 is tracked apart
+    bool seen_zero = false;
+    size_t m = 0;
+    for (size_t i = 0; i < n; ++i) {
+        const uint64_t x = v[i];
+        if (x == 0) {
+            if (!seen_zero) { seen_zero = true; v[m++] = 0; }
+            continue;
+        }
+        size_t h = static_cast<size_t>((x * 0x9E3779B97F4A7C15ull) >> (64 - lg));
+        while (table[h] != 0 && table[h] != x) h = (h + 1) & (cap - 1);
+        if (table[h] == 0) { table[h] = x; v[m++] = x; }
+    }
+    return m;
+}
+
+// One line -> a set: already one if the tokens came strictly increasing (sourmash writes its mins
+// sorted), otherwise deduplicated.
 size_t parse_line_set(const char* b, const char* e, const char* safe_end, uint64_t* dst)
 {
     bool inc = true;
     size_t n = parse_tokens(b, e, safe_end, dst, &inc);
-    if (!inc) {                                                         // unordered_set semantics
-        std::sort(dst, dst + n);
-        n = static_cast<size_t>(std::unique(dst, dst + n) - dst);
-    }
+    if (!inc) n = dedupe_first_occurrence(dst, n);
     return n;
 }
 
@@ -182,7 +225,7 @@ void index_lines(const char* data, size_t size, int named, std::vector<LineRef>&
         }
     if (pos < size) add_line(data + pos, data + size);
     const int64_t n = static_cast<int64_t>(lines.size());
-#pragma omp parallel for schedule(dynamic, 1)
+#pragma omp parallel for schedule(dynamic, 4)
     for (int64_t i = 0; i < n; ++i) lines[static_cast<size_t>(i)].bound = count_digit_runs(lines[i].b, lines[i].e);
 }
 
@@ -255,7 +298,14 @@ void mvs_free_hash_batch(mvs_hash_batch* b)
     std::free(b);
 }
 
+static int parse_hash_file_impl(const char* path, int named, bool want_pinned, mvs_hash_batch** out);
+
 int mvs_parse_hash_file(const char* path, int named, mvs_hash_batch** out)
+{
+    return parse_hash_file_impl(path, named, true, out);
+}
+
+static int parse_hash_file_impl(const char* path, int named, bool want_pinned, mvs_hash_batch** out)
 {
     if (!path || !out) return MVS_ERR_INVALID_ARG;
     *out = nullptr;
@@ -263,8 +313,11 @@ int mvs_parse_hash_file(const char* path, int named, mvs_hash_batch** out)
     if (!mf.ok) return MVS_ERR_IO;
 
     // 1. line index + an upper bound of every line's token count (both parallel)
+    const bool timing = std::getenv("MVS_TIMING") != nullptr;
+    const auto tp0 = std::chrono::steady_clock::now();
     std::vector<LineRef> lines;
     index_lines(mf.data, mf.size, named, lines);
+    const auto tp1 = std::chrono::steady_clock::now();
     const int64_t n = static_cast<int64_t>(lines.size());
 
     mvs_hash_batch* b = static_cast<mvs_hash_batch*>(std::calloc(1, sizeof(mvs_hash_batch)));
@@ -278,9 +331,15 @@ int mvs_parse_hash_file(const char* path, int named, mvs_hash_batch** out)
         bound_total += lines[static_cast<size_t>(i)].bound;
     }
     b->offsets[n] = bound_total;
-    b->hashes = static_cast<uint64_t*>(host_alloc_any(sizeof(uint64_t) * (bound_total + 2), &b->hashes_pinned));
+    if (want_pinned) {
+        b->hashes = static_cast<uint64_t*>(host_alloc_any(sizeof(uint64_t) * (bound_total + 2), &b->hashes_pinned));
+    } else {                                     // pageable: no CUDA call, so a context can be created meanwhile
+        b->hashes_pinned = 0;
+        b->hashes = static_cast<uint64_t*>(std::malloc(sizeof(uint64_t) * (bound_total + 2)));
+    }
     if (!b->hashes) { mvs_free_hash_batch(b); return MVS_ERR_OOM; }
 
+    const auto tp2 = std::chrono::steady_clock::now();
     // 2. parse + dedupe every line straight into its slot of the (pinned) CSR payload
     std::vector<uint64_t> count(static_cast<size_t>(n ? n : 1));
     const char* safe_end = mf.data + mf.size;
@@ -290,6 +349,11 @@ int mvs_parse_hash_file(const char* path, int named, mvs_hash_batch** out)
         count[static_cast<size_t>(i)] = parse_line_set(ln.b, ln.e, safe_end, b->hashes + b->offsets[i]);
     }
 
+    const auto tp3 = std::chrono::steady_clock::now();
+    if (timing)
+        std::fprintf(stderr, "mvs_timing parse: index_s=%.4f alloc_s=%.4f tokens_s=%.4f threads=%d\n",
+                     std::chrono::duration<double>(tp1 - tp0).count(), std::chrono::duration<double>(tp2 - tp1).count(),
+                     std::chrono::duration<double>(tp3 - tp2).count(), omp_get_max_threads());
     // 3. close the gaps left by malformed / duplicated tokens (none for well-formed files)
     uint64_t total = 0;
     for (int64_t i = 0; i < n; ++i) {
@@ -384,28 +448,14 @@ void mvs_partition_samples(const uint64_t* offsets, int64_t n_samples, int n_par
     bounds[n_parts] = n_samples;
 }
 
-int mvs_sketch_file(mvs_ctx* const* ctxs, int n_ctx, const char* hash_file, const char* index_folder, int d,
-                    int use_int16, uint64_t seed, int verbose)
+// sketch() after the parse: project hb on the given contexts (one host thread each), print the
+// reference's lines, write db/.  t0 = start of the reference's timer (:255, includes the parse).
+static int sketch_parsed(mvs_ctx* const* ctxs, int n_ctx, mvs_hash_batch* hb, const std::string& dir, int d,
+                         int use_int16, uint64_t seed, int verbose, std::chrono::steady_clock::time_point t0,
+                         double parse_s, double wait_ctx_s)
 {
-    if (!ctxs || n_ctx <= 0 || !hash_file || !index_folder || d <= 0) return MVS_ERR_INVALID_ARG;
-    std::string dir(index_folder);
-    if (dir.empty() || dir.back() != '/') dir += '/';                   // :239-241
-    std::error_code ec;
-    if (fs::exists(dir, ec)) {                                          // :244-252 (wipes the folder)
-        for (const auto& entry : fs::directory_iterator(dir, ec)) fs::remove_all(entry.path(), ec);
-    } else {
-        fs::create_directories(dir, ec);
-    }
-    const auto t0 = std::chrono::steady_clock::now();                   // :255 timer includes the parse
-
-    mvs_hash_batch* hb = nullptr;
-    int rc = mvs_parse_hash_file(hash_file, 1, &hb);
-    if (rc != MVS_OK) {
-        std::fprintf(stderr, "Error opening %s for reading.\n", hash_file);   // :260
-        return rc;
-    }
-    if (verbose) std::printf("Loaded %lld hash sets from %s\n", static_cast<long long>(hb->n_samples), hash_file);
-
+    const auto t_start = std::chrono::steady_clock::now();
+    int rc = MVS_OK;
     const int64_t n = hb->n_samples;
     const size_t count = static_cast<size_t>(n) * static_cast<size_t>(d);
     int pin32 = 0, pin16 = 0;
@@ -441,13 +491,94 @@ int mvs_sketch_file(mvs_ctx* const* ctxs, int n_ctx, const char* hash_file, cons
                             static_cast<long long>(i));
         const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         std::printf("Time to compute all projected vectors: %g seconds\n", sec);   // :300-303
+        const auto t_projected = std::chrono::steady_clock::now();
         rc = mvs_write_db(dir.c_str(), n, d, hb->names, sumsq.data(), v32, v16);
+        if (std::getenv("MVS_TIMING")) {                                // stage split for tools/cli_bench.py
+            const auto t_written = std::chrono::steady_clock::now();
+            std::fprintf(stderr,
+                         "mvs_timing parse_s=%.6f wait_ctx_s=%.6f project_s=%.6f write_s=%.6f samples=%lld hashes=%llu\n",
+                         parse_s, wait_ctx_s, std::chrono::duration<double>(t_projected - t_start).count(),
+                         std::chrono::duration<double>(t_written - t_projected).count(), static_cast<long long>(n),
+                         static_cast<unsigned long long>(hb->n_hashes));
+        }
     } else {
         std::fprintf(stderr, "mvs: projection failed: %s\n", mvs_strerror(rc));
     }
     host_free_any(v32, pin32);
     host_free_any(v16, pin16);
+    return rc;
+}
+
+static std::string prepare_index_folder(const char* index_folder)
+{
+    std::string dir(index_folder);
+    if (dir.empty() || dir.back() != '/') dir += '/';                   // :239-241
+    std::error_code ec;
+    if (fs::exists(dir, ec)) {                                          // :244-252 (wipes the folder)
+        for (const auto& entry : fs::directory_iterator(dir, ec)) fs::remove_all(entry.path(), ec);
+    } else {
+        fs::create_directories(dir, ec);
+    }
+    return dir;
+}
+
+int mvs_sketch_file(mvs_ctx* const* ctxs, int n_ctx, const char* hash_file, const char* index_folder, int d,
+                    int use_int16, uint64_t seed, int verbose)
+{
+    if (!ctxs || n_ctx <= 0 || !hash_file || !index_folder || d <= 0) return MVS_ERR_INVALID_ARG;
+    const std::string dir = prepare_index_folder(index_folder);
+    const auto t0 = std::chrono::steady_clock::now();                   // :255 timer includes the parse
+    mvs_hash_batch* hb = nullptr;
+    int rc = mvs_parse_hash_file(hash_file, 1, &hb);
+    if (rc != MVS_OK) {
+        std::fprintf(stderr, "Error opening %s for reading.\n", hash_file);   // :260
+        return rc;
+    }
+    if (verbose) std::printf("Loaded %lld hash sets from %s\n", static_cast<long long>(hb->n_samples), hash_file);
+    const double parse_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    rc = sketch_parsed(ctxs, n_ctx, hb, dir, d, use_int16, seed, verbose, t0, parse_s, 0.0);
     mvs_free_hash_batch(hb);
+    return rc;
+}
+
+// The CLI's entry: same as mvs_sketch_file, but the contexts of `devices` are created on a second
+// host thread WHILE the hash file is parsed (CUDA start-up costs about a second on an 8-GPU host,
+// the parse of config 2's text about as much).  The parse then cannot use pinned memory (that needs
+// a context), so the payload is page-locked in place (cudaHostRegister) once the context is up.
+int mvs_sketch_file_on_devices(const int* devices, int n_dev, const char* hash_file, const char* index_folder, int d,
+                               int use_int16, uint64_t seed, int verbose)
+{
+    if (!devices || n_dev <= 0 || !hash_file || !index_folder || d <= 0) return MVS_ERR_INVALID_ARG;
+    std::vector<mvs_ctx*> ctxs(static_cast<size_t>(n_dev), nullptr);
+    int create_rc = MVS_OK;
+    std::thread creator([&] {
+        for (int k = 0; k < n_dev && create_rc == MVS_OK; ++k) create_rc = mvs_create(&ctxs[static_cast<size_t>(k)], devices[k]);
+    });
+    const auto t0 = std::chrono::steady_clock::now();
+    mvs_hash_batch* hb = nullptr;
+    int rc = parse_hash_file_impl(hash_file, 1, false, &hb);
+    const auto t1 = std::chrono::steady_clock::now();
+    creator.join();
+    const auto t2 = std::chrono::steady_clock::now();
+    if (rc != MVS_OK && create_rc == MVS_OK) {
+        std::fprintf(stderr, "Error opening %s for reading.\n", hash_file);   // :260
+        prepare_index_folder(index_folder);                            // the reference has wiped it by then
+    }
+    if (create_rc != MVS_OK) rc = create_rc;                            // no usable GPU: index_folder stays untouched
+    if (rc == MVS_OK) {
+        const std::string dir = prepare_index_folder(index_folder);    // the reference wipes it before the parse (:244)
+        if (verbose) std::printf("Loaded %lld hash sets from %s\n", static_cast<long long>(hb->n_samples), hash_file);
+        const auto t3 = std::chrono::steady_clock::now();
+        const int registered = hb->n_hashes ? mvs_host_register(hb->hashes, sizeof(uint64_t) * hb->n_hashes) : -1;
+        if (std::getenv("MVS_TIMING"))
+            std::fprintf(stderr, "mvs_timing host_register_s=%.6f\n",
+                         std::chrono::duration<double>(std::chrono::steady_clock::now() - t3).count());
+        rc = sketch_parsed(ctxs.data(), n_dev, hb, dir, d, use_int16, seed, verbose, t0,
+                           std::chrono::duration<double>(t1 - t0).count(), std::chrono::duration<double>(t2 - t1).count());
+        if (registered == MVS_OK) mvs_host_unregister(hb->hashes);
+    }
+    mvs_free_hash_batch(hb);
+    for (mvs_ctx* c : ctxs) mvs_destroy(c);
     return rc;
 }
 

@@ -115,20 +115,15 @@ int main(int argc, char** argv)
         input = tmp_hash_file;
     }
 
-    std::vector<mvs_ctx*> ctxs;
-    for (long long g = 0; g < gpus; ++g) {
-        mvs_ctx* c = nullptr;
-        const int rc = mvs_create(&c, static_cast<int>(g));
-        if (rc != MVS_OK) {
-            std::fprintf(stderr, "project_everything: cuda:%lld: %s\n", g, mvs_strerror(rc));
-            for (mvs_ctx* x : ctxs) mvs_destroy(x);
-            return 2;
-        }
-        ctxs.push_back(c);
+    std::vector<int> devices;
+    for (long long g = 0; g < gpus; ++g) devices.push_back(static_cast<int>(g));
+    // contexts are created while the hash file is parsed (CUDA start-up overlaps the parse)
+    const int rc = mvs_sketch_file_on_devices(devices.data(), static_cast<int>(devices.size()), input.c_str(),
+                                              output.c_str(), static_cast<int>(d), int16 ? 1 : 0, seed, quiet ? 0 : 1);
+    if (rc == MVS_ERR_NO_DEVICE) {                                              // index_folder was not touched
+        std::fprintf(stderr, "project_everything: %s\n", mvs_strerror(rc));
+        return 2;
     }
-    const int rc = mvs_sketch_file(ctxs.data(), static_cast<int>(ctxs.size()), input.c_str(), output.c_str(),
-                                   static_cast<int>(d), int16 ? 1 : 0, seed, quiet ? 0 : 1);
-    for (mvs_ctx* x : ctxs) mvs_destroy(x);
     if (rc != MVS_OK && rc != MVS_ERR_IO) {
         std::fprintf(stderr, "project_everything: %s\n", mvs_strerror(rc));
         return 2;

@@ -28,7 +28,12 @@ def parse_file(path, named):
     hashes = np.ctypeslib.as_array(b.hashes, shape=(max(1, int(b.n_hashes)),))[: int(b.n_hashes)].copy()
     names = [b.names[i].decode() for i in range(n)] if named else None
     lib.mvs_free_hash_batch(hb)
-    return 0, names, [hashes[int(off[i]):int(off[i + 1])] for i in range(n)]
+    # the order inside a set is free (first occurrences in file order; the projection is a sum):
+    # return every set sorted, after checking it holds no repeated value
+    sets = [hashes[int(off[i]):int(off[i + 1])] for i in range(n)]
+    for x in sets:
+        assert len(np.unique(x)) == len(x)
+    return 0, names, [np.sort(x) for x in sets]
 
 
 def test_parser_matches_reference_edge_cases(tmp_path):

@@ -1,0 +1,118 @@
+"""cli_bench.py -- wall-clock of the `project_everything sketch` CLI (parse + project + write db/) on a synthetic
+hash FILE, ours on the GPU next to the reference binary on the host cores (SURVEY 8d CPU baseline (ii)), and a
+byte comparison of the two vectors.bin on the reference's prefix.  Run on the GPU box:
+
+    python tools/cli_bench.py [--samples 2000] [--hashes 50000] [--ref-samples 64] [--d 2048] > gpurun_out/cli_bench.json
+
+The reference binary is oracle/_ref/{native|v3}/project_everything (the unmodified reference sources, built by
+oracle/Makefile); it is only timed and compared here, never linked into the product.  Tooling, not product."""
+import argparse
+import hashlib
+import json
+import os
+import re
+import shutil
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "metagenome_vector_sketches_b200", "bin", "project_everything")
+
+
+def sh(cmd, env=None):
+    t = time.perf_counter()
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env)
+    return time.perf_counter() - t, r
+
+
+def ref_binary():
+    for tag in ("native", "v3"):
+        p = os.path.join(ROOT, "oracle", "_ref", tag, "project_everything")
+        if os.path.exists(p):
+            r = subprocess.run([p], capture_output=True)          # usage + exit 1 when the ISA is runnable
+            if r.returncode in (0, 1):
+                return p, tag
+    return None, None
+
+
+def sha(path):
+    h = hashlib.sha256()
+    with open(path, "rb") as f:
+        for blk in iter(lambda: f.read(1 << 24), b""):
+            h.update(blk)
+    return h.hexdigest()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--samples", type=int, default=2000)
+    ap.add_argument("--hashes", type=int, default=50000)
+    ap.add_argument("--ref-samples", type=int, default=64)
+    ap.add_argument("--d", type=int, default=2048)
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--work", default="/tmp/mvs_cli_bench")
+    a = ap.parse_args()
+    os.makedirs(a.work, exist_ok=True)
+    gen = os.path.join(a.work, "gen_hash_file")
+    subprocess.check_call(["g++", "-O2", "-fopenmp", "-o", gen, os.path.join(ROOT, "tools", "gen_hash_file.cpp")])
+    full = os.path.join(a.work, "full.txt")
+    pref = os.path.join(a.work, "prefix.txt")
+    subprocess.check_call([gen, full, str(a.samples), str(a.hashes)])
+    subprocess.check_call([gen, pref, str(a.ref_samples), str(a.hashes)])   # same generator: the first samples of `full`
+    out = {"workload": "%d samples x %d hashes (mvs-synth-v1), d=%d, text hash file %.2f GB" % (
+        a.samples, a.hashes, a.d, os.path.getsize(full) / 1e9), "host_cores": os.cpu_count()}
+
+    env = dict(os.environ, MVS_TIMING="1")
+    runs = []
+    for rep in range(3):                          # rep 0 includes CUDA context creation on a cold driver
+        db = os.path.join(a.work, "db_ours/")
+        wall, r = sh([BIN, "sketch", full, db, "-d", str(a.d), "--quiet", "--gpus", str(a.gpus)], env)
+        kv = dict(re.findall(r"(\w+)=([0-9.]+)", r.stderr))
+        if r.returncode != 0 or "project_s" not in kv:
+            out["error"] = (r.stdout + r.stderr)[-400:]
+            print(json.dumps(out))
+            return 1
+        runs.append({"wall_s": wall, "parse_s": float(kv["parse_s"]), "wait_cuda_context_s": float(kv["wait_ctx_s"]),
+                     "host_register_s": float(kv.get("host_register_s", 0)), "project_s": float(kv["project_s"]),
+                     "write_s": float(kv["write_s"]), "parse_index_s": float(kv.get("index_s", 0)),
+                     "parse_tokens_s": float(kv.get("tokens_s", 0))})
+        n_hashes = int(kv["hashes"])
+    best = min(runs, key=lambda x: x["wall_s"])
+    out["ours"] = {"runs": runs, "best_wall_s": best["wall_s"], "hashes": n_hashes,
+                   "hashes_per_s_wall": n_hashes / best["wall_s"],
+                   "hashes_per_s_parse_project_write": n_hashes / (best["parse_s"] + best["host_register_s"] +
+                                                                   best["project_s"] + best["write_s"]),
+                   "note": "wall includes process start and CUDA context creation (overlapped with the parse; the "
+                           "remainder is wait_cuda_context_s), which the second figure leaves out",
+                   "text_GB_per_s_parse": os.path.getsize(full) / 1e9 / best["parse_s"], "gpus": a.gpus}
+
+    # parity on the prefix: ours vs the reference CLI, same file
+    dbp = os.path.join(a.work, "db_ours_prefix/")
+    sh([BIN, "sketch", pref, dbp, "-d", str(a.d), "--quiet"])
+    refbin, tag = ref_binary()
+    if refbin:
+        dbr = os.path.join(a.work, "db_ref_prefix/")
+        env_ref = dict(os.environ, OMP_NUM_THREADS=str(os.cpu_count()))
+        wall, r = sh([refbin, "sketch", pref, dbr, "-d", str(a.d)], env_ref)
+        m = re.search(r"Time to compute all projected vectors: (\S+) seconds", r.stdout)
+        ref_hashes = a.ref_samples * a.hashes
+        out["reference"] = {"binary": "oracle/_ref/%s/project_everything" % tag, "threads": os.cpu_count(),
+                            "samples": a.ref_samples, "wall_s": wall,
+                            "reported_projection_s": float(m.group(1)) if m else None,
+                            "hashes_per_s_wall": ref_hashes / wall}
+        same = sha(dbp + "vectors.bin") == sha(dbr + "vectors.bin")
+        out["parity"] = {"vectors_bin_identical_on_prefix": same,
+                         "dimension_txt_identical": open(dbp + "dimension.txt").read() == open(dbr + "dimension.txt").read(),
+                         "names_identical": [l.rsplit(" ", 1)[0] for l in open(dbp + "vector_norms.txt")] ==
+                                            [l.rsplit(" ", 1)[0] for l in open(dbr + "vector_norms.txt")]}
+        out["speedup_wall_per_hash"] = out["ours"]["hashes_per_s_wall"] / out["reference"]["hashes_per_s_wall"]
+    else:
+        out["reference"] = {"unavailable": "oracle/_ref not built"}
+    print(json.dumps(out))
+    shutil.rmtree(a.work, ignore_errors=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
