@@ -551,8 +551,15 @@ int mvs_sketch_file_on_devices(const int* devices, int n_dev, const char* hash_f
     if (!devices || n_dev <= 0 || !hash_file || !index_folder || d <= 0) return MVS_ERR_INVALID_ARG;
     std::vector<mvs_ctx*> ctxs(static_cast<size_t>(n_dev), nullptr);
     int create_rc = MVS_OK;
-    std::thread creator([&] {
-        for (int k = 0; k < n_dev && create_rc == MVS_OK; ++k) create_rc = mvs_create(&ctxs[static_cast<size_t>(k)], devices[k]);
+    std::vector<int> create_rcs(static_cast<size_t>(n_dev), MVS_OK);
+    std::thread creator([&] {                                          // one creating thread per device
+        std::vector<std::thread> th;
+        for (int k = 1; k < n_dev; ++k)
+            th.emplace_back([&, k] { create_rcs[static_cast<size_t>(k)] = mvs_create(&ctxs[static_cast<size_t>(k)], devices[k]); });
+        create_rcs[0] = mvs_create(&ctxs[0], devices[0]);
+        for (auto& t : th) t.join();
+        for (int r : create_rcs)
+            if (r != MVS_OK && create_rc == MVS_OK) create_rc = r;
     });
     const auto t0 = std::chrono::steady_clock::now();
     mvs_hash_batch* hb = nullptr;
