@@ -157,6 +157,37 @@ void mvs_host_free(void* p);
 int mvs_host_register(void* p, size_t bytes);       /* pin caller-owned memory */
 int mvs_host_unregister(void* p);
 
+/* ---- all-pairs comparison of projected vectors --------------------
+ * Replaces compute_sparse_dot_products_optimized (reference src/pairwise_comp_optimized.cpp:57-160)
+ * and the block loops of its main (:949-983).  dot(i, j) = sum_k a[i][k] * b[j][k] in int32
+ * arithmetic (modulo 2^32, as the reference's Eigen MatrixXi product); a pair is kept iff
+ * (int64)dot / d > 0.05 * (norms_i[i] + norms_j[j]) with truncating integer division (:140-143);
+ * norms are SQUARED norms as the reference holds them (:895-901).  Kept pairs are returned sorted
+ * by (row, col) -- the order of the reference's double loop -- in a library-allocated result. */
+typedef struct mvs_sparse_result {
+    int64_t n;             /* kept pairs */
+    int32_t* rows;         /* n row indices (block-relative for _block, global for _shard) */
+    int32_t* cols;         /* n column indices */
+    int64_t* values;       /* n dot products (the wrapped int32 value, widened) */
+    double gemm_ms;        /* CUDA-event time of the dot-product kernel(s) */
+    double filter_ms;      /* CUDA-event time of threshold + count + scan + emit */
+    double wall_ms;        /* host wall clock of the call, copies included */
+    uint64_t h2d_bytes, d2h_bytes;
+} mvs_sparse_result;
+
+/* One block pair, host buffers in row-major [m x d] (the memory image of the reference's d x m
+ * column-major MatrixXi blocks).  Same argument meaning as the reference function. */
+int mvs_pairwise_block(mvs_ctx* ctx, const int32_t* block_i, int64_t mi, const int32_t* block_j, int64_t mj,
+                       int d, const double* norms_i, const double* norms_j, mvs_sparse_result** out);
+
+/* Rows [begin_row, end_row) of a db against all n_total vectors (one shard of the reference's main,
+ * :936-983): vectors = the int32 image of vectors.bin, norms_sq[n_total].  The db is uploaded once
+ * and stays resident in HBM; indices in the result are global. */
+int mvs_pairwise_shard(mvs_ctx* ctx, const int32_t* vectors, int64_t n_total, int d, const double* norms_sq,
+                       int64_t begin_row, int64_t end_row, mvs_sparse_result** out);
+
+void mvs_free_sparse_result(mvs_sparse_result* r);
+
 /* ---- measurement ------------------------------------------------------------------ */
 typedef struct mvs_timing {
     float kernel_ms;       /* mean CUDA-event time (on the launching stream) of the projection +

@@ -59,6 +59,11 @@ SIGNATURES = {
                                   C.c_uint64, C.c_int]),
     "mvs_sketch_file_on_devices": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.c_char_p, C.c_char_p, C.c_int, C.c_int,
                                              C.c_uint64, C.c_int]),
+    "mvs_pairwise_block": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int, C.c_void_p,
+                                     C.c_void_p, C.c_void_p]),
+    "mvs_pairwise_shard": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_int64,
+                                     C.c_void_p]),
+    "mvs_free_sparse_result": (None, [C.c_void_p]),
     "mvs_standalone_file": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_uint64, C.c_char_p]),
     "mvs_convert_signatures": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int, C.c_int]),
     "mvs_sort_unique": (C.c_int64, [C.c_void_p, C.c_int64]),

@@ -10,6 +10,7 @@
 // device is missing or a launch fails the call returns an error.
 #include "../../include/mvs_b200.h"
 #include "mvs_kernels.cuh"
+#include "mvs_internal.h"
 
 #include <algorithm>
 #include <cstdio>
@@ -349,6 +350,13 @@ const char* mvs_strerror(int status)
 }
 
 int mvs_last_cuda_error(const mvs_ctx* ctx) { return ctx ? ctx->last_cuda : 0; }
+
+}  // extern "C"  (the internal accessors of mvs_internal.h have C++ linkage)
+int mvs_internal_device(const mvs_ctx* ctx) { return ctx->device; }
+cudaStream_t mvs_internal_stream(mvs_ctx* ctx) { return ctx->slots[0].stream; }
+void mvs_internal_set_cuda_error(mvs_ctx* ctx, cudaError_t e) { ctx->last_cuda = static_cast<int>(e); }
+void mvs_internal_count_launches(mvs_ctx* ctx, uint64_t n) { ctx->launches += n; }
+extern "C" {
 
 int mvs_create(mvs_ctx** out, int device)
 {

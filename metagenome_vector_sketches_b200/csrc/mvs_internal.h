@@ -1,0 +1,12 @@
+// mvs_internal.h -- what the other translation units of libmvs_b200.so may use of a context
+// (the struct itself stays private to mvs_capi.cu).  Not part of the C ABI.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+struct mvs_ctx;
+
+int mvs_internal_device(const mvs_ctx* ctx);
+cudaStream_t mvs_internal_stream(mvs_ctx* ctx);                  // the stream of slot 0
+void mvs_internal_set_cuda_error(mvs_ctx* ctx, cudaError_t e);
+void mvs_internal_count_launches(mvs_ctx* ctx, uint64_t n);

@@ -96,3 +96,45 @@ uint64_t oracle_sumsq(const int32_t *v, int d)
     for (int i = 0; i < d; ++i) ss += (uint64_t)((int64_t)v[i] * (int64_t)v[i]);
     return ss;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * Pairwise comparison of projected vectors:
+ *   compute_sparse_dot_products_optimized   /root/reference/src/pairwise_comp_optimized.cpp:57-160
+ * The live code is :135-147: an Eigen MatrixXi product (int32 multiply-add, i.e. arithmetic
+ * modulo 2^32 reinterpreted as int32), then for every (i, j) in row-major order
+ *   threshold = 0.05 * (norms_i(i) + norms_j(j))          (norms are squared norms, double)
+ *   keep (i, j, dot) iff  (int64)dot / dimension > threshold   (integer division, truncating)
+ * Blocks are row-major [m x d] (the memory layout of the reference's column-major d x m block).
+ * Returns the number of kept pairs; writes at most cap of them.
+ * ------------------------------------------------------------------------------------------ */
+int64_t oracle_pairwise_block(const int32_t *block_i, int64_t mi, const int32_t *block_j, int64_t mj, int d,
+                              const double *norms_i, const double *norms_j,
+                              int32_t *rows, int32_t *cols, int64_t *values, int64_t cap)
+{
+    int64_t n = 0;
+    for (int64_t i = 0; i < mi; ++i) {
+        for (int64_t j = 0; j < mj; ++j) {
+            uint32_t acc = 0;                                  /* int32 wraparound, well defined */
+            const int32_t *a = block_i + i * (int64_t)d, *b = block_j + j * (int64_t)d;
+            for (int k = 0; k < d; ++k) acc += (uint32_t)a[k] * (uint32_t)b[k];
+            const int64_t dot_product = (int64_t)(int32_t)acc;
+            const double threshold = 0.05 * (norms_i[i] + norms_j[j]);
+            if (dot_product / d > threshold) {
+                if (n < cap) { rows[n] = (int32_t)i; cols[n] = (int32_t)j; values[n] = dot_product; }
+                ++n;
+            }
+        }
+    }
+    return n;
+}
+
+/* Jaccard estimate and its 8-bit quantisation as stored in shard_k/matrix.bin
+ *   /root/reference/src/pairwise_comp_optimized.cpp:654-665 */
+uint16_t oracle_quantize_jaccard(int64_t value, int d, double norm_row, double norm_col)
+{
+    const double MULT_CONST = 255.0;
+    double inter = (double)value / d;
+    double jaccard = inter / (norm_row + norm_col - inter);
+    if (jaccard > 1) jaccard = 1;
+    return (uint16_t)round(jaccard * MULT_CONST);
+}

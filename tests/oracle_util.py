@@ -131,3 +131,69 @@ def parse_line_like_reference(text):
             break
         out.append((-v) & 0xFFFFFFFFFFFFFFFF if neg else v)
     return out
+
+
+# ---- pairwise comparison (reference src/pairwise_comp_optimized.cpp:57-160) ----
+_ref_pw = None
+
+
+def _pairwise_call(fn, a, b, d, ni, nj, with_seconds):
+    a = np.ascontiguousarray(a, dtype=np.int32)
+    b = np.ascontiguousarray(b, dtype=np.int32)
+    ni = np.ascontiguousarray(ni, dtype=np.float64)
+    nj = np.ascontiguousarray(nj, dtype=np.float64)
+    mi, mj = a.shape[0], b.shape[0]
+    cap = mi * mj
+    rows = np.empty(cap, dtype=np.int32)
+    cols = np.empty(cap, dtype=np.int32)
+    vals = np.empty(cap, dtype=np.int64)
+    args = [a.ctypes.data, mi, b.ctypes.data, mj, d, ni.ctypes.data, nj.ctypes.data, rows.ctypes.data,
+            cols.ctypes.data, vals.ctypes.data, cap]
+    sec = C.c_double(0)
+    if with_seconds:
+        args.append(C.byref(sec))
+    n = fn(*args)
+    return rows[:n].copy(), cols[:n].copy(), vals[:n].copy(), sec.value
+
+
+def oracle_pairwise(a, b, d, ni, nj):
+    lib = oracle()
+    lib.oracle_pairwise_block.restype = C.c_int64
+    lib.oracle_pairwise_block.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int, C.c_void_p,
+                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+    return _pairwise_call(lib.oracle_pairwise_block, a, b, d, ni, nj, False)[:3]
+
+
+def oracle_quantize_jaccard(value, d, norm_row, norm_col):
+    lib = oracle()
+    lib.oracle_quantize_jaccard.restype = C.c_uint16
+    lib.oracle_quantize_jaccard.argtypes = [C.c_int64, C.c_int, C.c_double, C.c_double]
+    return int(lib.oracle_quantize_jaccard(int(value), int(d), float(norm_row), float(norm_col)))
+
+
+def ref_pairwise_lib():
+    """The unmodified reference function behind oracle/ref_pairwise_shim.cpp, or None if not built."""
+    global _ref_pw
+    if _ref_pw is None:
+        d = ref_dir()
+        if d is None or not os.path.exists(os.path.join(d, "libref_pairwise.so")):
+            return None
+        lib = C.CDLL(os.path.join(d, "libref_pairwise.so"))
+        lib.ref_pairwise_block.restype = C.c_int64
+        lib.ref_pairwise_block.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int, C.c_void_p,
+                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                           C.POINTER(C.c_double)]
+        _ref_pw = lib
+    return _ref_pw
+
+
+def ref_pairwise(a, b, d, ni, nj):
+    return _pairwise_call(ref_pairwise_lib().ref_pairwise_block, a, b, d, ni, nj, True)
+
+
+def norms_sq_like_reference(vectors, d):
+    """all_norms of pairwise_comp_optimized.cpp:889-901: the norm PRINTED by sketch() with 6 significant
+    digits (project_everything.cpp:327-330), parsed back with stod and squared."""
+    v = np.asarray(vectors, dtype=np.float64)
+    norm = np.sqrt((v * v).sum(axis=1) / float(d))
+    return np.array([float("%g" % x) ** 2 for x in norm], dtype=np.float64)

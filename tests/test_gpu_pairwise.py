@@ -1,0 +1,117 @@
+"""GPU parity of the all-pairs comparison through the C ABI, against the oracle
+(oracle/mvs_oracle.c oracle_pairwise_block, pinned to the reference function by tests/test_oracle.py)
+and, where the compiled reference travels with the repo, against the reference function itself.
+Bit-exact: dot products are int32 arithmetic modulo 2^32, the keep-test is integer division + one
+double comparison, the order is the reference's (row, col) loop order."""
+import numpy as np
+import pytest
+
+import metagenome_vector_sketches_b200 as mvs
+from metagenome_vector_sketches_b200 import pairwise as pw
+from oracle_util import (load_toy_ref, norms_sq_like_reference, oracle_pairwise, ref_pairwise, ref_pairwise_lib)
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def sk():
+    s = mvs.Sketcher(0)
+    yield s
+    s.close()
+
+
+def same(got, want):
+    return all(np.array_equal(a, b) for a, b in zip(got[:3], want[:3]))
+
+
+def toy():
+    ref = load_toy_ref("d2048")
+    v = ref["vectors"].reshape(-1, 2048)
+    return v, pw.norms_squared_from_db(ref["norms_txt"].strip().split("\n"))
+
+
+def test_toy_db_pairs_match_oracle_and_reference(sk):
+    v, nrm = toy()
+    got = pw.compute_sparse_dot_products(sk, v, v, nrm, nrm)
+    want = oracle_pairwise(v, v, 2048, nrm, nrm)
+    assert len(want[0]) == 1291 and same(got, want)
+    if ref_pairwise_lib() is not None:
+        assert same(got, ref_pairwise(v, v, 2048, nrm, nrm))
+    sh = pw.pairwise_shard(sk, v, nrm)
+    assert same(sh, want)
+    part = pw.pairwise_shard(sk, v, nrm, 20, 45)                       # a shard of rows: global indices
+    keep = (want[0] >= 20) & (want[0] < 45)
+    assert same(part, [w[keep] for w in want])
+
+
+@pytest.mark.parametrize("mi,mj,d", [(1, 1, 1), (3, 5, 7), (37, 53, 300), (128, 128, 64), (129, 127, 2048),
+                                     (200, 333, 100), (257, 1, 4096), (64, 300, 18)])
+def test_ragged_blocks_all_dimensions(sk, mi, mj, d):
+    rng = np.random.default_rng(mi * 1000 + mj + d)
+    a = rng.integers(-60, 61, (mi, d), dtype=np.int64).astype(np.int32)
+    b = rng.integers(-60, 61, (mj, d), dtype=np.int64).astype(np.int32)
+    k = min(mi, mj) // 2
+    b[:k] = a[:k]                                                      # related vectors pass the threshold
+    if k > 2:
+        b[1] = -a[1]
+        b[2] = a[2] // 2
+    ni, nj = norms_sq_like_reference(a, d), norms_sq_like_reference(b, d)
+    got = pw.compute_sparse_dot_products(sk, a, b, ni, nj)
+    assert same(got, oracle_pairwise(a, b, d, ni, nj))
+
+
+def test_int32_wraparound_is_the_references(sk):
+    """Eigen's MatrixXi product wraps modulo 2^32; with tiny norms every positive wrapped value is kept,
+    so the triples expose the wrapped dot products themselves."""
+    rng = np.random.default_rng(5)
+    for scale in (40000, 2 ** 20, 2 ** 31 - 1):
+        a = rng.integers(-scale, scale + 1, (70, 96), dtype=np.int64).astype(np.int32)
+        b = rng.integers(-scale, scale + 1, (45, 96), dtype=np.int64).astype(np.int32)
+        a[0] = np.int32(-2 ** 31)
+        ni, nj = np.zeros(70), np.zeros(45)
+        got = pw.compute_sparse_dot_products(sk, a, b, ni, nj)
+        want = oracle_pairwise(a, b, 96, ni, nj)
+        assert len(want[0]) > 500 and same(got, want)
+        if ref_pairwise_lib() is not None:
+            assert same(got, ref_pairwise(a, b, 96, ni, nj))
+
+
+def test_threshold_edges_and_negative_quotients(sk):
+    # dot / d truncates toward zero: -1 / 8 == 0 > threshold only if threshold < 0 (negative "norms")
+    a = np.array([[1, 0, 0, 0, 0, 0, 0, 0], [8, 0, 0, 0, 0, 0, 0, 0], [-1, 0, 0, 0, 0, 0, 0, 0]], dtype=np.int32)
+    b = np.array([[1, 0, 0, 0, 0, 0, 0, 0], [7, 0, 0, 0, 0, 0, 0, 0], [9, 0, 0, 0, 0, 0, 0, 0]], dtype=np.int32)
+    for ni, nj in ((np.zeros(3), np.zeros(3)), (np.full(3, -1.0), np.zeros(3)), (np.full(3, 10.0), np.full(3, 10.0)),
+                   (np.array([0.0, 20.0, 0.0]), np.array([0.0, 0.0, 100.0]))):
+        got = pw.compute_sparse_dot_products(sk, a, b, ni, nj)
+        assert same(got, oracle_pairwise(a, b, 8, ni, nj))
+
+
+def test_empty_blocks_and_errors(sk):
+    z = np.zeros((0, 16), dtype=np.int32)
+    v = np.ones((4, 16), dtype=np.int32)
+    assert len(pw.compute_sparse_dot_products(sk, z, v, np.zeros(0), np.zeros(4)).rows) == 0
+    assert len(pw.compute_sparse_dot_products(sk, v, z, np.zeros(4), np.zeros(0)).rows) == 0
+    assert len(pw.pairwise_shard(sk, v, np.zeros(4), 2, 2).rows) == 0
+    with pytest.raises(mvs.MvsError):
+        pw.pairwise_shard(sk, v, np.zeros(4), 3, 9)
+    with pytest.raises(ValueError):
+        pw.compute_sparse_dot_products(sk, v, np.ones((4, 8), dtype=np.int32), np.zeros(4), np.zeros(4))
+
+
+def test_shard_of_projected_synthetic_db_matches_blockwise_oracle(sk):
+    """End to end on our own projection output: 600 samples in 30 families sharing most hashes (so that
+    neighbours exist), d = 2048; the shard call (several GEMM row blocks) equals the oracle."""
+    rng = np.random.default_rng(11)
+    fams = [rng.integers(0, 2 ** 54, 3000, dtype=np.uint64) for _ in range(30)]
+    sets = []
+    for s in range(600):
+        base = fams[s % 30]
+        keepn = int(rng.integers(1500, 3000))
+        extra = rng.integers(0, 2 ** 54, int(rng.integers(10, 800)), dtype=np.uint64)
+        sets.append(np.unique(np.concatenate([base[:keepn], extra])))
+    vec = sk.project_sets(sets, 2048)
+    nrm = norms_sq_like_reference(vec, 2048)
+    got = pw.pairwise_shard(sk, vec, nrm)
+    want = oracle_pairwise(vec, vec, 2048, nrm, nrm)
+    assert len(want[0]) > 600 * 5 and same(got, want)
+    assert got.gemm_ms > 0 and got.h2d_bytes == vec.nbytes + 8 * 600

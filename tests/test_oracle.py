@@ -102,3 +102,63 @@ def test_live_reference_if_built():
     for n, d in [(0, 64), (1, 1), (17, 63), (500, 2048), (1000, 130), (3, 4160)]:
         h = np.unique(rng.integers(0, 2 ** 64 - 1, n, dtype=np.uint64))
         assert np.array_equal(ref_set(h, d), oracle_set(h, d))
+
+
+# ---- pairwise comparison: oracle pinned to the reference function ----------------
+def _pairwise_cases():
+    import importlib.util
+    import os
+    from oracle_util import GOLDEN
+    spec = importlib.util.spec_from_file_location("mgp", os.path.join(GOLDEN, "make_golden_pairwise.py"))
+    mgp = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mgp)
+    z = np.load(os.path.join(GOLDEN, "pairwise_ref.npz"))
+    return mgp, z
+
+
+def test_pairwise_oracle_matches_reference_goldens():
+    from oracle_util import load_toy_ref, oracle_pairwise
+    mgp, z = _pairwise_cases()
+    ref = load_toy_ref("d2048")
+    v = ref["vectors"].reshape(-1, 2048)
+    nrm = np.array([float(l.rsplit(" ", 1)[1]) ** 2 for l in ref["norms_txt"].strip().split("\n")])
+    r, c, val = oracle_pairwise(v, v, 2048, nrm, nrm)
+    assert len(r) == 1291
+    assert np.array_equal(r, z["toy_rows"]) and np.array_equal(c, z["toy_cols"]) and np.array_equal(val, z["toy_values"])
+    for k, (seed, mi, mj, d, scale, zn) in enumerate(z["specs"].tolist()):
+        a, b, ni, nj = mgp.random_case(seed, mi, mj, d, scale, bool(zn))
+        r, c, val = oracle_pairwise(a, b, d, ni, nj)
+        assert len(r) > 0
+        assert np.array_equal(r, z["r%d_rows" % k]) and np.array_equal(c, z["r%d_cols" % k])
+        assert np.array_equal(val, z["r%d_values" % k])
+
+
+def test_pairwise_oracle_matches_live_reference_if_built():
+    from oracle_util import oracle_pairwise, ref_pairwise, ref_pairwise_lib, norms_sq_like_reference
+    if ref_pairwise_lib() is None:
+        pytest.skip("oracle/_ref/*/libref_pairwise.so not built")
+    rng = np.random.default_rng(3)
+    for mi, mj, d, scale in ((20, 31, 64, 100), (50, 50, 130, 3000), (33, 17, 48, 2 ** 31 - 1)):
+        a = rng.integers(-scale, scale + 1, (mi, d), dtype=np.int64).astype(np.int32)
+        b = rng.integers(-scale, scale + 1, (mj, d), dtype=np.int64).astype(np.int32)
+        b[:10] = a[:10]
+        for ni, nj in ((norms_sq_like_reference(a, d), norms_sq_like_reference(b, d)), (np.zeros(mi), np.zeros(mj))):
+            want = ref_pairwise(a, b, d, np.nan_to_num(ni), np.nan_to_num(nj))
+            got = oracle_pairwise(a, b, d, np.nan_to_num(ni), np.nan_to_num(nj))
+            assert all(np.array_equal(x, y) for x, y in zip(got, want[:3]))
+
+
+def test_jaccard_quantisation_matches_query_goldens():
+    """pairwise_comp_optimized.cpp:654-665 on the toy db reproduces the 8-bit values behind KAT-4
+    (tests/golden/pairwise_top10.json: DRR000821 vs DRR000822 -> 0.317647 = 81/255)."""
+    from oracle_util import load_toy, load_toy_ref, oracle_quantize_jaccard
+    names, _, _ = load_toy()
+    z = np.load(__import__("os").path.join(__import__("oracle_util").GOLDEN, "pairwise_ref.npz"))
+    ref = load_toy_ref("d2048")
+    nrm = np.array([float(l.rsplit(" ", 1)[1]) ** 2 for l in ref["norms_txt"].strip().split("\n")])
+    i, j = names.index("DRR000821"), names.index("DRR000822")
+    k = np.flatnonzero((z["toy_rows"] == i) & (z["toy_cols"] == j))
+    assert len(k) == 1
+    q = oracle_quantize_jaccard(int(z["toy_values"][k[0]]), 2048, nrm[i], nrm[j])
+    assert q == 81 and abs(q / 255.0 - 0.317647) < 1e-6
+    assert oracle_quantize_jaccard(int(z["toy_values"][(z["toy_rows"] == i) & (z["toy_cols"] == i)][0]), 2048, nrm[i], nrm[i]) == 255
