@@ -171,6 +171,7 @@ typedef struct mvs_sparse_result {
     int64_t* values;       /* n dot products (the wrapped int32 value, widened) */
     double gemm_ms;        /* CUDA-event time of the dot-product kernel(s) */
     double filter_ms;      /* CUDA-event time of threshold + count + scan + emit */
+    double prep_ms;        /* host wall time of the operand preparation (min/max + int8 limb planes) */
     double wall_ms;        /* host wall clock of the call, copies included */
     uint64_t h2d_bytes, d2h_bytes;
 } mvs_sparse_result;
@@ -211,7 +212,9 @@ int mvs_get_timing(mvs_ctx* ctx, mvs_timing* t);    /* synchronises the context'
  *        IMAD.WIDE + one LOP3 per counted op). */
 int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second);
 
-/* Kernel tuning knobs for experiments (0 = default).  Unknown keys are ignored. */
+/* Kernel tuning knobs for experiments (0 = default).  Unknown keys are ignored.
+ * "pairwise_path": 0 = tensor-core limb GEMM (default), 1 = IMAD GEMM; "pairwise_limbs": 0 = from the data,
+ * 1..4 = use at least that many base-256 limbs (both paths are exact; the knobs exist for the parity tests). */
 int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value);
 
 #ifdef __cplusplus

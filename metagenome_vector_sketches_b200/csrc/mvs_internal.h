@@ -10,3 +10,5 @@ int mvs_internal_device(const mvs_ctx* ctx);
 cudaStream_t mvs_internal_stream(mvs_ctx* ctx);                  // the stream of slot 0
 void mvs_internal_set_cuda_error(mvs_ctx* ctx, cudaError_t e);
 void mvs_internal_count_launches(mvs_ctx* ctx, uint64_t n);
+int mvs_internal_pairwise_path(const mvs_ctx* ctx);               // option "pairwise_path"
+int mvs_internal_pairwise_limbs(const mvs_ctx* ctx);              // option "pairwise_limbs"

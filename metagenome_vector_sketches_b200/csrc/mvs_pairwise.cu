@@ -17,9 +17,15 @@ namespace {
 
 struct Dev {                                     // device allocation freed on scope exit
     void* p = nullptr;
-    ~Dev() { if (p) cudaFree(p); }
+    ~Dev() { release(); }
+    void release() { if (p) cudaFree(p); p = nullptr; }
     cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 16); }
     template <typename T> T* as() const { return static_cast<T*>(p); }
+};
+
+struct OutBuf {                                  // device triples of one row block, reused across blocks
+    Dev rows, cols, vals;
+    unsigned long long cap = 0;
 };
 
 struct Triples {
@@ -37,12 +43,76 @@ struct Triples {
         }                                                                     \
     } while (0)
 
-// One block of rows against one block of columns, all operands resident in HBM.  Appends the kept
-// triples (row_base + i, col_base + j, dot) in (i, j) order to `out`; adds the CUDA-event times.
-int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const int32_t* d_A, int64_t mi, const int32_t* d_B, int64_t mj, int d,
-                  const double* d_ni, const double* d_nj, int32_t row_base, int32_t col_base, int32_t* d_C,
-                  unsigned long long* d_counts, Triples& out, double& gemm_ms, double& filter_ms, uint64_t& d2h_bytes)
+// An int32 operand matrix resident in HBM, plus (tensor-core path) its int8 limb planes.
+struct Operand {
+    const int32_t* v = nullptr;                  // [n x d] int32
+    int64_t n = 0;
+    Dev planes;                                  // [P][n_pad x k_pad] int8
+    int P = 0;
+    int64_t n_pad = 0;
+    int k_pad = 0;
+};
+
+// limbs needed so that every value in [lo, hi] is a sum of P balanced base-256 digits (P = 4 covers int32 mod 2^32)
+int limbs_for_range(int lo, int hi)
 {
+    long long top = 0;                           // (256^P - 1) / 255
+    for (int P = 1; P <= 3; ++P) {
+        top = top * 256 + 1;
+        if (static_cast<long long>(lo) >= -128 * top && static_cast<long long>(hi) <= 127 * top) return P;
+    }
+    return 4;
+}
+
+int prepare_operand(mvs_ctx* ctx, cudaStream_t st, Operand& op, int d, int* d_mm)
+{
+    const int init[2] = {2147483647, -2147483647 - 1};
+    PW_CUDA(ctx, cudaMemcpyAsync(d_mm, init, sizeof init, cudaMemcpyHostToDevice, st));
+    mvs::pairwise_minmax_kernel<<<1184, 256, 0, st>>>(op.v, op.n * d, d_mm);
+    PW_CUDA(ctx, cudaGetLastError());
+    int mm[2];
+    PW_CUDA(ctx, cudaMemcpyAsync(mm, d_mm, sizeof mm, cudaMemcpyDeviceToHost, st));
+    PW_CUDA(ctx, cudaStreamSynchronize(st));
+    op.P = std::max(limbs_for_range(mm[0], mm[1]), mvs_internal_pairwise_limbs(ctx));
+    // one extra zero tile of rows: a row block may start at any row (shards), its last tile then reads past n
+    op.n_pad = (op.n + mvs::kImBM - 1) / mvs::kImBM * mvs::kImBM + mvs::kImBM;
+    op.k_pad = (d + mvs::kImBK - 1) / mvs::kImBK * mvs::kImBK;
+    PW_CUDA(ctx, op.planes.alloc(static_cast<size_t>(op.P) * op.n_pad * op.k_pad));
+    const int64_t threads = op.n_pad * (op.k_pad / 4);
+    mvs::pairwise_split_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, st>>>(
+        op.v, op.n, d, op.P, op.planes.as<int8_t>(), op.n_pad, op.k_pad);
+    PW_CUDA(ctx, cudaGetLastError());
+    mvs_internal_count_launches(ctx, 2);
+    return MVS_OK;
+}
+
+mvs::ImmaPlan make_plan(int PA, int PB)
+{
+    mvs::ImmaPlan plan{};
+    const int smax = std::min(PA + PB - 2, 3);   // weights 256^s with s > 3 vanish modulo 2^32
+    for (int s = smax; s >= 0; --s) {
+        bool first = true;
+        for (int p = 0; p < PA; ++p) {
+            const int q = s - p;
+            if (q < 0 || q >= PB) continue;
+            plan.p[plan.npairs] = static_cast<unsigned char>(p);
+            plan.q[plan.npairs] = static_cast<unsigned char>(q);
+            plan.shift_before[plan.npairs] = (first && plan.npairs > 0) ? 1 : 0;
+            first = false;
+            ++plan.npairs;
+        }
+    }
+    return plan;
+}
+
+// Rows [r0, r0 + mi) of A against all of B, operands resident in HBM.  Appends the kept triples
+// (row_base + i, col_base + j, dot) in (i, j) order to `out`; adds the CUDA-event times.
+int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, int64_t mi, const Operand& B, int d,
+                  const double* d_ni, const double* d_nj, int32_t row_base, int32_t col_base, int32_t* d_C,
+                  uint32_t* d_segcount, unsigned long long* d_rowoff, OutBuf& ob, Triples& out, double& gemm_ms,
+                  double& filter_ms, uint64_t& d2h_bytes)
+{
+    const int64_t mj = B.n;
     if (mi == 0 || mj == 0) return MVS_OK;
     cudaEvent_t e0, e1, e2;
     PW_CUDA(ctx, cudaEventCreate(&e0));
@@ -51,31 +121,47 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const int32_t* d_A, int64_t mi,
     struct EvGuard { cudaEvent_t a, b, c; ~EvGuard() { cudaEventDestroy(a); cudaEventDestroy(b); cudaEventDestroy(c); } } guard{e0, e1, e2};
 
     const int64_t ldc = (mj + 3) & ~int64_t{3};
-    const dim3 grid(static_cast<unsigned>((mj + mvs::kPwBN - 1) / mvs::kPwBN), static_cast<unsigned>((mi + mvs::kPwBM - 1) / mvs::kPwBM));
-    const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(d_A) & 15) == 0) && ((reinterpret_cast<uintptr_t>(d_B) & 15) == 0);
+    const int32_t* d_A = A.v + r0 * d;
     PW_CUDA(ctx, cudaEventRecord(e0, st));
-    if (vec) mvs::pairwise_dot_kernel<true><<<grid, mvs::kPwThreads, 0, st>>>(d_A, mi, d_B, mj, d, d_C, ldc);
-    else mvs::pairwise_dot_kernel<false><<<grid, mvs::kPwThreads, 0, st>>>(d_A, mi, d_B, mj, d, d_C, ldc);
+    if (A.P > 0) {                               // tensor-core limb GEMM
+        const mvs::ImmaPlan plan = make_plan(A.P, B.P);
+        const dim3 grid(static_cast<unsigned>((mj + mvs::kImBN - 1) / mvs::kImBN), static_cast<unsigned>((mi + mvs::kImBM - 1) / mvs::kImBM));
+        mvs::pairwise_dot_imma_kernel<<<grid, mvs::kImThreads, mvs::kImSmemBytes, st>>>(
+            A.planes.as<int8_t>() + r0 * A.k_pad, A.n_pad * A.k_pad, B.planes.as<int8_t>(), B.n_pad * B.k_pad, A.k_pad, plan,
+            mi, mj, d_C, ldc);
+    } else {                                     // IMAD GEMM
+        const dim3 grid(static_cast<unsigned>((mj + mvs::kPwBN - 1) / mvs::kPwBN), static_cast<unsigned>((mi + mvs::kPwBM - 1) / mvs::kPwBM));
+        const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(d_A) & 15) == 0) && ((reinterpret_cast<uintptr_t>(B.v) & 15) == 0);
+        if (vec) mvs::pairwise_dot_kernel<true><<<grid, mvs::kPwThreads, 0, st>>>(d_A, mi, B.v, mj, d, d_C, ldc);
+        else mvs::pairwise_dot_kernel<false><<<grid, mvs::kPwThreads, 0, st>>>(d_A, mi, B.v, mj, d, d_C, ldc);
+    }
     PW_CUDA(ctx, cudaGetLastError());
     PW_CUDA(ctx, cudaEventRecord(e1, st));
-    const unsigned row_ctas = static_cast<unsigned>((mi + 7) / 8);
-    mvs::pairwise_count_kernel<<<row_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_counts);
+    const int nseg = static_cast<int>((mj + mvs::kPwSeg - 1) / mvs::kPwSeg);
+    const unsigned seg_ctas = static_cast<unsigned>((mi * nseg + 7) / 8);
+    mvs::pairwise_count_kernel<<<seg_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_segcount, nseg);
     PW_CUDA(ctx, cudaGetLastError());
-    mvs::pairwise_scan_kernel<<<1, 1024, 0, st>>>(d_counts, mi);
+    mvs::pairwise_scan_kernel<<<1, 1024, 0, st>>>(d_segcount, nseg, d_rowoff, mi);
     PW_CUDA(ctx, cudaGetLastError());
     unsigned long long total = 0;
-    PW_CUDA(ctx, cudaMemcpyAsync(&total, d_counts + mi, sizeof total, cudaMemcpyDeviceToHost, st));
+    PW_CUDA(ctx, cudaMemcpyAsync(&total, d_rowoff + mi, sizeof total, cudaMemcpyDeviceToHost, st));
     PW_CUDA(ctx, cudaStreamSynchronize(st));
     mvs_internal_count_launches(ctx, 3);
     d2h_bytes += sizeof total;
 
     if (total) {
-        Dev rows, cols, vals;
-        PW_CUDA(ctx, rows.alloc(total * sizeof(int32_t)));
-        PW_CUDA(ctx, cols.alloc(total * sizeof(int32_t)));
-        PW_CUDA(ctx, vals.alloc(total * sizeof(int64_t)));
-        mvs::pairwise_emit_kernel<<<row_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_counts, row_base, col_base,
-                                                           rows.as<int32_t>(), cols.as<int32_t>(), vals.as<long long>());
+        if (total > ob.cap) {                    // grow (rare: the buffers start at 4 Mi triples)
+            ob.rows.release();
+            ob.cols.release();
+            ob.vals.release();
+            ob.cap = total + total / 4;
+            PW_CUDA(ctx, ob.rows.alloc(ob.cap * sizeof(int32_t)));
+            PW_CUDA(ctx, ob.cols.alloc(ob.cap * sizeof(int32_t)));
+            PW_CUDA(ctx, ob.vals.alloc(ob.cap * sizeof(int64_t)));
+        }
+        Dev &rows = ob.rows, &cols = ob.cols, &vals = ob.vals;
+        mvs::pairwise_emit_kernel<<<seg_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_segcount, nseg, d_rowoff, row_base,
+                                                           col_base, rows.as<int32_t>(), cols.as<int32_t>(), vals.as<long long>());
         PW_CUDA(ctx, cudaGetLastError());
         mvs_internal_count_launches(ctx, 1);
         PW_CUDA(ctx, cudaEventRecord(e2, st));
@@ -100,7 +186,49 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const int32_t* d_A, int64_t mi,
     return MVS_OK;
 }
 
-int finish(Triples& t, double gemm_ms, double filter_ms, double wall_ms, uint64_t h2d, uint64_t d2h, mvs_sparse_result** out)
+// All row blocks of A[begin, end) against B; scratch sized for `rb` rows.
+int run_blocks(mvs_ctx* ctx, cudaStream_t st, Operand& A, int64_t begin, int64_t end, Operand& B, bool same, int d,
+               const double* d_ni, const double* d_nj, Triples& t, double& gemm_ms, double& filter_ms, double& prep_ms,
+               uint64_t& d2h)
+{
+    const int64_t mj = B.n;
+    const int64_t ldc = (mj + 3) & ~int64_t{3};
+    const int64_t rb = std::min<int64_t>(std::max<int64_t>(128, std::min<int64_t>(8192, (int64_t{1} << 30) / (4 * std::max<int64_t>(ldc, 1)) / 128 * 128)),
+                                         (end - begin + 127) / 128 * 128);
+    const int nseg = static_cast<int>((mj + mvs::kPwSeg - 1) / mvs::kPwSeg);
+    Dev C, segcount, rowoff, mm;
+    OutBuf ob;
+    ob.cap = 4ull << 20;
+    PW_CUDA(ctx, ob.rows.alloc(ob.cap * sizeof(int32_t)));
+    PW_CUDA(ctx, ob.cols.alloc(ob.cap * sizeof(int32_t)));
+    PW_CUDA(ctx, ob.vals.alloc(ob.cap * sizeof(int64_t)));
+    PW_CUDA(ctx, C.alloc(static_cast<size_t>(rb) * ldc * 4));
+    PW_CUDA(ctx, segcount.alloc(static_cast<size_t>(rb) * nseg * 4));
+    PW_CUDA(ctx, rowoff.alloc(static_cast<size_t>(rb + 1) * 8));
+    if (mvs_internal_pairwise_path(ctx) != 1) {
+        const auto t0 = std::chrono::steady_clock::now();
+        PW_CUDA(ctx, mm.alloc(8));
+        PW_CUDA(ctx, cudaFuncSetAttribute(mvs::pairwise_dot_imma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mvs::kImSmemBytes));
+        int rc = prepare_operand(ctx, st, B, d, mm.as<int>());
+        if (rc != MVS_OK) return rc;
+        if (!same) {
+            rc = prepare_operand(ctx, st, A, d, mm.as<int>());
+            if (rc != MVS_OK) return rc;
+        }
+        PW_CUDA(ctx, cudaStreamSynchronize(st));
+        prep_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+    const Operand& Aref = same ? B : A;
+    for (int64_t r0 = begin; r0 < end; r0 += rb) {
+        const int64_t m = std::min(rb, end - r0);
+        const int rc = pairwise_core(ctx, st, Aref, r0, m, B, d, d_ni + r0, d_nj, static_cast<int32_t>(r0), 0, C.as<int32_t>(),
+                                     segcount.as<uint32_t>(), rowoff.as<unsigned long long>(), ob, t, gemm_ms, filter_ms, d2h);
+        if (rc != MVS_OK) return rc;
+    }
+    return MVS_OK;
+}
+
+int finish(Triples& t, double gemm_ms, double filter_ms, double prep_ms, double wall_ms, uint64_t h2d, uint64_t d2h, mvs_sparse_result** out)
 {
     mvs_sparse_result* r = static_cast<mvs_sparse_result*>(std::calloc(1, sizeof(mvs_sparse_result)));
     if (!r) return MVS_ERR_OOM;
@@ -120,20 +248,12 @@ int finish(Triples& t, double gemm_ms, double filter_ms, double wall_ms, uint64_
     }
     r->gemm_ms = gemm_ms;
     r->filter_ms = filter_ms;
+    r->prep_ms = prep_ms;
     r->wall_ms = wall_ms;
     r->h2d_bytes = h2d;
     r->d2h_bytes = d2h;
     *out = r;
     return MVS_OK;
-}
-
-// rows per GEMM call: the dense int32 C block stays <= 1 GiB
-int64_t rows_per_call(int64_t mj)
-{
-    const int64_t ldc = (mj + 3) & ~int64_t{3};
-    int64_t rb = (int64_t{1} << 30) / (4 * std::max<int64_t>(ldc, 1));
-    rb = std::max<int64_t>(128, std::min<int64_t>(8192, rb / 128 * 128));
-    return rb;
 }
 
 }  // namespace
@@ -161,34 +281,31 @@ int mvs_pairwise_block(mvs_ctx* ctx, const int32_t* block_i, int64_t mi, const i
     PW_CUDA(ctx, cudaSetDevice(mvs_internal_device(ctx)));
     cudaStream_t st = mvs_internal_stream(ctx);
     Triples t;
-    double gemm_ms = 0, filter_ms = 0;
+    double gemm_ms = 0, filter_ms = 0, prep_ms = 0;
     uint64_t h2d = 0, d2h = 0;
     if (mi > 0 && mj > 0) {
-        Dev A, B, ni, nj, C, counts;
+        Dev A, B, ni, nj;
         const size_t ab = static_cast<size_t>(mi) * d * 4, bb = static_cast<size_t>(mj) * d * 4;
-        const int64_t rb = std::min<int64_t>(rows_per_call(mj), mi);
-        const int64_t ldc = (mj + 3) & ~int64_t{3};
         PW_CUDA(ctx, A.alloc(ab));
         PW_CUDA(ctx, B.alloc(bb));
         PW_CUDA(ctx, ni.alloc(static_cast<size_t>(mi) * 8));
         PW_CUDA(ctx, nj.alloc(static_cast<size_t>(mj) * 8));
-        PW_CUDA(ctx, C.alloc(static_cast<size_t>(rb) * ldc * 4));
-        PW_CUDA(ctx, counts.alloc(static_cast<size_t>(rb + 1) * 8));
         PW_CUDA(ctx, cudaMemcpyAsync(A.p, block_i, ab, cudaMemcpyHostToDevice, st));
         PW_CUDA(ctx, cudaMemcpyAsync(B.p, block_j, bb, cudaMemcpyHostToDevice, st));
         PW_CUDA(ctx, cudaMemcpyAsync(ni.p, norms_i, static_cast<size_t>(mi) * 8, cudaMemcpyHostToDevice, st));
         PW_CUDA(ctx, cudaMemcpyAsync(nj.p, norms_j, static_cast<size_t>(mj) * 8, cudaMemcpyHostToDevice, st));
         h2d = ab + bb + static_cast<uint64_t>(mi + mj) * 8;
-        for (int64_t r0 = 0; r0 < mi; r0 += rb) {
-            const int64_t m = std::min(rb, mi - r0);
-            const int rc = pairwise_core(ctx, st, A.as<int32_t>() + r0 * d, m, B.as<int32_t>(), mj, d, ni.as<double>() + r0,
-                                         nj.as<double>(), static_cast<int32_t>(r0), 0, C.as<int32_t>(),
-                                         counts.as<unsigned long long>(), t, gemm_ms, filter_ms, d2h);
-            if (rc != MVS_OK) return rc;
-        }
+        Operand opA, opB;
+        opA.v = A.as<int32_t>();
+        opA.n = mi;
+        opB.v = B.as<int32_t>();
+        opB.n = mj;
+        const int rc = run_blocks(ctx, st, opA, 0, mi, opB, false, d, ni.as<double>(), nj.as<double>(), t, gemm_ms, filter_ms,
+                                  prep_ms, d2h);
+        if (rc != MVS_OK) return rc;
     }
     const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-    return finish(t, gemm_ms, filter_ms, wall, h2d, d2h, out);
+    return finish(t, gemm_ms, filter_ms, prep_ms, wall, h2d, d2h, out);
 }
 
 int mvs_pairwise_shard(mvs_ctx* ctx, const int32_t* vectors, int64_t n_total, int d, const double* norms_sq,
@@ -203,32 +320,26 @@ int mvs_pairwise_shard(mvs_ctx* ctx, const int32_t* vectors, int64_t n_total, in
     PW_CUDA(ctx, cudaSetDevice(mvs_internal_device(ctx)));
     cudaStream_t st = mvs_internal_stream(ctx);
     Triples t;
-    double gemm_ms = 0, filter_ms = 0;
+    double gemm_ms = 0, filter_ms = 0, prep_ms = 0;
     uint64_t h2d = 0, d2h = 0;
-    const int64_t mi = end_row - begin_row;
-    if (mi > 0) {
+    if (end_row > begin_row) {
         // the whole db stays resident (n_total x d x 4 bytes: 8 GB per million vectors at d = 2048)
-        Dev V, nrm, C, counts;
+        Dev V, nrm;
         const size_t vb = static_cast<size_t>(n_total) * d * 4;
-        const int64_t rb = std::min<int64_t>(rows_per_call(n_total), mi);
-        const int64_t ldc = (n_total + 3) & ~int64_t{3};
         PW_CUDA(ctx, V.alloc(vb));
         PW_CUDA(ctx, nrm.alloc(static_cast<size_t>(n_total) * 8));
-        PW_CUDA(ctx, C.alloc(static_cast<size_t>(rb) * ldc * 4));
-        PW_CUDA(ctx, counts.alloc(static_cast<size_t>(rb + 1) * 8));
         PW_CUDA(ctx, cudaMemcpyAsync(V.p, vectors, vb, cudaMemcpyHostToDevice, st));
         PW_CUDA(ctx, cudaMemcpyAsync(nrm.p, norms_sq, static_cast<size_t>(n_total) * 8, cudaMemcpyHostToDevice, st));
         h2d = vb + static_cast<uint64_t>(n_total) * 8;
-        for (int64_t r0 = begin_row; r0 < end_row; r0 += rb) {
-            const int64_t m = std::min(rb, end_row - r0);
-            const int rc = pairwise_core(ctx, st, V.as<int32_t>() + r0 * d, m, V.as<int32_t>(), n_total, d,
-                                         nrm.as<double>() + r0, nrm.as<double>(), static_cast<int32_t>(r0), 0,
-                                         C.as<int32_t>(), counts.as<unsigned long long>(), t, gemm_ms, filter_ms, d2h);
-            if (rc != MVS_OK) return rc;
-        }
+        Operand op, unused;
+        op.v = V.as<int32_t>();
+        op.n = n_total;
+        const int rc = run_blocks(ctx, st, unused, begin_row, end_row, op, true, d, nrm.as<double>(), nrm.as<double>(), t, gemm_ms,
+                                  filter_ms, prep_ms, d2h);
+        if (rc != MVS_OK) return rc;
     }
     const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-    return finish(t, gemm_ms, filter_ms, wall, h2d, d2h, out);
+    return finish(t, gemm_ms, filter_ms, prep_ms, wall, h2d, d2h, out);
 }
 
 }  // extern "C"

@@ -7,14 +7,14 @@
 // and the kept triples are returned in row-major (i, then j) order, like the reference's double loop.
 //
 // How:
-//   1. pairwise_dot_kernel: register-tiled int32 GEMM on the FMA-heavy pipe (IMAD is exact modulo 2^32 by
-//      construction, for ANY int32 input; a tensor-core path would need 10 u8 x u8 limb products for that and is
-//      left to a later round).  128 x 128 x 16 CTA tiles, 256 threads, 8 x 8 outputs per thread,
-//      operands staged k-major in shared memory (double buffered, register prefetch), dense C written once.
-//   2. pairwise_count_kernel: one warp per row applies the threshold and counts the kept columns.
-//   3. pairwise_scan_kernel: exclusive scan of the row counts (single CTA; rows per call <= a few thousand).
-//   4. pairwise_emit_kernel: one warp per row writes its kept triples in column order at the scanned offset
-//      (ballot + popc prefix inside the warp): deterministic order, no atomics.
+//   1a. pairwise_dot_imma_kernel (default): the int32 operands are split into balanced base-256 limbs and the
+//       limb products run on the tensor cores (int8 IMMA, int32 accumulate), combined modulo 2^32 by Horner's
+//       rule in one accumulator set -- exact for any int32 input; see the section header below.
+//   1b. pairwise_dot_kernel (cross-check path, option "pairwise_path" = 1): register-tiled int32 GEMM on the
+//       FMA-heavy pipe (IMAD is exact modulo 2^32 by construction).  128 x 128 x 16 CTA tiles, 256 threads,
+//       8 x 8 outputs per thread, operands staged k-major in shared memory (double buffered).
+//   2.  pairwise_count_kernel / pairwise_scan_kernel / pairwise_emit_kernel: threshold + ordered compaction of the
+//       dense C block into (row, col, dot) triples in the reference's loop order, no atomics.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -153,36 +153,258 @@ pairwise_dot_kernel(const int32_t* __restrict__ A, int64_t mi, const int32_t* __
     }
 }
 
-// counts[i] = number of columns kept in row i.  One warp per row.
+// ------------------------------------------------------------------------------------------------------
+// Tensor-core path: int32 = up to 4 balanced base-256 limbs, v = sum_p 256^p * s_p with s_p in [-128, 127]
+// (exact modulo 2^32), so   dot mod 2^32 = sum_{p + q <= 3} 256^(p+q) * (A_p . B_q)   with int8 x int8 -> int32
+// limb products on the tensor cores (IMMA m16n8k32 via mma.sync: 572 TMAC/s measured on B200, 31x the IMAD
+// pipe; tools/kexp/mma_probe.cu).  Sketch entries are small (|v| ~ sqrt(#hashes)), so P = 2 limbs (4 limb
+// products) is the common case; P is chosen from the min/max of the operands and P = 4 (10 products) is exact
+// for ANY int32 input.  One accumulator set serves all products by Horner's rule: the limb pairs are run
+// in order of decreasing p + q and the accumulators are shifted left by 8 between weights; a limb product
+// accumulates at most d * 2^14 per weight, and int32 wrap-around is exactly what the reference computes.
+// ------------------------------------------------------------------------------------------------------
+constexpr int kImBM = 128, kImBN = 128, kImBK = 64;       // k in BYTES (= int8 elements) per stage
+constexpr int kImPitch = kImBK + 16;                      // 80-byte rows: ldmatrix reads are bank-conflict free
+constexpr int kImStages = 4;
+constexpr int kImThreads = 256;
+constexpr int kImStageBytes = (kImBM + kImBN) * kImPitch; // 20480
+constexpr int kImSmemBytes = kImStages * kImStageBytes;   // 81920
+
+struct ImmaPlan {                                         // limb pairs in order of decreasing weight
+    int npairs;
+    unsigned char p[10], q[10], shift_before[10];         // shift_before: accumulators <<= 8 before this pair
+};
+
+// min / max of an int32 array (order-independent atomics on two words initialised to INT_MAX / INT_MIN)
+__global__ void __launch_bounds__(256) pairwise_minmax_kernel(const int32_t* __restrict__ v, int64_t n, int* __restrict__ mm)
+{
+    int lo = 2147483647, hi = -2147483647 - 1;
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int x = v[i];
+        lo = min(lo, x);
+        hi = max(hi, x);
+    }
+#pragma unroll
+    for (int m = 16; m; m >>= 1) {
+        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, m));
+        hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, m));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(mm, lo);
+        atomicMax(mm + 1, hi);
+    }
+}
+
+// V [n x d] int32 -> P planes of int8 [n_pad x k_pad] (row-major, zero padded).  One thread = 4 consecutive k.
+__global__ void __launch_bounds__(256)
+pairwise_split_kernel(const int32_t* __restrict__ V, int64_t n, int d, int P, int8_t* __restrict__ planes, int64_t n_pad, int k_pad)
+{
+    const int64_t quads = static_cast<int64_t>(k_pad) / 4;
+    const int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (t >= n_pad * quads) return;
+    const int64_t row = t / quads;
+    const int k = static_cast<int>(t - row * quads) * 4;
+    long long v[4] = {0, 0, 0, 0};
+    if (row < n)
+        for (int e = 0; e < 4; ++e)
+            if (k + e < d) v[e] = V[row * d + k + e];
+    for (int p = 0; p < P; ++p) {
+        uint32_t word = 0;
+        for (int e = 0; e < 4; ++e) {
+            const int s = static_cast<int>(static_cast<signed char>(v[e] & 0xFF));
+            word |= static_cast<uint32_t>(s & 0xFF) << (8 * e);
+            v[e] = (v[e] - s) >> 8;                                  // exact: v - s is a multiple of 256
+        }
+        *reinterpret_cast<uint32_t*>(planes + (static_cast<int64_t>(p) * n_pad + row) * k_pad + k) = word;
+    }
+}
+
+__device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void* gsrc)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3)
+{
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ void imma16832(int (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
+{
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// C[i][j] = sum_k A[i][k] * B[j][k] (mod 2^32) from limb planes.  grid = (nj_pad/128, mi_pad/128); planes are
+// padded to multiples of 128 rows and 64 k, so the main loop has no edge handling; only the C store is guarded.
+// 8 warps = 2 (m) x 4 (n); a warp owns 64 x 32 outputs = 4 x 4 IMMA tiles (64 accumulator registers).
+__global__ void __launch_bounds__(kImThreads, 2)
+pairwise_dot_imma_kernel(const int8_t* __restrict__ Ap, int64_t a_plane_stride, const int8_t* __restrict__ Bp,
+                         int64_t b_plane_stride, int k_pad, ImmaPlan plan, int64_t mi, int64_t mj,
+                         int32_t* __restrict__ C, int64_t ldc)
+{
+    extern __shared__ __align__(128) unsigned char im_smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp & 1, wn = warp >> 1;
+    const int64_t row0 = static_cast<int64_t>(blockIdx.y) * kImBM;
+    const int64_t col0 = static_cast<int64_t>(blockIdx.x) * kImBN;
+    const uint32_t smem_base = static_cast<uint32_t>(__cvta_generic_to_shared(im_smem));
+
+    const int nk = k_pad / kImBK;
+    const int steps = plan.npairs * nk;
+
+    // loader: 1024 16-byte chunks per stage (512 of A, 512 of B), 4 per thread: chunk c -> row c / 4, k-chunk c % 4
+    auto issue = [&](int t) {
+        const int pair = t / nk, kk = t - pair * nk;
+        const int8_t* a = Ap + plan.p[pair] * a_plane_stride + row0 * k_pad + kk * kImBK;
+        const int8_t* b = Bp + plan.q[pair] * b_plane_stride + col0 * k_pad + kk * kImBK;
+        const uint32_t st = smem_base + (t % kImStages) * kImStageBytes;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int c = tid + i * kImThreads;
+            const int r = c >> 2, kc = (c & 3) * 16;
+            cp_async16(st + r * kImPitch + kc, a + static_cast<int64_t>(r) * k_pad + kc);
+            cp_async16(st + (kImBM + r) * kImPitch + kc, b + static_cast<int64_t>(r) * k_pad + kc);
+        }
+    };
+
+    int acc[4][4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) acc[i][j][e] = 0;
+
+    // ldmatrix lane addressing (see header of this section): A: row = (l & 7) + 8 * ((l >> 3) & 1), k += 16 * (l >> 4)
+    //                                                         B: n   = (l & 7) + 8 * (l >> 4),       k += 16 * ((l >> 3) & 1)
+    const uint32_t a_lane = static_cast<uint32_t>((wm * 64 + (lane & 7) + ((lane >> 3) & 1) * 8) * kImPitch + (lane >> 4) * 16);
+    const uint32_t b_lane = static_cast<uint32_t>((kImBM + wn * 32 + (lane & 7) + (lane >> 4) * 8) * kImPitch + ((lane >> 3) & 1) * 16);
+
+#pragma unroll
+    for (int t = 0; t < kImStages - 1; ++t) {
+        if (t < steps) issue(t);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    for (int t = 0; t < steps; ++t) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(kImStages - 2) : "memory");
+        __syncthreads();
+        if (t + kImStages - 1 < steps) issue(t + kImStages - 1);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+
+        const int pair = t / nk;
+        if (t - pair * nk == 0 && plan.shift_before[pair]) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) acc[i][j][e] = static_cast<int>(static_cast<uint32_t>(acc[i][j][e]) << 8);
+        }
+        const uint32_t st = smem_base + (t % kImStages) * kImStageBytes;
+#pragma unroll
+        for (int ks = 0; ks < kImBK / 32; ++ks) {
+            uint32_t a[4][4], b[4][2];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) ldmatrix_x4(st + a_lane + i * 16 * kImPitch + ks * 32, a[i][0], a[i][1], a[i][2], a[i][3]);
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+                ldmatrix_x4(st + b_lane + j * 16 * kImPitch + ks * 32, b[2 * j][0], b[2 * j][1], b[2 * j + 1][0], b[2 * j + 1][1]);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) imma16832(acc[i][j], a[i], b[j][0], b[j][1]);
+        }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+
+    // accumulator layout of m16n8: c0,c1 -> (row g, cols 2t, 2t+1), c2,c3 -> (row g + 8, same cols); g = lane / 4, t = lane % 4
+    const int g = lane >> 2, tq = lane & 3;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int64_t r = row0 + wm * 64 + i * 16 + g + h * 8;
+            if (r >= mi) continue;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int64_t c = col0 + wn * 32 + j * 8 + tq * 2;
+                int32_t* dst = C + r * ldc + c;
+                if (c + 1 < mj) *reinterpret_cast<int2*>(dst) = make_int2(acc[i][j][2 * h], acc[i][j][2 * h + 1]);   // ldc even, c even
+                else if (c < mj) dst[0] = acc[i][j][2 * h];
+            }
+        }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Threshold + ordered compaction.  The columns of a row are cut into segments of 128; one warp owns one
+// (row, segment): lane L holds columns 4L..4L+3 of the segment (one 16-byte load).
+//   pairwise_count_kernel : segcount[row][seg] = kept columns of the segment
+//   pairwise_scan_kernel  : rowoff[row] = exclusive scan of the row totals (single CTA), total in rowoff[mi]
+//   pairwise_emit_kernel  : non-empty segments write their triples at rowoff[row] + sum of the earlier
+//                           segments of the row + rank inside the segment: (row, col) order, no atomics;
+//                           empty segments (almost all of them) do not read C again.
+// ------------------------------------------------------------------------------------------------------
+constexpr int kPwSeg = 128;
+
+__device__ __forceinline__ unsigned pw_keep_mask4(const int32_t* __restrict__ crow, int64_t j, int64_t mj, int d, double ni,
+                                                 const double* __restrict__ norms_j, int4& v)
+{
+    v = make_int4(0, 0, 0, 0);
+    unsigned m = 0;
+    if (j + 3 < mj) {                                                // ldc % 4 == 0 and C 16-byte aligned (host)
+        v = *reinterpret_cast<const int4*>(crow + j);
+        m |= pw_keep(v.x, d, ni, norms_j[j]) ? 1u : 0u;
+        m |= pw_keep(v.y, d, ni, norms_j[j + 1]) ? 2u : 0u;
+        m |= pw_keep(v.z, d, ni, norms_j[j + 2]) ? 4u : 0u;
+        m |= pw_keep(v.w, d, ni, norms_j[j + 3]) ? 8u : 0u;
+    } else {
+        int32_t* e = &v.x;
+        for (int t = 0; t < 4; ++t)
+            if (j + t < mj) {
+                e[t] = crow[j + t];
+                m |= pw_keep(e[t], d, ni, norms_j[j + t]) ? (1u << t) : 0u;
+            }
+    }
+    return m;
+}
+
 __global__ void __launch_bounds__(256)
 pairwise_count_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int64_t ldc, int d,
                       const double* __restrict__ norms_i, const double* __restrict__ norms_j,
-                      unsigned long long* __restrict__ counts)
+                      uint32_t* __restrict__ segcount, int nseg)
 {
-    const int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (row >= mi) return;
+    const int64_t w = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (w >= mi * nseg) return;
+    const int64_t row = w / nseg;
+    const int seg = static_cast<int>(w - row * nseg);
     const int lane = threadIdx.x & 31;
-    const double ni = norms_i[row];
-    const int32_t* c = C + row * ldc;
-    unsigned int n = 0;
-    for (int64_t j = lane; j < mj; j += 32) n += pw_keep(c[j], d, ni, norms_j[j]) ? 1u : 0u;
+    int4 v;
+    unsigned n = __popc(pw_keep_mask4(C + row * ldc, static_cast<int64_t>(seg) * kPwSeg + lane * 4, mj, d, norms_i[row], norms_j, v));
 #pragma unroll
     for (int m = 16; m; m >>= 1) n += __shfl_xor_sync(0xffffffffu, n, m);
-    if (lane == 0) counts[row] = n;
+    if (lane == 0) segcount[w] = n;
 }
 
-// In-place exclusive scan of counts[0..n), total in counts[n].  One CTA of 1024 threads.
+// rowoff[0..mi) = exclusive scan of the row totals of segcount, rowoff[mi] = total.  One CTA of 1024 threads.
 __global__ void __launch_bounds__(1024)
-pairwise_scan_kernel(unsigned long long* __restrict__ counts, int64_t n)
+pairwise_scan_kernel(const uint32_t* __restrict__ segcount, int nseg, unsigned long long* __restrict__ rowoff, int64_t n)
 {
     __shared__ unsigned long long warp_sums[32];
     __shared__ unsigned long long carry;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) carry = 0;
+    // row totals first, one warp per row (coalesced reads of the row's segment counts)
+    for (int64_t r = warp; r < n; r += 32) {
+        unsigned long long t = 0;
+        for (int k = lane; k < nseg; k += 32) t += segcount[r * nseg + k];
+#pragma unroll
+        for (int m = 16; m; m >>= 1) t += __shfl_xor_sync(0xffffffffu, t, m);
+        if (lane == 0) rowoff[r] = t;
+    }
     __syncthreads();
     for (int64_t base = 0; base < n; base += 1024) {
         const int64_t i = base + threadIdx.x;
-        const unsigned long long v = i < n ? counts[i] : 0ull;
+        const unsigned long long v = i < n ? rowoff[i] : 0ull;
         unsigned long long x = v;
 #pragma unroll
         for (int m = 1; m < 32; m <<= 1) {
@@ -192,54 +414,60 @@ pairwise_scan_kernel(unsigned long long* __restrict__ counts, int64_t n)
         if (lane == 31) warp_sums[warp] = x;
         __syncthreads();
         if (warp == 0) {
-            unsigned long long s = warp_sums[lane];
+            unsigned long long t = warp_sums[lane];
 #pragma unroll
             for (int m = 1; m < 32; m <<= 1) {
-                const unsigned long long y = __shfl_up_sync(0xffffffffu, s, m);
-                if (lane >= m) s += y;
+                const unsigned long long y = __shfl_up_sync(0xffffffffu, t, m);
+                if (lane >= m) t += y;
             }
-            warp_sums[lane] = s;                 // inclusive over warps
+            warp_sums[lane] = t;                 // inclusive over warps
         }
         __syncthreads();
         const unsigned long long before = carry + (warp ? warp_sums[warp - 1] : 0ull) + (x - v);
-        if (i < n) counts[i] = before;
+        if (i < n) rowoff[i] = before;
         __syncthreads();
         if (threadIdx.x == 1023) carry = before + v;
         __syncthreads();
     }
-    if (threadIdx.x == 0) counts[n] = carry;
+    if (threadIdx.x == 0) rowoff[n] = carry;
 }
 
-// Row i writes its kept (row, col, dot) triples in column order starting at offsets[i].
 __global__ void __launch_bounds__(256)
 pairwise_emit_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int64_t ldc, int d,
                      const double* __restrict__ norms_i, const double* __restrict__ norms_j,
-                     const unsigned long long* __restrict__ offsets, int32_t row_base, int32_t col_base,
+                     const uint32_t* __restrict__ segcount, int nseg, const unsigned long long* __restrict__ rowoff,
+                     int32_t row_base, int32_t col_base,
                      int32_t* __restrict__ rows, int32_t* __restrict__ cols, long long* __restrict__ values)
 {
-    const int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (row >= mi) return;
+    const int64_t w = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (w >= mi * nseg) return;
+    if (segcount[w] == 0) return;                                    // warp-uniform
+    const int64_t row = w / nseg;
+    const int seg = static_cast<int>(w - row * nseg);
     const int lane = threadIdx.x & 31;
-    const double ni = norms_i[row];
-    const int32_t* c = C + row * ldc;
-    unsigned long long pos = offsets[row];
-    for (int64_t j0 = 0; j0 < mj; j0 += 32) {
-        const int64_t j = j0 + lane;
-        int32_t dot = 0;
-        bool keep = false;
-        if (j < mj) {
-            dot = c[j];
-            keep = pw_keep(dot, d, ni, norms_j[j]);
-        }
-        const unsigned int m = __ballot_sync(0xffffffffu, keep);
-        if (keep) {
-            const unsigned long long at = pos + __popc(m & ((1u << lane) - 1u));
-            rows[at] = row_base + static_cast<int32_t>(row);
-            cols[at] = col_base + static_cast<int32_t>(j);
-            values[at] = static_cast<long long>(dot);
-        }
-        pos += __popc(m);
+    unsigned long long before = 0;                                    // kept columns of the row left of this segment
+    for (int t = lane; t < seg; t += 32) before += segcount[row * nseg + t];
+#pragma unroll
+    for (int m = 16; m; m >>= 1) before += __shfl_xor_sync(0xffffffffu, before, m);
+    int4 v;
+    const int64_t j = static_cast<int64_t>(seg) * kPwSeg + lane * 4;
+    const unsigned m4 = pw_keep_mask4(C + row * ldc, j, mj, d, norms_i[row], norms_j, v);
+    unsigned mine = __popc(m4), incl = mine;
+#pragma unroll
+    for (int m = 1; m < 32; m <<= 1) {
+        const unsigned y = __shfl_up_sync(0xffffffffu, incl, m);
+        if (lane >= m) incl += y;
     }
+    unsigned long long at = rowoff[row] + before + (incl - mine);
+    const int32_t e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int t = 0; t < 4; ++t)
+        if (m4 & (1u << t)) {
+            rows[at] = row_base + static_cast<int32_t>(row);
+            cols[at] = col_base + static_cast<int32_t>(j + t);
+            values[at] = static_cast<long long>(e[t]);
+            ++at;
+        }
 }
 
 }  // namespace mvs

@@ -17,13 +17,13 @@ import numpy as np
 
 from ._lib import check
 
-SparseResult = namedtuple("SparseResult", "rows cols values gemm_ms filter_ms wall_ms h2d_bytes d2h_bytes")
+SparseResult = namedtuple("SparseResult", "rows cols values gemm_ms filter_ms prep_ms wall_ms h2d_bytes d2h_bytes")
 
 
 class _CSparse(C.Structure):
     _fields_ = [("n", C.c_int64), ("rows", C.POINTER(C.c_int32)), ("cols", C.POINTER(C.c_int32)),
                 ("values", C.POINTER(C.c_int64)), ("gemm_ms", C.c_double), ("filter_ms", C.c_double),
-                ("wall_ms", C.c_double), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+                ("prep_ms", C.c_double), ("wall_ms", C.c_double), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
 
 
 def _take(lib, ptr):
@@ -35,7 +35,7 @@ def _take(lib, ptr):
         vals = np.ctypeslib.as_array(r.values, shape=(n,)).copy()
     else:
         rows, cols, vals = np.empty(0, np.int32), np.empty(0, np.int32), np.empty(0, np.int64)
-    out = SparseResult(rows, cols, vals, r.gemm_ms, r.filter_ms, r.wall_ms, int(r.h2d_bytes), int(r.d2h_bytes))
+    out = SparseResult(rows, cols, vals, r.gemm_ms, r.filter_ms, r.prep_ms, r.wall_ms, int(r.h2d_bytes), int(r.d2h_bytes))
     lib.mvs_free_sparse_result(ptr)
     return out
 

@@ -13,9 +13,13 @@ from oracle_util import (load_toy_ref, norms_sq_like_reference, oracle_pairwise,
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module")
-def sk():
+# every test runs on the tensor-core limb GEMM (limbs from the data, and forced to 3 and 4 limbs = 8 and 10
+# limb products) and on the IMAD GEMM: all four must give the reference's bits
+@pytest.fixture(scope="module", params=["imma", "imma3", "imma4", "imad"])
+def sk(request):
     s = mvs.Sketcher(0)
+    s.set_option("pairwise_path", 1 if request.param == "imad" else 0)
+    s.set_option("pairwise_limbs", {"imma": 0, "imma3": 3, "imma4": 4, "imad": 0}[request.param])
     yield s
     s.close()
 
