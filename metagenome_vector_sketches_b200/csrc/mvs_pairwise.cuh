@@ -252,19 +252,36 @@ pairwise_dot_imma_kernel(const int8_t* __restrict__ Ap, int64_t a_plane_stride, 
     const int nk = k_pad / kImBK;
     const int steps = plan.npairs * nk;
 
-    // loader: 1024 16-byte chunks per stage (512 of A, 512 of B), 4 per thread: chunk c -> row c / 4, k-chunk c % 4
-    auto issue = [&](int t) {
-        const int pair = t / nk, kk = t - pair * nk;
-        const int8_t* a = Ap + plan.p[pair] * a_plane_stride + row0 * k_pad + kk * kImBK;
-        const int8_t* b = Bp + plan.q[pair] * b_plane_stride + col0 * k_pad + kk * kImBK;
-        const uint32_t st = smem_base + (t % kImStages) * kImStageBytes;
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            const int c = tid + i * kImThreads;
-            const int r = c >> 2, kc = (c & 3) * 16;
-            cp_async16(st + r * kImPitch + kc, a + static_cast<int64_t>(r) * k_pad + kc);
-            cp_async16(st + (kImBM + r) * kImPitch + kc, b + static_cast<int64_t>(r) * k_pad + kc);
+    // the plan in shared memory (dynamic indexing of kernel parameters would go through local memory)
+    __shared__ int s_p[10], s_q[10], s_shift[10];
+    if (tid < 10) { s_p[tid] = plan.p[tid]; s_q[tid] = plan.q[tid]; s_shift[tid] = plan.shift_before[tid]; }
+    __syncthreads();
+
+    // loader: 1024 16-byte chunks per stage (512 of A, 512 of B), 4 per thread: thread -> rows tid / 4 and tid / 4 + 64,
+    // k-chunk tid % 4.  Producer state (pair, k-step, stage) advances by one per issue: no division in the loop.
+    const int lrow = tid >> 2, lkc = (tid & 3) * 16;
+    const int64_t a_thread = (row0 + lrow) * k_pad + lkc, b_thread = (col0 + lrow) * k_pad + lkc;
+    const int64_t half = static_cast<int64_t>(64) * k_pad;
+    const uint32_t s_thread = static_cast<uint32_t>(lrow * kImPitch + lkc);
+    int p_pair = 0, p_kk = 0, p_stage = 0;
+    const int8_t* a_src = Ap + s_p[0] * a_plane_stride + a_thread;
+    const int8_t* b_src = Bp + s_q[0] * b_plane_stride + b_thread;
+    auto issue = [&]() {
+        const uint32_t st = smem_base + p_stage * kImStageBytes + s_thread;
+        cp_async16(st, a_src);
+        cp_async16(st + 64 * kImPitch, a_src + half);
+        cp_async16(st + kImBM * kImPitch, b_src);
+        cp_async16(st + (kImBM + 64) * kImPitch, b_src + half);
+        a_src += kImBK;
+        b_src += kImBK;
+        if (++p_kk == nk) {
+            p_kk = 0;
+            if (++p_pair < plan.npairs) {
+                a_src = Ap + s_p[p_pair] * a_plane_stride + a_thread;
+                b_src = Bp + s_q[p_pair] * b_plane_stride + b_thread;
+            }
         }
+        if (++p_stage == kImStages) p_stage = 0;
     };
 
     int acc[4][4][4];
@@ -282,17 +299,17 @@ pairwise_dot_imma_kernel(const int8_t* __restrict__ Ap, int64_t a_plane_stride, 
 
 #pragma unroll
     for (int t = 0; t < kImStages - 1; ++t) {
-        if (t < steps) issue(t);
+        if (t < steps) issue();
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
+    int c_pair = 0, c_kk = 0, c_stage = 0;
     for (int t = 0; t < steps; ++t) {
         asm volatile("cp.async.wait_group %0;" ::"n"(kImStages - 2) : "memory");
         __syncthreads();
-        if (t + kImStages - 1 < steps) issue(t + kImStages - 1);
+        if (t + kImStages - 1 < steps) issue();
         asm volatile("cp.async.commit_group;" ::: "memory");
 
-        const int pair = t / nk;
-        if (t - pair * nk == 0 && plan.shift_before[pair]) {
+        if (c_kk == 0 && s_shift[c_pair]) {
 #pragma unroll
             for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -300,7 +317,7 @@ pairwise_dot_imma_kernel(const int8_t* __restrict__ Ap, int64_t a_plane_stride, 
 #pragma unroll
                     for (int e = 0; e < 4; ++e) acc[i][j][e] = static_cast<int>(static_cast<uint32_t>(acc[i][j][e]) << 8);
         }
-        const uint32_t st = smem_base + (t % kImStages) * kImStageBytes;
+        const uint32_t st = smem_base + c_stage * kImStageBytes;
 #pragma unroll
         for (int ks = 0; ks < kImBK / 32; ++ks) {
             uint32_t a[4][4], b[4][2];
@@ -314,6 +331,8 @@ pairwise_dot_imma_kernel(const int8_t* __restrict__ Ap, int64_t a_plane_stride, 
 #pragma unroll
                 for (int j = 0; j < 4; ++j) imma16832(acc[i][j], a[i], b[j][0], b[j][1]);
         }
+        if (++c_kk == nk) { c_kk = 0; ++c_pair; }
+        if (++c_stage == kImStages) c_stage = 0;
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
 
