@@ -213,8 +213,9 @@ int mvs_get_timing(mvs_ctx* ctx, mvs_timing* t);    /* synchronises the context'
 int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second);
 
 /* Kernel tuning knobs for experiments (0 = default).  Unknown keys are ignored.
- * "pairwise_path": 0 = tensor-core limb GEMM (default), 1 = IMAD GEMM; "pairwise_limbs": 0 = from the data,
- * 1..4 = use at least that many base-256 limbs (both paths are exact; the knobs exist for the parity tests). */
+ * "pairwise_path": 0 = tcgen05 limb GEMM (TMA + TMEM, default), 1 = IMAD GEMM, 2 = mma.sync limb GEMM;
+ * "pairwise_limbs": 0 = from the data, 1..4 = use at least that many base-256 limbs (all paths are exact; the
+ * knobs exist for the parity tests). */
 int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value);
 
 #ifdef __cplusplus

@@ -5,6 +5,7 @@
 #include "../../include/mvs_b200.h"
 #include "mvs_internal.h"
 #include "mvs_pairwise.cuh"
+#include "mvs_pairwise_umma.cuh"
 
 #include <algorithm>
 #include <chrono>
@@ -51,7 +52,60 @@ struct Operand {
     int P = 0;
     int64_t n_pad = 0;
     int k_pad = 0;
+    CUtensorMap tmap{};                          // tcgen05 path: 3-D map {k, row, plane}, box 128 B x 128 rows x 1
 };
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (libcuda is not linked directly)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled()
+{
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess) p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+bool make_tensor_map(Operand& op)
+{
+    EncodeTiledFn enc = encode_tiled();
+    if (!enc) return false;
+    const cuuint64_t dims[3] = {static_cast<cuuint64_t>(op.k_pad), static_cast<cuuint64_t>(op.n_pad), static_cast<cuuint64_t>(op.P)};
+    const cuuint64_t strides[2] = {static_cast<cuuint64_t>(op.k_pad), static_cast<cuuint64_t>(op.k_pad) * static_cast<cuuint64_t>(op.n_pad)};
+    const cuuint32_t box[3] = {mvs::kUmBKB, mvs::kUmBM, 1}, estr[3] = {1, 1, 1};
+    return enc(&op.tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, op.planes.p, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+mvs::UmmaPlan make_umma_plan(int PA, int PB, bool allow_fused)
+{
+    mvs::UmmaPlan pl{};
+    pl.smax = std::min(PA + PB - 2, 3);
+    if (allow_fused && PA + PB <= 4) {           // FUSED: all planes of a k-slice in one stage
+        pl.ngroups = 1;
+        pl.a_count = PA;
+        pl.b_count = PB;
+        pl.a_first[0] = 0;
+        pl.b_first[0] = 0;
+    } else {                                     // STREAM: one limb pair per group
+        pl.a_count = pl.b_count = 1;
+        for (int s = pl.smax; s >= 0; --s)
+            for (int p = 0; p < PA; ++p) {
+                const int q = s - p;
+                if (q < 0 || q >= PB) continue;
+                pl.a_first[pl.ngroups] = static_cast<unsigned char>(p);
+                pl.b_first[pl.ngroups] = static_cast<unsigned char>(q);
+                ++pl.ngroups;
+            }
+    }
+    const int stage_bytes = (pl.a_count + pl.b_count) * mvs::kUmTile;
+    pl.stages = std::max(2, std::min(6, mvs::kUmSmemBudget / stage_bytes));
+    return pl;
+}
 
 // limbs needed so that every value in [lo, hi] is a sum of P balanced base-256 digits (P = 4 covers int32 mod 2^32)
 int limbs_for_range(int lo, int hi)
@@ -76,13 +130,14 @@ int prepare_operand(mvs_ctx* ctx, cudaStream_t st, Operand& op, int d, int* d_mm
     op.P = std::max(limbs_for_range(mm[0], mm[1]), mvs_internal_pairwise_limbs(ctx));
     // one extra zero tile of rows: a row block may start at any row (shards), its last tile then reads past n
     op.n_pad = (op.n + mvs::kImBM - 1) / mvs::kImBM * mvs::kImBM + mvs::kImBM;
-    op.k_pad = (d + mvs::kImBK - 1) / mvs::kImBK * mvs::kImBK;
+    op.k_pad = (d + mvs::kUmBKB - 1) / mvs::kUmBKB * mvs::kUmBKB;      // 128: a multiple of both paths' k-slices
     PW_CUDA(ctx, op.planes.alloc(static_cast<size_t>(op.P) * op.n_pad * op.k_pad));
     const int64_t threads = op.n_pad * (op.k_pad / 4);
     mvs::pairwise_split_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, st>>>(
         op.v, op.n, d, op.P, op.planes.as<int8_t>(), op.n_pad, op.k_pad);
     PW_CUDA(ctx, cudaGetLastError());
     mvs_internal_count_launches(ctx, 2);
+    if (mvs_internal_pairwise_path(ctx) == 0 && !make_tensor_map(op)) return MVS_ERR_CUDA;
     return MVS_OK;
 }
 
@@ -122,8 +177,17 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
 
     const int64_t ldc = (mj + 3) & ~int64_t{3};
     const int32_t* d_A = A.v + r0 * d;
+    const int nseg = static_cast<int>((mj + mvs::kPwSeg - 1) / mvs::kPwSeg);
+    const unsigned seg_ctas = static_cast<unsigned>((mi * nseg + 7) / 8);
     PW_CUDA(ctx, cudaEventRecord(e0, st));
-    if (A.P > 0) {                               // tensor-core limb GEMM
+    if (A.P > 0 && mvs_internal_pairwise_path(ctx) == 0) {   // tcgen05 limb GEMM (TMA + TMEM)
+        const mvs::UmmaPlan plan = make_umma_plan(A.P, B.P, mvs_internal_pairwise_stream(ctx) == 0);
+        const size_t smem = static_cast<size_t>(plan.stages) * (plan.a_count + plan.b_count) * mvs::kUmTile + 1024 + 256;
+        PW_CUDA(ctx, cudaFuncSetAttribute(mvs::pairwise_dot_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        const dim3 grid(static_cast<unsigned>(nseg), static_cast<unsigned>((mi + mvs::kUmBM - 1) / mvs::kUmBM));
+        mvs::pairwise_dot_umma_kernel<<<grid, mvs::kUmThreads, smem, st>>>(A.tmap, B.tmap, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C,
+                                                                        ldc);
+    } else if (A.P > 0) {                        // warp-level mma.sync limb GEMM
         const mvs::ImmaPlan plan = make_plan(A.P, B.P);
         const dim3 grid(static_cast<unsigned>((mj + mvs::kImBN - 1) / mvs::kImBN), static_cast<unsigned>((mi + mvs::kImBM - 1) / mvs::kImBM));
         mvs::pairwise_dot_imma_kernel<<<grid, mvs::kImThreads, mvs::kImSmemBytes, st>>>(
@@ -137,16 +201,15 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
     }
     PW_CUDA(ctx, cudaGetLastError());
     PW_CUDA(ctx, cudaEventRecord(e1, st));
-    const int nseg = static_cast<int>((mj + mvs::kPwSeg - 1) / mvs::kPwSeg);
-    const unsigned seg_ctas = static_cast<unsigned>((mi * nseg + 7) / 8);
     mvs::pairwise_count_kernel<<<seg_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_segcount, nseg);
     PW_CUDA(ctx, cudaGetLastError());
+    mvs_internal_count_launches(ctx, 1);
     mvs::pairwise_scan_kernel<<<1, 1024, 0, st>>>(d_segcount, nseg, d_rowoff, mi);
     PW_CUDA(ctx, cudaGetLastError());
     unsigned long long total = 0;
     PW_CUDA(ctx, cudaMemcpyAsync(&total, d_rowoff + mi, sizeof total, cudaMemcpyDeviceToHost, st));
     PW_CUDA(ctx, cudaStreamSynchronize(st));
-    mvs_internal_count_launches(ctx, 3);
+    mvs_internal_count_launches(ctx, 2);
     d2h_bytes += sizeof total;
 
     if (total) {

@@ -32,7 +32,7 @@ __device__ __forceinline__ bool pw_keep(int32_t dot, int d, double ni, double nj
     const double threshold = 0.05 * (ni + nj);
     if (threshold >= 0.0) {
         if (threshold >= 2147483647.0) return false;                  // |q| <= 2^31
-        const long long need = (static_cast<long long>(threshold) + 1) * d;   // floor == trunc for >= 0
+        const long long need = (static_cast<long long>(__double2int_rd(threshold)) + 1) * d;   // one F2I instead of a 64-bit conversion
         return static_cast<long long>(dot) >= need;
     }
     const int q = dot / d;                                            // same truncation as int64 / int

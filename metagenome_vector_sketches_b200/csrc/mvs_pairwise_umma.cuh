@@ -1,0 +1,195 @@
+// mvs_pairwise_umma.cuh -- the limb GEMM of the all-pairs comparison on the 5th-generation tensor cores
+// (tcgen05.mma kind::i8, accumulators in TMEM, operands staged by TMA with the 128-byte swizzle); default path of
+// mvs_pairwise_block / mvs_pairwise_shard.  Math and limb decomposition: see mvs_pairwise.cuh.
+//
+//   C[i][j] = sum over limb pairs (p, q), p + q <= 3, of 256^(p+q) * sum_k A_p[i][k] * B_q[j][k]      (mod 2^32)
+//
+// One CTA = one 128 x 128 tile of C, 192 threads: warp 0 (one lane) = TMA producer, warp 1 (one lane) = MMA issuer,
+// warps 2..5 = epilogue.  Every weight s = p + q owns its own 128-column int32 accumulator in TMEM (<= 4 weights =
+// the SM's 512 columns), so limb pairs may run in any order and the Horner combine v = (v << 8) + acc_s happens
+// once, in the epilogue, on the way from TMEM to registers.  Because of that freedom a pipeline stage holds ALL limb
+// planes of one 128-byte k-slice (FUSED, when they fit: PA + PB <= 4, i.e. the normal 2-limb case) and every staged
+// byte feeds up to four MMAs; with more limbs the planes are streamed pair by pair (STREAM).  The kernel is bound
+// by L2 -> shared-memory operand traffic, which FUSED halves.
+// The epilogue only combines and stores: with one CTA per SM it is serialised with the main loop, so the keep-test
+// stays in the massively parallel pairwise_count_kernel (fusing it here cost 1 ms per 10^8 pairs, the separate pass
+// costs 0.15 ms).
+#pragma once
+#include <cstdint>
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include "mvs_pairwise.cuh"
+
+namespace mvs {
+
+constexpr int kUmBM = 128, kUmBN = 128, kUmBKB = 128, kUmK = 32;     // k in bytes (= int8 elements)
+constexpr int kUmTile = kUmBM * kUmBKB;                              // 16 KB: one plane tile of A or of B
+constexpr int kUmThreads = 192;
+constexpr int kUmTmemCols = 512;
+constexpr int kUmSmemBudget = 200 * 1024;
+
+struct UmmaPlan {
+    int ngroups;                                 // FUSED: 1, STREAM: number of limb pairs
+    int a_count, b_count;                        // planes of A / of B per stage
+    int stages;
+    int smax;                                    // highest weight p + q in use
+    unsigned char a_first[10], b_first[10];      // first plane of each group
+};
+
+__device__ __forceinline__ uint32_t um_smem(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void um_mbar_init(uint32_t bar, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count)); }
+__device__ __forceinline__ void um_mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void um_mbar_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok = 0;
+    unsigned long long spins = 0;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (!ok && ++spins > (1ull << 28)) __trap();                  // a lost arrival must not hang the GPU
+    } while (!ok);
+}
+__device__ __forceinline__ void um_tma_load_3d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1, int c2)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+// shared-memory matrix descriptor: K-major, 128-byte swizzle, 8-row groups 1024 bytes apart, sm_100 descriptor version
+__device__ __forceinline__ uint64_t um_desc_sw128(uint32_t addr)
+{
+    return static_cast<uint64_t>((addr & 0x3FFFFu) >> 4) | (static_cast<uint64_t>(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+__device__ __forceinline__ void um_mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void um_commit(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void um_tmem_ld32(uint32_t taddr, uint32_t (&r)[32])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]),
+                   "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+                   "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// grid = (ceil(mj / 128), ceil(mi / 128)); A rows start at plane row a_row0 (any row: the planes carry a zero tile
+// of padding).
+__global__ void __launch_bounds__(kUmThreads, 1)
+pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, UmmaPlan plan, int k_pad,
+                         int a_row0, int64_t mi, int64_t mj, int32_t* __restrict__ C, int64_t ldc)
+{
+    extern __shared__ uint8_t um_smem_raw[];
+    const uint32_t base = (um_smem(um_smem_raw) + 1023u) & ~1023u;     // SW128 tiles need 1024-byte alignment
+    uint8_t* gen = um_smem_raw + (base - um_smem(um_smem_raw));
+    const int stage_bytes = (plan.a_count + plan.b_count) * kUmTile;
+    const int stages = plan.stages;
+    const uint32_t bars = base + stages * stage_bytes;                 // full[stages], empty[stages], tmem_full
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gen + stages * stage_bytes + (2 * stages + 1) * 8);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < stages; ++s) { um_mbar_init(bars + s * 8, 1); um_mbar_init(bars + (stages + s) * 8, 1); }
+        um_mbar_init(bars + 2 * stages * 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(um_smem(tmem_slot)), "r"(kUmTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int nkb = k_pad / kUmBKB;
+    if (warp == 0) {
+        if (lane == 0) {                                               // ---- TMA producer ----
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int g = 0; g < plan.ngroups; ++g)
+                for (int kb = 0; kb < nkb; ++kb) {
+                    um_mbar_wait(bars + (stages + stage) * 8, phase ^ 1);
+                    um_mbar_expect_tx(bars + stage * 8, static_cast<uint32_t>(stage_bytes));
+                    const uint32_t st = base + stage * stage_bytes;
+                    for (int i = 0; i < plan.a_count; ++i)
+                        um_tma_load_3d(st + i * kUmTile, &tmA, bars + stage * 8, kb * kUmBKB, a_row0 + static_cast<int>(blockIdx.y) * kUmBM,
+                                       plan.a_first[g] + i);
+                    for (int j = 0; j < plan.b_count; ++j)
+                        um_tma_load_3d(st + (plan.a_count + j) * kUmTile, &tmB, bars + stage * 8, kb * kUmBKB,
+                                       static_cast<int>(blockIdx.x) * kUmBN, plan.b_first[g] + j);
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {                                               // ---- MMA issuer ----
+            // instruction descriptor: D = S32 (2 << 4), A and B signed 8 bit (1 << 7, 1 << 10), both K-major, N >> 3, M >> 4
+            const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(kUmBN >> 3) << 17) |
+                                   (static_cast<uint32_t>(kUmBM >> 4) << 24);
+            int stage = 0;
+            uint32_t phase = 0, started = 0;
+            for (int g = 0; g < plan.ngroups; ++g)
+                for (int kb = 0; kb < nkb; ++kb) {
+                    um_mbar_wait(bars + stage * 8, phase);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t st = base + stage * stage_bytes;
+                    for (int i = 0; i < plan.a_count; ++i)
+                        for (int j = 0; j < plan.b_count; ++j) {
+                            const int s = plan.a_first[g] + i + plan.b_first[g] + j;
+                            if (s > 3) continue;                       // 256^s vanishes modulo 2^32
+                            const uint32_t tacc = tmem_base + static_cast<uint32_t>(s * kUmBN);
+                            const uint32_t a0 = st + i * kUmTile, b0 = st + (plan.a_count + j) * kUmTile;
+#pragma unroll
+                            for (int k = 0; k < kUmBKB / kUmK; ++k) {
+                                um_mma_i8(tacc, um_desc_sw128(a0 + k * kUmK), um_desc_sw128(b0 + k * kUmK), idesc, (started >> s) & 1u);
+                                started |= 1u << s;
+                            }
+                        }
+                    um_commit(bars + (stages + stage) * 8);            // frees the stage when these MMAs are done
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
+            um_commit(bars + 2 * stages * 8);                          // all accumulators complete
+        }
+    } else {                                                           // ---- epilogue: TMEM -> Horner -> C ----
+        um_mbar_wait(bars + 2 * stages * 8, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int q = warp & 3;                                        // TMEM lane quarter this warp may read
+        const int64_t row = static_cast<int64_t>(blockIdx.y) * kUmBM + q * 32 + lane;
+        for (int c0 = 0; c0 < kUmBN; c0 += 32) {
+            uint32_t v[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) v[e] = 0;
+            for (int s = plan.smax; s >= 0; --s) {
+                uint32_t r[32];
+                um_tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(s * kUmBN + c0), r);
+#pragma unroll
+                for (int e = 0; e < 32; ++e) v[e] = (v[e] << 8) + r[e];
+            }
+            const int64_t col = static_cast<int64_t>(blockIdx.x) * kUmBN + c0;
+            if (row < mi) {
+                int32_t* dst = C + row * ldc + col;
+                if (col + 31 < mj) {                                   // ldc % 4 == 0, C 16-byte aligned (host)
+#pragma unroll
+                    for (int e = 0; e < 32; e += 4) *reinterpret_cast<int4*>(dst + e) = make_int4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+                } else {
+                    for (int e = 0; e < 32; ++e)
+                        if (col + e < mj) dst[e] = static_cast<int32_t>(v[e]);
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kUmTmemCols) : "memory");
+}
+
+}  // namespace mvs

@@ -13,13 +13,17 @@ from oracle_util import (load_toy_ref, norms_sq_like_reference, oracle_pairwise,
 pytestmark = pytest.mark.gpu
 
 
-# every test runs on the tensor-core limb GEMM (limbs from the data, and forced to 3 and 4 limbs = 8 and 10
-# limb products) and on the IMAD GEMM: all four must give the reference's bits
-@pytest.fixture(scope="module", params=["imma", "imma3", "imma4", "imad"])
+# every test runs on the tcgen05 limb GEMM (limbs from the data = FUSED stages, and forced to 3 and 4 limbs = 8 and
+# 10 limb products streamed pair by pair), on the mma.sync limb GEMM and on the IMAD GEMM: all must give the
+# reference's bits
+PATHS = {"umma": (0, 0), "umma3": (0, 3), "umma4": (0, 4), "mma": (2, 0), "mma4": (2, 4), "imad": (1, 0)}
+
+
+@pytest.fixture(scope="module", params=list(PATHS))
 def sk(request):
     s = mvs.Sketcher(0)
-    s.set_option("pairwise_path", 1 if request.param == "imad" else 0)
-    s.set_option("pairwise_limbs", {"imma": 0, "imma3": 3, "imma4": 4, "imad": 0}[request.param])
+    s.set_option("pairwise_path", PATHS[request.param][0])
+    s.set_option("pairwise_limbs", PATHS[request.param][1])
     yield s
     s.close()
 
