@@ -204,8 +204,11 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
     mvs::pairwise_count_kernel<<<seg_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_segcount, nseg);
     PW_CUDA(ctx, cudaGetLastError());
     mvs_internal_count_launches(ctx, 1);
-    mvs::pairwise_scan_kernel<<<1, 1024, 0, st>>>(d_segcount, nseg, d_rowoff, mi);
+    mvs::pairwise_rowsum_kernel<<<static_cast<unsigned>((mi + 7) / 8), 256, 0, st>>>(d_segcount, nseg, d_rowoff, mi);
     PW_CUDA(ctx, cudaGetLastError());
+    mvs::pairwise_scan_kernel<<<1, 1024, 0, st>>>(d_rowoff, mi);
+    PW_CUDA(ctx, cudaGetLastError());
+    mvs_internal_count_launches(ctx, 1);
     unsigned long long total = 0;
     PW_CUDA(ctx, cudaMemcpyAsync(&total, d_rowoff + mi, sizeof total, cudaMemcpyDeviceToHost, st));
     PW_CUDA(ctx, cudaStreamSynchronize(st));

@@ -358,7 +358,7 @@ pairwise_dot_imma_kernel(const int8_t* __restrict__ Ap, int64_t a_plane_stride, 
 // Threshold + ordered compaction.  The columns of a row are cut into segments of 128; one warp owns one
 // (row, segment): lane L holds columns 4L..4L+3 of the segment (one 16-byte load).
 //   pairwise_count_kernel : segcount[row][seg] = kept columns of the segment
-//   pairwise_scan_kernel  : rowoff[row] = exclusive scan of the row totals (single CTA), total in rowoff[mi]
+//   pairwise_rowsum_kernel / pairwise_scan_kernel : rowoff[row] = exclusive scan of the row totals, total in rowoff[mi]
 //   pairwise_emit_kernel  : non-empty segments write their triples at rowoff[row] + sum of the earlier
 //                           segments of the row + rank inside the segment: (row, col) order, no atomics;
 //                           empty segments (almost all of them) do not read C again.
@@ -404,22 +404,28 @@ pairwise_count_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int
     if (lane == 0) segcount[w] = n;
 }
 
-// rowoff[0..mi) = exclusive scan of the row totals of segcount, rowoff[mi] = total.  One CTA of 1024 threads.
+// rowoff[row] = kept columns of the row = sum of its segment counts.  One warp per row.
+__global__ void __launch_bounds__(256)
+pairwise_rowsum_kernel(const uint32_t* __restrict__ segcount, int nseg, unsigned long long* __restrict__ rowoff, int64_t n)
+{
+    const int64_t r = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (r >= n) return;
+    const int lane = threadIdx.x & 31;
+    unsigned long long t = 0;
+    for (int k = lane; k < nseg; k += 32) t += segcount[r * nseg + k];
+#pragma unroll
+    for (int m = 16; m; m >>= 1) t += __shfl_xor_sync(0xffffffffu, t, m);
+    if (lane == 0) rowoff[r] = t;
+}
+
+// In-place exclusive scan of rowoff[0..n), total in rowoff[n].  One CTA of 1024 threads (n <= 8192 rows per call).
 __global__ void __launch_bounds__(1024)
-pairwise_scan_kernel(const uint32_t* __restrict__ segcount, int nseg, unsigned long long* __restrict__ rowoff, int64_t n)
+pairwise_scan_kernel(unsigned long long* __restrict__ rowoff, int64_t n)
 {
     __shared__ unsigned long long warp_sums[32];
     __shared__ unsigned long long carry;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) carry = 0;
-    // row totals first, one warp per row (coalesced reads of the row's segment counts)
-    for (int64_t r = warp; r < n; r += 32) {
-        unsigned long long t = 0;
-        for (int k = lane; k < nseg; k += 32) t += segcount[r * nseg + k];
-#pragma unroll
-        for (int m = 16; m; m >>= 1) t += __shfl_xor_sync(0xffffffffu, t, m);
-        if (lane == 0) rowoff[r] = t;
-    }
     __syncthreads();
     for (int64_t base = 0; base < n; base += 1024) {
         const int64_t i = base + threadIdx.x;

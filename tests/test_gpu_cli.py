@@ -127,3 +127,86 @@ def test_reference_driver_linked_against_our_shim(tmp_path, toy_hash_file):
     ref = load_toy_ref("d2048")
     assert hashlib.sha256((db / "vectors.bin").read_bytes()).hexdigest() == ref["vectors_sha256"]
     assert (db / "vector_norms.txt").read_text() == ref["norms_txt"] or ref_dir() != REFV3
+
+
+PWB = os.path.join(BIN, "pairwise_comp_b200")
+SHARD_FILES = ("matrix.bin", "row_index.bin", "neighbor_start.bin")
+
+
+def _synthetic_db(path, n=700, d=256, seed=5):
+    """A db/ with families of similar vectors (so that most rows have several neighbours), written in the
+    reference's layout with the norms printed like sketch() prints them."""
+    rng = np.random.default_rng(seed)
+    fam = np.rint(rng.normal(0, 120, ((n + 9) // 10, d)))
+    v = (fam[np.arange(n) // 10] + np.rint(rng.normal(0, 70, (n, d)))).astype(np.int32)
+    v[13] = 0                                                           # a zero vector: no neighbours at all, not even itself
+    os.makedirs(path, exist_ok=True)
+    v.tofile(os.path.join(path, "vectors.bin"))
+    open(os.path.join(path, "dimension.txt"), "w").write("%d\n" % d)
+    open(os.path.join(path, "dtype.txt"), "w").write("int32\n")
+    norm = np.sqrt((v.astype(np.float64) ** 2).sum(axis=1) / d)
+    with open(os.path.join(path, "vector_norms.txt"), "w") as f:
+        for i, x in enumerate(norm):
+            f.write("s%04d %g\n" % (i, x))
+    return path + "/"
+
+
+@pytest.mark.parametrize("case", ["toy_one_chunk", "toy_chunks_of_16", "synthetic_shard_1_of_3", "synthetic_small_chunks"])
+def test_pairwise_cli_writes_the_reference_shard_files(tmp_path, toy_hash_file, case):
+    """SURVEY 8f rank 4 end to end: our GPU pairwise CLI against the reference binary on the same db and the same
+    arguments -- matrix.bin / row_index.bin / neighbor_start.bin byte for byte (the row order inside them is the
+    iteration order of an unordered_map fed in the reference's block order, which depends on --max_memory_gb)."""
+    ref = os.path.join(REFV3, "pairwise_comp_optimized")
+    if not (os.path.exists(ref) and os.path.exists(PWB)):
+        pytest.skip("reference pairwise binary / pairwise_comp_b200 not prebuilt")
+    if case.startswith("toy"):
+        db = tmp_path / "db"
+        assert run([PE, "sketch", toy_hash_file, str(db), "-d", "2048", "--quiet"]).returncode == 0
+        db = str(db) + "/"
+        # chunk = max_bytes / (4 d)^2: 12 GB -> 192 vectors (one block); 1 GB -> 16 vectors (4 x 4 blocks of the 61)
+        mem, shards, idx = ("12", "1", "0") if case == "toy_one_chunk" else ("1", "1", "0")
+    else:
+        db = _synthetic_db(str(tmp_path / "sdb"))
+        # d = 256: (4 d)^2 = 2^20 -> 0.1 GB = 102 vectors per chunk, 0.02 GB = 20 per chunk
+        mem, shards, idx = ("0.1", "3", "1") if case == "synthetic_shard_1_of_3" else ("0.02", "2", "0")
+    outs = {}
+    for tag, exe in (("ref", ref), ("ours", PWB)):
+        out = tmp_path / ("mat_" + tag)
+        out.mkdir()
+        r = run([exe, "--db", db, "--output_folder", str(out) + "/", "--max_memory_gb", mem, "--num_threads", "4",
+                 "--num_shards", shards, "--shard_idx", idx])
+        assert r.returncode == 0, r.stdout + r.stderr
+        outs[tag] = {f: (out / ("shard_" + idx) / f).read_bytes() for f in SHARD_FILES}
+        assert "Total computation time" in r.stdout
+    for f in SHARD_FILES:
+        assert len(outs["ref"][f]) > 8 and outs["ours"][f] == outs["ref"][f], (case, f)
+
+
+def test_pairwise_cli_feeds_query_pc_mat_kat4(tmp_path, toy_hash_file):
+    """Our projection -> our pairwise -> the reference's query_pc_mat gives KAT-4's top-10 lists."""
+    q = os.path.join(REFV3, "query_pc_mat")
+    if not (os.path.exists(q) and os.path.exists(PWB)):
+        pytest.skip("query_pc_mat / pairwise_comp_b200 not prebuilt")
+    db = tmp_path / "db"
+    assert run([PE, "sketch", toy_hash_file, str(db), "-d", "2048", "--quiet"]).returncode == 0
+    mat = tmp_path / "mat"
+    mat.mkdir()
+    r = run([PWB, "--db", str(db) + "/", "--output_folder", str(mat) + "/", "--max_memory_gb", "12", "--num_threads", "1",
+             "--num_shards", "1", "--shard_idx", "0"])
+    assert r.returncode == 0, r.stderr
+    qf = tmp_path / "q.txt"
+    qf.write_text("DRR000821\nDRR000837\n")
+    r = run([q, "--matrix", str(mat) + "/", "--db", str(db) + "/", "--query_file", str(qf), "--top", "10", "--print"])
+    assert r.returncode == 0, r.stderr
+    golden = json.load(open(os.path.join(GOLDEN, "pairwise_top10.json")))
+    assert _neighbours(r.stdout) == _neighbours(golden["stdout"])
+
+
+def test_pairwise_cli_grammar(tmp_path):
+    if not os.path.exists(PWB):
+        pytest.skip("pairwise_comp_b200 not prebuilt")
+    assert run([PWB]).returncode == 1                                    # missing required options: usage, exit 1
+    assert run([PWB, "--help"]).returncode == 0
+    r = run([PWB, "--db", str(tmp_path) + "/", "--output_folder", str(tmp_path) + "/", "--max_memory_gb", "1", "--num_threads", "1",
+             "--num_shards", "1", "--shard_idx", "0"])
+    assert r.returncode == 1 and "vector_norms.txt" in r.stderr          # reference :858-861
