@@ -493,7 +493,7 @@ static int sketch_parsed(mvs_ctx* const* ctxs, int n_ctx, mvs_hash_batch* hb, co
         std::printf("Time to compute all projected vectors: %g seconds\n", sec);   // :300-303
         const auto t_projected = std::chrono::steady_clock::now();
         rc = mvs_write_db(dir.c_str(), n, d, hb->names, sumsq.data(), v32, v16);
-        if (std::getenv("MVS_TIMING")) {                                // stage split for tools/cli_bench.py
+        if (std::getenv("MVS_TIMING")) {                                // stage split for tests/perf_cli.py
             const auto t_written = std::chrono::steady_clock::now();
             std::fprintf(stderr,
                          "mvs_timing parse_s=%.6f wait_ctx_s=%.6f project_s=%.6f write_s=%.6f samples=%lld hashes=%llu\n",

@@ -1,11 +1,11 @@
-"""cli_bench.py -- wall-clock of the `project_everything sketch` CLI (parse + project + write db/) on a synthetic
+"""perf_cli.py -- wall-clock of the `project_everything sketch` CLI (parse + project + write db/) on a synthetic
 hash FILE, ours on the GPU next to the reference binary on the host cores (SURVEY 8d CPU baseline (ii)), and a
 byte comparison of the two vectors.bin on the reference's prefix.  Run on the GPU box:
 
-    python tools/cli_bench.py [--samples 2000] [--hashes 50000] [--ref-samples 64] [--d 2048] > gpurun_out/cli_bench.json
+    python tests/perf_cli.py [--samples 2000] [--hashes 50000] [--ref-samples 64] [--d 2048] > gpurun_out/cli_bench.json
 
 The reference binary is oracle/_ref/{native|v3}/project_everything (the unmodified reference sources, built by
-oracle/Makefile); it is only timed and compared here, never linked into the product.  Tooling, not product."""
+oracle/Makefile); it is only timed and compared here, never linked into the product.  Lives under tests/ for that reason; not collected by pytest."""
 import argparse
 import hashlib
 import json

@@ -1,13 +1,13 @@
-"""pairwise_bench.py -- throughput of the all-pairs comparison on a synthetic db, next to the
+"""perf_pairwise.py -- throughput of the all-pairs comparison on a synthetic db, next to the
 reference function (oracle/_ref/*/libref_pairwise.so = the unmodified reference source) on the host cores.
 
-    python tools/pairwise_bench.py [--n 10000] [--d 2048] [--ref-n 768] > gpurun_out/pairwise_bench.json
+    python tests/perf_pairwise.py [--n 10000] [--d 2048] [--ref-n 768] > gpurun_out/pairwise_bench.json
 
 db: n vectors in families of 20 that share a base vector (so that neighbours exist), entries ~ N(0, 220) like the
 projection of ~5e4-hash samples (two base-256 limbs).  value = pairs compared per second (kernel time, db resident in HBM);
 e2e = the same through mvs_pairwise_shard with host buffers (upload + result download inside the timed region).
 Roofline: one IMAD per (pair, dimension) against the live IMAD issue peak (mvs_int_issue_peak(1)).
-Tooling, not product code; the oracle is used only as the checker / CPU baseline."""
+Lives under tests/ because it executes oracle/_ref (the compiled reference) as checker and CPU baseline; not collected by pytest."""
 import argparse
 import json
 import os
@@ -18,7 +18,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))   # oracle_util: the checker / CPU baseline
 
 import metagenome_vector_sketches_b200 as mvs  # noqa: E402
 from metagenome_vector_sketches_b200 import pairwise as pw  # noqa: E402
