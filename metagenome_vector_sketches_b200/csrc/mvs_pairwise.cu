@@ -184,9 +184,14 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
         const mvs::UmmaPlan plan = make_umma_plan(A.P, B.P, mvs_internal_pairwise_stream(ctx) == 0);
         const size_t smem = static_cast<size_t>(plan.stages) * (plan.a_count + plan.b_count) * mvs::kUmTile + 1024 + 256;
         PW_CUDA(ctx, cudaFuncSetAttribute(mvs::pairwise_dot_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-        const dim3 grid(static_cast<unsigned>(nseg), static_cast<unsigned>((mi + mvs::kUmBM - 1) / mvs::kUmBM));
+        const int tiles_n = nseg, tiles_m = static_cast<int>((mi + mvs::kUmBM - 1) / mvs::kUmBM);
+        const int64_t ntiles = static_cast<int64_t>(tiles_n) * tiles_m;
+        if (ntiles > 0x7fffffffLL) return MVS_ERR_TOO_LARGE;
+        int sms = 0;
+        PW_CUDA(ctx, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, mvs_internal_device(ctx)));
+        const unsigned grid = static_cast<unsigned>(std::min<int64_t>(ntiles, sms));    // persistent: one CTA per SM
         mvs::pairwise_dot_umma_kernel<<<grid, mvs::kUmThreads, smem, st>>>(A.tmap, B.tmap, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C,
-                                                                        ldc);
+                                                                        ldc, tiles_n, static_cast<int>(ntiles));
     } else if (A.P > 0) {                        // warp-level mma.sync limb GEMM
         const mvs::ImmaPlan plan = make_plan(A.P, B.P);
         const dim3 grid(static_cast<unsigned>((mj + mvs::kImBN - 1) / mvs::kImBN), static_cast<unsigned>((mi + mvs::kImBM - 1) / mvs::kImBM));

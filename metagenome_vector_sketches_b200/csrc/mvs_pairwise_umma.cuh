@@ -4,16 +4,15 @@
 //
 //   C[i][j] = sum over limb pairs (p, q), p + q <= 3, of 256^(p+q) * sum_k A_p[i][k] * B_q[j][k]      (mod 2^32)
 //
-// One CTA = one 128 x 128 tile of C, 192 threads: warp 0 (one lane) = TMA producer, warp 1 (one lane) = MMA issuer,
-// warps 2..5 = epilogue.  Every weight s = p + q owns its own 128-column int32 accumulator in TMEM (<= 4 weights =
+// Persistent CTAs (one per SM) loop over 128 x 128 tiles of C; 192 threads: warp 0 (one lane) = TMA producer,
+// warp 1 (one lane) = MMA issuer, warps 2..5 = epilogue.  Every weight s = p + q owns its own 128-column int32 accumulator in TMEM (<= 4 weights =
 // the SM's 512 columns), so limb pairs may run in any order and the Horner combine v = (v << 8) + acc_s happens
 // once, in the epilogue, on the way from TMEM to registers.  Because of that freedom a pipeline stage holds ALL limb
 // planes of one 128-byte k-slice (FUSED, when they fit: PA + PB <= 4, i.e. the normal 2-limb case) and every staged
 // byte feeds up to four MMAs; with more limbs the planes are streamed pair by pair (STREAM).  The kernel is bound
 // by L2 -> shared-memory operand traffic, which FUSED halves.
-// The epilogue only combines and stores: with one CTA per SM it is serialised with the main loop, so the keep-test
-// stays in the massively parallel pairwise_count_kernel (fusing it here cost 1 ms per 10^8 pairs, the separate pass
-// costs 0.15 ms).
+// The epilogue only combines and stores, and it frees TMEM as soon as its row is in registers: the keep-test stays
+// in the massively parallel pairwise_count_kernel (fusing it here cost 1 ms per 10^8 pairs, the separate pass 0.15 ms).
 #pragma once
 #include <cstdint>
 #include <cuda.h>
@@ -82,24 +81,32 @@ __device__ __forceinline__ void um_tmem_ld32(uint32_t taddr, uint32_t (&r)[32])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// grid = (ceil(mj / 128), ceil(mi / 128)); A rows start at plane row a_row0 (any row: the planes carry a zero tile
-// of padding).
+__device__ __forceinline__ void um_mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
+
+// Persistent: grid = min(#tiles, #SMs); CTA c owns tiles c, c + grid, ... (row-major over the tile grid, so the CTAs
+// running together share a couple of A row-blocks and stream B from L2).  A rows start at plane row a_row0 (any row:
+// the planes carry a zero tile of padding).  The three roles run decoupled across tiles: the producer keeps the
+// stage ring full while the epilogue of the previous tile drains TMEM, the MMA issuer restarts as soon as the
+// epilogue has COPIED the accumulators to registers (tmem_empty), and the global stores of a tile overlap the
+// main loop of the next one.
 __global__ void __launch_bounds__(kUmThreads, 1)
 pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, UmmaPlan plan, int k_pad,
-                         int a_row0, int64_t mi, int64_t mj, int32_t* __restrict__ C, int64_t ldc)
+                         int a_row0, int64_t mi, int64_t mj, int32_t* __restrict__ C, int64_t ldc, int tiles_n, int ntiles)
 {
     extern __shared__ uint8_t um_smem_raw[];
     const uint32_t base = (um_smem(um_smem_raw) + 1023u) & ~1023u;     // SW128 tiles need 1024-byte alignment
     uint8_t* gen = um_smem_raw + (base - um_smem(um_smem_raw));
     const int stage_bytes = (plan.a_count + plan.b_count) * kUmTile;
     const int stages = plan.stages;
-    const uint32_t bars = base + stages * stage_bytes;                 // full[stages], empty[stages], tmem_full
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gen + stages * stage_bytes + (2 * stages + 1) * 8);
+    const uint32_t bars = base + stages * stage_bytes;                 // full[stages], empty[stages], tmem_full, tmem_empty
+    const uint32_t bar_tmem_full = bars + 2 * stages * 8, bar_tmem_empty = bar_tmem_full + 8;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gen + stages * stage_bytes + (2 * stages + 2) * 8);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < stages; ++s) { um_mbar_init(bars + s * 8, 1); um_mbar_init(bars + (stages + s) * 8, 1); }
-        um_mbar_init(bars + 2 * stages * 8, 1);
+        um_mbar_init(bar_tmem_full, 1);
+        um_mbar_init(bar_tmem_empty, 4);                               // one arrival per epilogue warp
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -116,19 +123,21 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         if (lane == 0) {                                               // ---- TMA producer ----
             int stage = 0;
             uint32_t phase = 0;
-            for (int g = 0; g < plan.ngroups; ++g)
-                for (int kb = 0; kb < nkb; ++kb) {
-                    um_mbar_wait(bars + (stages + stage) * 8, phase ^ 1);
-                    um_mbar_expect_tx(bars + stage * 8, static_cast<uint32_t>(stage_bytes));
-                    const uint32_t st = base + stage * stage_bytes;
-                    for (int i = 0; i < plan.a_count; ++i)
-                        um_tma_load_3d(st + i * kUmTile, &tmA, bars + stage * 8, kb * kUmBKB, a_row0 + static_cast<int>(blockIdx.y) * kUmBM,
-                                       plan.a_first[g] + i);
-                    for (int j = 0; j < plan.b_count; ++j)
-                        um_tma_load_3d(st + (plan.a_count + j) * kUmTile, &tmB, bars + stage * 8, kb * kUmBKB,
-                                       static_cast<int>(blockIdx.x) * kUmBN, plan.b_first[g] + j);
-                    if (++stage == stages) { stage = 0; phase ^= 1; }
-                }
+            for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+                const int tile_m = t / tiles_n, tile_n = t - tile_m * tiles_n;
+                for (int g = 0; g < plan.ngroups; ++g)
+                    for (int kb = 0; kb < nkb; ++kb) {
+                        um_mbar_wait(bars + (stages + stage) * 8, phase ^ 1);
+                        um_mbar_expect_tx(bars + stage * 8, static_cast<uint32_t>(stage_bytes));
+                        const uint32_t st = base + stage * stage_bytes;
+                        for (int i = 0; i < plan.a_count; ++i)
+                            um_tma_load_3d(st + i * kUmTile, &tmA, bars + stage * 8, kb * kUmBKB, a_row0 + tile_m * kUmBM, plan.a_first[g] + i);
+                        for (int j = 0; j < plan.b_count; ++j)
+                            um_tma_load_3d(st + (plan.a_count + j) * kUmTile, &tmB, bars + stage * 8, kb * kUmBKB, tile_n * kUmBN,
+                                           plan.b_first[g] + j);
+                        if (++stage == stages) { stage = 0; phase ^= 1; }
+                    }
+            }
         }
     } else if (warp == 1) {
         if (lane == 0) {                                               // ---- MMA issuer ----
@@ -136,60 +145,77 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(kUmBN >> 3) << 17) |
                                    (static_cast<uint32_t>(kUmBM >> 4) << 24);
             int stage = 0;
-            uint32_t phase = 0, started = 0;
-            for (int g = 0; g < plan.ngroups; ++g)
-                for (int kb = 0; kb < nkb; ++kb) {
-                    um_mbar_wait(bars + stage * 8, phase);
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint32_t st = base + stage * stage_bytes;
-                    for (int i = 0; i < plan.a_count; ++i)
-                        for (int j = 0; j < plan.b_count; ++j) {
-                            const int s = plan.a_first[g] + i + plan.b_first[g] + j;
-                            if (s > 3) continue;                       // 256^s vanishes modulo 2^32
-                            const uint32_t tacc = tmem_base + static_cast<uint32_t>(s * kUmBN);
-                            const uint32_t a0 = st + i * kUmTile, b0 = st + (plan.a_count + j) * kUmTile;
+            uint32_t phase = 0, tile_phase = 0;
+            for (int t = blockIdx.x; t < ntiles; t += gridDim.x, tile_phase ^= 1) {
+                um_mbar_wait(bar_tmem_empty, tile_phase ^ 1);          // the epilogue has copied the previous tile out of TMEM
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                uint32_t started = 0;
+                for (int g = 0; g < plan.ngroups; ++g)
+                    for (int kb = 0; kb < nkb; ++kb) {
+                        um_mbar_wait(bars + stage * 8, phase);
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        const uint32_t st = base + stage * stage_bytes;
+                        for (int i = 0; i < plan.a_count; ++i)
+                            for (int j = 0; j < plan.b_count; ++j) {
+                                const int s = plan.a_first[g] + i + plan.b_first[g] + j;
+                                if (s > 3) continue;                   // 256^s vanishes modulo 2^32
+                                const uint32_t tacc = tmem_base + static_cast<uint32_t>(s * kUmBN);
+                                const uint32_t a0 = st + i * kUmTile, b0 = st + (plan.a_count + j) * kUmTile;
 #pragma unroll
-                            for (int k = 0; k < kUmBKB / kUmK; ++k) {
-                                um_mma_i8(tacc, um_desc_sw128(a0 + k * kUmK), um_desc_sw128(b0 + k * kUmK), idesc, (started >> s) & 1u);
-                                started |= 1u << s;
+                                for (int k = 0; k < kUmBKB / kUmK; ++k) {
+                                    um_mma_i8(tacc, um_desc_sw128(a0 + k * kUmK), um_desc_sw128(b0 + k * kUmK), idesc, (started >> s) & 1u);
+                                    started |= 1u << s;
+                                }
                             }
-                        }
-                    um_commit(bars + (stages + stage) * 8);            // frees the stage when these MMAs are done
-                    if (++stage == stages) { stage = 0; phase ^= 1; }
-                }
-            um_commit(bars + 2 * stages * 8);                          // all accumulators complete
-        }
-    } else {                                                           // ---- epilogue: TMEM -> Horner -> C ----
-        um_mbar_wait(bars + 2 * stages * 8, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const int q = warp & 3;                                        // TMEM lane quarter this warp may read
-        const int64_t row = static_cast<int64_t>(blockIdx.y) * kUmBM + q * 32 + lane;
-        for (int c0 = 0; c0 < kUmBN; c0 += 32) {
-            uint32_t v[32];
-#pragma unroll
-            for (int e = 0; e < 32; ++e) v[e] = 0;
-            for (int s = plan.smax; s >= 0; --s) {
-                uint32_t r[32];
-                um_tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(s * kUmBN + c0), r);
-#pragma unroll
-                for (int e = 0; e < 32; ++e) v[e] = (v[e] << 8) + r[e];
+                        um_commit(bars + (stages + stage) * 8);        // frees the stage when these MMAs are done
+                        if (++stage == stages) { stage = 0; phase ^= 1; }
+                    }
+                um_commit(bar_tmem_full);                              // all accumulators of this tile complete
             }
-            const int64_t col = static_cast<int64_t>(blockIdx.x) * kUmBN + c0;
-            if (row < mi) {
-                int32_t* dst = C + row * ldc + col;
-                if (col + 31 < mj) {                                   // ldc % 4 == 0, C 16-byte aligned (host)
+        }
+    } else {                                                           // ---- epilogue: TMEM -> Horner -> registers -> C ----
+        const int q = warp & 3;                                        // TMEM lane quarter this warp may read
+        uint32_t tile_phase = 0;
+        for (int t = blockIdx.x; t < ntiles; t += gridDim.x, tile_phase ^= 1) {
+            const int tile_m = t / tiles_n, tile_n = t - tile_m * tiles_n;
+            um_mbar_wait(bar_tmem_full, tile_phase);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            uint32_t v[kUmBN];                                         // this thread's row of the tile: 128 registers
 #pragma unroll
-                    for (int e = 0; e < 32; e += 4) *reinterpret_cast<int4*>(dst + e) = make_int4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+            for (int c0 = 0; c0 < kUmBN; c0 += 32) {
+#pragma unroll
+                for (int e = 0; e < 32; ++e) v[c0 + e] = 0;
+                for (int s = plan.smax; s >= 0; --s) {
+                    uint32_t r[32];
+                    um_tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(s * kUmBN + c0), r);
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) v[c0 + e] = (v[c0 + e] << 8) + r[e];
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) um_mbar_arrive(bar_tmem_empty);             // TMEM may be overwritten; the stores below overlap the next tile
+            const int64_t row = static_cast<int64_t>(tile_m) * kUmBM + q * 32 + lane;
+            if (row < mi) {
+                const int64_t col = static_cast<int64_t>(tile_n) * kUmBN;
+                int32_t* dst = C + row * ldc + col;
+                if (col + kUmBN <= mj) {                               // ldc % 4 == 0, C 16-byte aligned (host)
+#pragma unroll
+                    for (int e = 0; e < kUmBN; e += 4) *reinterpret_cast<int4*>(dst + e) = make_int4(v[e], v[e + 1], v[e + 2], v[e + 3]);
                 } else {
-                    for (int e = 0; e < 32; ++e)
+#pragma unroll
+                    for (int e = 0; e < kUmBN; ++e)
                         if (col + e < mj) dst[e] = static_cast<int32_t>(v[e]);
                 }
             }
         }
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kUmTmemCols) : "memory");
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kUmTmemCols) : "memory");
+    }
 }
 
 }  // namespace mvs
