@@ -13,3 +13,4 @@ void mvs_internal_count_launches(mvs_ctx* ctx, uint64_t n);
 int mvs_internal_pairwise_path(const mvs_ctx* ctx);               // option "pairwise_path"
 int mvs_internal_pairwise_limbs(const mvs_ctx* ctx);              // option "pairwise_limbs"
 int mvs_internal_pairwise_stream(const mvs_ctx* ctx);             // option "pairwise_stream"
+int mvs_internal_pairwise_cluster(const mvs_ctx* ctx);            // option "pairwise_cluster"

@@ -52,7 +52,6 @@ struct Operand {
     int P = 0;
     int64_t n_pad = 0;
     int k_pad = 0;
-    CUtensorMap tmap{};                          // tcgen05 path: 3-D map {k, row, plane}, box 128 B x 128 rows x 1
 };
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (libcuda is not linked directly)
@@ -70,15 +69,54 @@ EncodeTiledFn encode_tiled()
     return fn;
 }
 
-bool make_tensor_map(Operand& op)
+// 3-D map {k, row, plane} over the limb planes; box = 128 bytes of k x box_rows rows x 1 plane, 128-byte swizzle
+bool make_tensor_map(const Operand& op, int box_rows, CUtensorMap* tm)
 {
     EncodeTiledFn enc = encode_tiled();
     if (!enc) return false;
     const cuuint64_t dims[3] = {static_cast<cuuint64_t>(op.k_pad), static_cast<cuuint64_t>(op.n_pad), static_cast<cuuint64_t>(op.P)};
     const cuuint64_t strides[2] = {static_cast<cuuint64_t>(op.k_pad), static_cast<cuuint64_t>(op.k_pad) * static_cast<cuuint64_t>(op.n_pad)};
-    const cuuint32_t box[3] = {mvs::kUmBKB, mvs::kUmBM, 1}, estr[3] = {1, 1, 1};
-    return enc(&op.tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, op.planes.p, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    const cuuint32_t box[3] = {mvs::kUmBKB, static_cast<cuuint32_t>(box_rows), 1}, estr[3] = {1, 1, 1};
+    return enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, op.planes.p, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int CM, int CN>
+cudaError_t launch_umma(cudaStream_t st, int sms, size_t smem, const CUtensorMap& tmA, const CUtensorMap& tmB, const mvs::UmmaPlan& plan,
+                        int k_pad, int a_row0, int64_t mi, int64_t mj, int32_t* d_C, int64_t ldc, int tiles_m, int tiles_n)
+{
+    auto kernel = mvs::pairwise_dot_umma_kernel<CM, CN>;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    constexpr int CS = CM * CN;
+    const int super_m = (tiles_m + CM - 1) / CM, super_n = (tiles_n + CN - 1) / CN;
+    const int64_t nsuper = static_cast<int64_t>(super_m) * super_n;
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim = dim3(mvs::kUmThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CS;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int max_clusters = sms / CS;
+    if (CS > 1) {                                // clusters that can be co-resident (GPC boundaries)
+        cfg.gridDim = dim3(static_cast<unsigned>(sms / CS * CS));
+        int q = 0;
+        if (cudaOccupancyMaxActiveClusters(&q, kernel, &cfg) == cudaSuccess && q > 0) max_clusters = q;
+        else cudaGetLastError();
+    }
+    const int nclusters = static_cast<int>(std::min<int64_t>(nsuper, max_clusters));
+    if (CS == 1) {                               // plain launch, no cluster attribute
+        kernel<<<static_cast<unsigned>(nclusters), mvs::kUmThreads, smem, st>>>(tmA, tmB, plan, k_pad, a_row0, mi, mj, d_C, ldc, super_n,
+                                                                              static_cast<int>(nsuper));
+        return cudaGetLastError();
+    }
+    cfg.gridDim = dim3(static_cast<unsigned>(nclusters * CS));
+    return cudaLaunchKernelEx(&cfg, kernel, tmA, tmB, plan, k_pad, a_row0, mi, mj, d_C, ldc, super_n, static_cast<int>(nsuper));
 }
 
 mvs::UmmaPlan make_umma_plan(int PA, int PB, bool allow_fused)
@@ -137,7 +175,6 @@ int prepare_operand(mvs_ctx* ctx, cudaStream_t st, Operand& op, int d, int* d_mm
         op.v, op.n, d, op.P, op.planes.as<int8_t>(), op.n_pad, op.k_pad);
     PW_CUDA(ctx, cudaGetLastError());
     mvs_internal_count_launches(ctx, 2);
-    if (mvs_internal_pairwise_path(ctx) == 0 && !make_tensor_map(op)) return MVS_ERR_CUDA;
     return MVS_OK;
 }
 
@@ -183,15 +220,23 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
     if (A.P > 0 && mvs_internal_pairwise_path(ctx) == 0) {   // tcgen05 limb GEMM (TMA + TMEM)
         const mvs::UmmaPlan plan = make_umma_plan(A.P, B.P, mvs_internal_pairwise_stream(ctx) == 0);
         const size_t smem = static_cast<size_t>(plan.stages) * (plan.a_count + plan.b_count) * mvs::kUmTile + 1024 + 256;
-        PW_CUDA(ctx, cudaFuncSetAttribute(mvs::pairwise_dot_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
         const int tiles_n = nseg, tiles_m = static_cast<int>((mi + mvs::kUmBM - 1) / mvs::kUmBM);
-        const int64_t ntiles = static_cast<int64_t>(tiles_n) * tiles_m;
-        if (ntiles > 0x7fffffffLL) return MVS_ERR_TOO_LARGE;
+        if (static_cast<int64_t>(tiles_n) * tiles_m > 0x3fffffffLL) return MVS_ERR_TOO_LARGE;
         int sms = 0;
         PW_CUDA(ctx, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, mvs_internal_device(ctx)));
-        const unsigned grid = static_cast<unsigned>(std::min<int64_t>(ntiles, sms));    // persistent: one CTA per SM
-        mvs::pairwise_dot_umma_kernel<<<grid, mvs::kUmThreads, smem, st>>>(A.tmap, B.tmap, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C,
-                                                                        ldc, tiles_n, static_cast<int>(ntiles));
+        // cluster shape: 1 x 1 by default.  Clusters of 1 x 2 / 2 x 2 CTAs sharing operand tiles by TMA multicast (option
+        // "pairwise_cluster" = 2 / 4) halve the L2 reads but are NOT faster: the main loop is bound by the bytes an SM
+        // can take in (~32 B/clk, the same with multicast), see DESIGN.md section 9
+        int cshape = mvs_internal_pairwise_cluster(ctx);
+        if (cshape == 0) cshape = 1;
+        const int cm = cshape == 4 ? 2 : 1, cn = cshape >= 2 ? 2 : 1;
+        CUtensorMap tmA, tmB;
+        if (!make_tensor_map(A, mvs::kUmBM / cn, &tmA) || !make_tensor_map(B, mvs::kUmBN / cm, &tmB)) return MVS_ERR_CUDA;
+        cudaError_t le;
+        if (cshape == 4) le = launch_umma<2, 2>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
+        else if (cshape == 2) le = launch_umma<1, 2>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
+        else le = launch_umma<1, 1>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
+        PW_CUDA(ctx, le);
     } else if (A.P > 0) {                        // warp-level mma.sync limb GEMM
         const mvs::ImmaPlan plan = make_plan(A.P, B.P);
         const dim3 grid(static_cast<unsigned>((mj + mvs::kImBN - 1) / mvs::kImBN), static_cast<unsigned>((mi + mvs::kImBM - 1) / mvs::kImBM));

@@ -82,17 +82,43 @@ __device__ __forceinline__ void um_tmem_ld32(uint32_t taddr, uint32_t (&r)[32])
 }
 
 __device__ __forceinline__ void um_mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
+__device__ __forceinline__ void um_tma_load_3d_mc(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1, int c2, uint16_t mask)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4, %5}], [%2], %6;"
+                 ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void um_commit_mc(uint32_t bar, uint16_t mask)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ uint32_t um_cluster_rank()
+{
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void um_cluster_sync()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 
-// Persistent: grid = min(#tiles, #SMs); CTA c owns tiles c, c + grid, ... (row-major over the tile grid, so the CTAs
-// running together share a couple of A row-blocks and stream B from L2).  A rows start at plane row a_row0 (any row:
-// the planes carry a zero tile of padding).  The three roles run decoupled across tiles: the producer keeps the
-// stage ring full while the epilogue of the previous tile drains TMEM, the MMA issuer restarts as soon as the
-// epilogue has COPIED the accumulators to registers (tmem_empty), and the global stores of a tile overlap the
-// main loop of the next one.
+// Persistent clusters of CM x CN CTAs (1-D grid, cluster = CM * CN consecutive CTAs); a cluster owns a super-tile of
+// (CM * 128) x (CN * 128) outputs, CTA (rm, rn) of it the 128 x 128 tile (rm, rn).  The kernel is bound by L2 -> SM
+// operand traffic, so the CTAs of a cluster row share their A tile and those of a cluster column their B tile: each
+// CTA fetches 1/CN of the A rows and 1/CM of the B rows of a stage and TMA-multicasts them to its peers (2 x 2:
+// half the traffic).  A stage may be refilled once every CTA that receives data from this producer has consumed it,
+// so the MMA commit of a CTA arrives (multicast) on the empty barriers of its row and column peers.
+// The three roles run decoupled across tiles: the producer keeps the stage ring full while the epilogue of the
+// previous tile drains TMEM, the MMA issuer restarts as soon as the epilogue has COPIED the accumulators to registers
+// (tmem_empty), and the global stores of a tile overlap the main loop of the next one.
+// A rows start at plane row a_row0 (any row); tiles past the edge read zeros (TMA out-of-bounds fill) and store nothing.
+template <int CM, int CN>
 __global__ void __launch_bounds__(kUmThreads, 1)
 pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, UmmaPlan plan, int k_pad,
-                         int a_row0, int64_t mi, int64_t mj, int32_t* __restrict__ C, int64_t ldc, int tiles_n, int ntiles)
+                         int a_row0, int64_t mi, int64_t mj, int32_t* __restrict__ C, int64_t ldc, int super_n, int nsuper)
 {
+    constexpr int CS = CM * CN;
+    constexpr int kARows = kUmBM / CN, kBRows = kUmBN / CM;            // rows of a tile this CTA fetches
     extern __shared__ uint8_t um_smem_raw[];
     const uint32_t base = (um_smem(um_smem_raw) + 1023u) & ~1023u;     // SW128 tiles need 1024-byte alignment
     uint8_t* gen = um_smem_raw + (base - um_smem(um_smem_raw));
@@ -102,9 +128,15 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const uint32_t bar_tmem_full = bars + 2 * stages * 8, bar_tmem_empty = bar_tmem_full + 8;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gen + stages * stage_bytes + (2 * stages + 2) * 8);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = CS > 1 ? static_cast<int>(um_cluster_rank()) : 0;
+    const int rm = rank / CN, rn = rank % CN;
+    uint16_t row_mask = 0, col_mask = 0;                               // peers sharing my A tile / my B tile (self included)
+    for (int j = 0; j < CN; ++j) row_mask |= static_cast<uint16_t>(1u << (rm * CN + j));
+    for (int i = 0; i < CM; ++i) col_mask |= static_cast<uint16_t>(1u << (i * CN + rn));
+    const int cluster_id = blockIdx.x / CS, nclusters = gridDim.x / CS;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < stages; ++s) { um_mbar_init(bars + s * 8, 1); um_mbar_init(bars + (stages + s) * 8, 1); }
+        for (int s = 0; s < stages; ++s) { um_mbar_init(bars + s * 8, 1); um_mbar_init(bars + (stages + s) * 8, CM + CN - 1); }
         um_mbar_init(bar_tmem_full, 1);
         um_mbar_init(bar_tmem_empty, 4);                               // one arrival per epilogue warp
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -115,6 +147,7 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (CS > 1) um_cluster_sync();                                     // peers' barriers are initialised before any remote arrival
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
 
@@ -123,18 +156,26 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         if (lane == 0) {                                               // ---- TMA producer ----
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-                const int tile_m = t / tiles_n, tile_n = t - tile_m * tiles_n;
+            for (int st_id = cluster_id; st_id < nsuper; st_id += nclusters) {
+                const int sm_ = st_id / super_n, sn_ = st_id - sm_ * super_n;
+                const int tile_m = sm_ * CM + rm, tile_n = sn_ * CN + rn;
                 for (int g = 0; g < plan.ngroups; ++g)
                     for (int kb = 0; kb < nkb; ++kb) {
                         um_mbar_wait(bars + (stages + stage) * 8, phase ^ 1);
                         um_mbar_expect_tx(bars + stage * 8, static_cast<uint32_t>(stage_bytes));
                         const uint32_t st = base + stage * stage_bytes;
-                        for (int i = 0; i < plan.a_count; ++i)
-                            um_tma_load_3d(st + i * kUmTile, &tmA, bars + stage * 8, kb * kUmBKB, a_row0 + tile_m * kUmBM, plan.a_first[g] + i);
-                        for (int j = 0; j < plan.b_count; ++j)
-                            um_tma_load_3d(st + (plan.a_count + j) * kUmTile, &tmB, bars + stage * 8, kb * kUmBKB, tile_n * kUmBN,
-                                           plan.b_first[g] + j);
+                        for (int i = 0; i < plan.a_count; ++i) {
+                            const uint32_t dst = st + i * kUmTile + rn * kARows * kUmBKB;
+                            const int r = a_row0 + tile_m * kUmBM + rn * kARows;
+                            if (CN > 1) um_tma_load_3d_mc(dst, &tmA, bars + stage * 8, kb * kUmBKB, r, plan.a_first[g] + i, row_mask);
+                            else um_tma_load_3d(dst, &tmA, bars + stage * 8, kb * kUmBKB, r, plan.a_first[g] + i);
+                        }
+                        for (int j = 0; j < plan.b_count; ++j) {
+                            const uint32_t dst = st + (plan.a_count + j) * kUmTile + rm * kBRows * kUmBKB;
+                            const int r = tile_n * kUmBN + rm * kBRows;
+                            if (CM > 1) um_tma_load_3d_mc(dst, &tmB, bars + stage * 8, kb * kUmBKB, r, plan.b_first[g] + j, col_mask);
+                            else um_tma_load_3d(dst, &tmB, bars + stage * 8, kb * kUmBKB, r, plan.b_first[g] + j);
+                        }
                         if (++stage == stages) { stage = 0; phase ^= 1; }
                     }
             }
@@ -144,9 +185,10 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             // instruction descriptor: D = S32 (2 << 4), A and B signed 8 bit (1 << 7, 1 << 10), both K-major, N >> 3, M >> 4
             const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(kUmBN >> 3) << 17) |
                                    (static_cast<uint32_t>(kUmBM >> 4) << 24);
+            const uint16_t peers = row_mask | col_mask;
             int stage = 0;
             uint32_t phase = 0, tile_phase = 0;
-            for (int t = blockIdx.x; t < ntiles; t += gridDim.x, tile_phase ^= 1) {
+            for (int st_id = cluster_id; st_id < nsuper; st_id += nclusters, tile_phase ^= 1) {
                 um_mbar_wait(bar_tmem_empty, tile_phase ^ 1);          // the epilogue has copied the previous tile out of TMEM
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 uint32_t started = 0;
@@ -167,7 +209,9 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                                     started |= 1u << s;
                                 }
                             }
-                        um_commit(bars + (stages + stage) * 8);        // frees the stage when these MMAs are done
+                        // frees the stage, here and in the peers whose producers write into this CTA
+                        if (CS > 1) um_commit_mc(bars + (stages + stage) * 8, peers);
+                        else um_commit(bars + (stages + stage) * 8);
                         if (++stage == stages) { stage = 0; phase ^= 1; }
                     }
                 um_commit(bar_tmem_full);                              // all accumulators of this tile complete
@@ -176,8 +220,9 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     } else {                                                           // ---- epilogue: TMEM -> Horner -> registers -> C ----
         const int q = warp & 3;                                        // TMEM lane quarter this warp may read
         uint32_t tile_phase = 0;
-        for (int t = blockIdx.x; t < ntiles; t += gridDim.x, tile_phase ^= 1) {
-            const int tile_m = t / tiles_n, tile_n = t - tile_m * tiles_n;
+        for (int st_id = cluster_id; st_id < nsuper; st_id += nclusters, tile_phase ^= 1) {
+            const int sm_ = st_id / super_n, sn_ = st_id - sm_ * super_n;
+            const int tile_m = sm_ * CM + rm, tile_n = sn_ * CN + rn;
             um_mbar_wait(bar_tmem_full, tile_phase);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             uint32_t v[kUmBN];                                         // this thread's row of the tile: 128 registers
@@ -196,8 +241,8 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             __syncwarp();
             if (lane == 0) um_mbar_arrive(bar_tmem_empty);             // TMEM may be overwritten; the stores below overlap the next tile
             const int64_t row = static_cast<int64_t>(tile_m) * kUmBM + q * 32 + lane;
-            if (row < mi) {
-                const int64_t col = static_cast<int64_t>(tile_n) * kUmBN;
+            const int64_t col = static_cast<int64_t>(tile_n) * kUmBN;
+            if (row < mi && col < mj) {
                 int32_t* dst = C + row * ldc + col;
                 if (col + kUmBN <= mj) {                               // ldc % 4 == 0, C 16-byte aligned (host)
 #pragma unroll
@@ -212,6 +257,7 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (CS > 1) um_cluster_sync();                                     // no CTA leaves while a peer may still multicast into it
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kUmTmemCols) : "memory");

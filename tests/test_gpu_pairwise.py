@@ -13,10 +13,11 @@ from oracle_util import (load_toy_ref, norms_sq_like_reference, oracle_pairwise,
 pytestmark = pytest.mark.gpu
 
 
-# every test runs on the tcgen05 limb GEMM (limbs from the data = FUSED stages, and forced to 3 and 4 limbs = 8 and
-# 10 limb products streamed pair by pair), on the mma.sync limb GEMM and on the IMAD GEMM: all must give the
-# reference's bits
-PATHS = {"umma": (0, 0), "umma3": (0, 3), "umma4": (0, 4), "mma": (2, 0), "mma4": (2, 4), "imad": (1, 0)}
+# every test runs on the tcgen05 limb GEMM (limbs from the data = FUSED stages, forced to 3 and 4 limbs = 8 and 10 limb
+# products streamed pair by pair; also as clusters of 1 x 2 and 2 x 2 CTAs with TMA multicast), on the mma.sync limb GEMM
+# and on the IMAD GEMM: all must give the reference's bits
+PATHS = {"umma": (0, 0, 0), "umma3": (0, 3, 0), "umma4": (0, 4, 0), "umma_1x2": (0, 0, 2), "umma_2x2": (0, 0, 4), "umma4_2x2": (0, 4, 4),
+         "mma": (2, 0, 0), "mma4": (2, 4, 0), "imad": (1, 0, 0)}
 
 
 @pytest.fixture(scope="module", params=list(PATHS))
@@ -24,6 +25,7 @@ def sk(request):
     s = mvs.Sketcher(0)
     s.set_option("pairwise_path", PATHS[request.param][0])
     s.set_option("pairwise_limbs", PATHS[request.param][1])
+    s.set_option("pairwise_cluster", PATHS[request.param][2])
     yield s
     s.close()
 

@@ -157,6 +157,63 @@ umma_limb_gemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
 }
 
+// MMA-only issue-rate probe: no TMA, the operands are whatever is in shared memory; one CTA per SM issues
+// iters x 4 MMAs of 128 x N x 32 (N = 64 / 128 / 256) into TMEM and waits for the commit.
+template <int N>
+__global__ void __launch_bounds__(128, 1) umma_rate_kernel(int iters)
+{
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    __shared__ uint64_t bar;
+    __shared__ uint32_t slot;
+    const int warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { mbar_init(smem_u32(&bar), 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&slot)), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = slot;
+    if (threadIdx.x == 0) {
+        const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(BM >> 4) << 24);
+        for (int it = 0; it < iters; ++it)
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                umma_i8(tmem_base + (it & 1) * N, smem_desc_sw128(base + k * UMMA_K), smem_desc_sw128(base + 32768 + k * UMMA_K), idesc, 1u);
+        umma_commit(smem_u32(&bar));
+        mbar_wait(smem_u32(&bar), 0);
+    }
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+}
+
+template <int N>
+static void run_rate()
+{
+    const size_t smem = 32768 + 256 * 128 + 2048;
+    CK(cudaFuncSetAttribute(umma_rate_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    const int iters = 20000;
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+        CK(cudaEventRecord(e0));
+        umma_rate_kernel<N><<<148, 128, smem>>>(iters);
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        CK(cudaGetLastError());
+        float ms;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep && ms < best) best = ms;
+    }
+    const double macs = 148.0 * iters * 4 * 128.0 * N * 32;
+    printf("tcgen05.mma kind::i8 128 x %3d x 32, issue only: %8.3f ms  %7.1f T MAC/s  (%.1f clk per MMA)\n", N, best, macs / (best * 1e-3) / 1e12,
+           best * 1e-3 * 1.965e9 / (iters * 4.0));
+}
+
 // ---------------------------------------------------------------- host ----------------------------------------------------------------
 typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                 const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -244,6 +301,10 @@ int main(int argc, char** argv)
         cudaFree(dA); cudaFree(dB); cudaFree(dC);
     }
     if (bad || (argc > 1 && !strcmp(argv[1], "check"))) return bad;
+
+    run_rate<64>();
+    run_rate<128>();
+    run_rate<256>();
 
     // ---- timing: one 8192-row block of a 10000-vector db, d = 2048 ----
     for (int P = 1; P <= 4; P += (P == 2 ? 2 : 1)) {
