@@ -14,3 +14,4 @@ int mvs_internal_pairwise_path(const mvs_ctx* ctx);               // option "pai
 int mvs_internal_pairwise_limbs(const mvs_ctx* ctx);              // option "pairwise_limbs"
 int mvs_internal_pairwise_stream(const mvs_ctx* ctx);             // option "pairwise_stream"
 int mvs_internal_pairwise_cluster(const mvs_ctx* ctx);            // option "pairwise_cluster"
+int mvs_internal_pairwise_pair(const mvs_ctx* ctx);               // option "pairwise_pair"

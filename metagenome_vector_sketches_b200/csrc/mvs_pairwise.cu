@@ -9,6 +9,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -81,11 +82,11 @@ bool make_tensor_map(const Operand& op, int box_rows, CUtensorMap* tm)
                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-template <int CM, int CN>
+template <int CM, int CN, bool F22>
 cudaError_t launch_umma(cudaStream_t st, int sms, size_t smem, const CUtensorMap& tmA, const CUtensorMap& tmB, const mvs::UmmaPlan& plan,
                         int k_pad, int a_row0, int64_t mi, int64_t mj, int32_t* d_C, int64_t ldc, int tiles_m, int tiles_n)
 {
-    auto kernel = mvs::pairwise_dot_umma_kernel<CM, CN>;
+    auto kernel = mvs::pairwise_dot_umma_kernel<CM, CN, F22>;
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return e;
     constexpr int CS = CM * CN;
@@ -117,6 +118,38 @@ cudaError_t launch_umma(cudaStream_t st, int sms, size_t smem, const CUtensorMap
     }
     cfg.gridDim = dim3(static_cast<unsigned>(nclusters * CS));
     return cudaLaunchKernelEx(&cfg, kernel, tmA, tmB, plan, k_pad, a_row0, mi, mj, d_C, ldc, super_n, static_cast<int>(nsuper));
+}
+
+// CTA pairs (tcgen05 cta_group::2): one cluster of two CTAs per 256 x 128 super-tile
+cudaError_t launch_umma_pair(cudaStream_t st, int sms, const CUtensorMap& tmA, const CUtensorMap& tmB, mvs::UmmaPlan plan, int k_pad,
+                             int a_row0, int a_row_last, int64_t mi, int64_t mj, int32_t* d_C, int64_t ldc, int tiles_m, int tiles_n)
+{
+    const bool f22 = plan.ngroups == 1 && plan.a_count == 2 && plan.b_count == 2;
+    auto kernel = f22 ? mvs::pairwise_dot_umma_pair_kernel<true> : mvs::pairwise_dot_umma_pair_kernel<false>;
+    const int stage_bytes = plan.a_count * mvs::kUmTile + plan.b_count * mvs::kUmPairBTile;
+    plan.stages = std::max(2, std::min(8, mvs::kUmSmemBudget / stage_bytes));
+    const size_t smem = static_cast<size_t>(plan.stages) * stage_bytes + 1024 + 256;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    const int64_t nsuper = static_cast<int64_t>((tiles_m + 1) / 2) * tiles_n;
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim = dim3(mvs::kUmThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cfg.gridDim = dim3(static_cast<unsigned>(sms / 2 * 2));
+    int max_pairs = sms / 2, q = 0;
+    if (cudaOccupancyMaxActiveClusters(&q, kernel, &cfg) == cudaSuccess && q > 0) max_pairs = std::min(max_pairs, q);
+    else cudaGetLastError();
+    const int npairs = static_cast<int>(std::min<int64_t>(nsuper, max_pairs));
+    cfg.gridDim = dim3(static_cast<unsigned>(npairs * 2));
+    return cudaLaunchKernelEx(&cfg, kernel, tmA, tmB, plan, k_pad, a_row0, a_row_last, mi, mj, d_C, ldc, tiles_n, static_cast<int>(nsuper));
 }
 
 mvs::UmmaPlan make_umma_plan(int PA, int PB, bool allow_fused)
@@ -218,7 +251,10 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
     const unsigned seg_ctas = static_cast<unsigned>((mi * nseg + 7) / 8);
     PW_CUDA(ctx, cudaEventRecord(e0, st));
     if (A.P > 0 && mvs_internal_pairwise_path(ctx) == 0) {   // tcgen05 limb GEMM (TMA + TMEM)
-        const mvs::UmmaPlan plan = make_umma_plan(A.P, B.P, mvs_internal_pairwise_stream(ctx) == 0);
+        mvs::UmmaPlan plan = make_umma_plan(A.P, B.P, mvs_internal_pairwise_stream(ctx) == 0);
+#ifdef MVS_UMMA_PROBE                            // diagnostic build only: switch kernel roles off (wrong results), see UmmaPlan::probe
+        if (const char* e = std::getenv("MVS_UMMA_PROBE")) plan.probe = std::atoi(e);
+#endif
         const size_t smem = static_cast<size_t>(plan.stages) * (plan.a_count + plan.b_count) * mvs::kUmTile + 1024 + 256;
         const int tiles_n = nseg, tiles_m = static_cast<int>((mi + mvs::kUmBM - 1) / mvs::kUmBM);
         if (static_cast<int64_t>(tiles_n) * tiles_m > 0x3fffffffLL) return MVS_ERR_TOO_LARGE;
@@ -230,13 +266,33 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
         int cshape = mvs_internal_pairwise_cluster(ctx);
         if (cshape == 0) cshape = 1;
         const int cm = cshape == 4 ? 2 : 1, cn = cshape >= 2 ? 2 : 1;
+        if (mvs_internal_pairwise_pair(ctx) == 1 && cshape == 1) {
+            CUtensorMap tmA, tmB;
+            if (!make_tensor_map(A, mvs::kUmBM, &tmA) || !make_tensor_map(B, mvs::kUmBN / 2, &tmB)) return MVS_ERR_CUDA;
+            PW_CUDA(ctx, launch_umma_pair(st, sms, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), static_cast<int>(A.n_pad - mvs::kUmBM), mi,
+                                          mj, d_C, ldc, tiles_m, tiles_n));
+        } else {
         CUtensorMap tmA, tmB;
         if (!make_tensor_map(A, mvs::kUmBM / cn, &tmA) || !make_tensor_map(B, mvs::kUmBN / cm, &tmB)) return MVS_ERR_CUDA;
         cudaError_t le;
-        if (cshape == 4) le = launch_umma<2, 2>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
-        else if (cshape == 2) le = launch_umma<1, 2>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
-        else le = launch_umma<1, 1>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
+        const bool f22 = plan.ngroups == 1 && plan.a_count == 2 && plan.b_count == 2;
+        if (cshape == 4) le = launch_umma<2, 2, false>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
+        else if (cshape == 2) le = launch_umma<1, 2, false>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
+        else if (f22) le = launch_umma<1, 1, true>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
+        else le = launch_umma<1, 1, false>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
         PW_CUDA(ctx, le);
+#ifdef MVS_UMMA_PROBE
+        if (cshape == 1 && std::getenv("MVS_UMMA_PROBE_PRINT")) {
+            static unsigned long long h[1024][4];
+            PW_CUDA(ctx, cudaStreamSynchronize(st));
+            PW_CUDA(ctx, cudaMemcpyFromSymbol(h, mvs::um_probe_cycles, sizeof h));
+            double a[4] = {0, 0, 0, 0};
+            const int n = static_cast<int>(std::min<int64_t>(static_cast<int64_t>(tiles_m) * tiles_n, sms));
+            for (int b = 0; b < n; ++b) for (int k = 0; k < 4; ++k) a[k] += static_cast<double>(h[b][k]) / n;
+            std::fprintf(stderr, "[umma probe] per CTA: wait tmem_empty %.0f clk, wait full %.0f clk, total %.0f clk, tiles %.1f\n", a[0], a[1], a[2], a[3]);
+        }
+#endif
+        }
     } else if (A.P > 0) {                        // warp-level mma.sync limb GEMM
         const mvs::ImmaPlan plan = make_plan(A.P, B.P);
         const dim3 grid(static_cast<unsigned>((mj + mvs::kImBN - 1) / mvs::kImBN), static_cast<unsigned>((mi + mvs::kImBM - 1) / mvs::kImBM));

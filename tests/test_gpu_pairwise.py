@@ -16,8 +16,10 @@ pytestmark = pytest.mark.gpu
 # every test runs on the tcgen05 limb GEMM (limbs from the data = FUSED stages, forced to 3 and 4 limbs = 8 and 10 limb
 # products streamed pair by pair; also as clusters of 1 x 2 and 2 x 2 CTAs with TMA multicast), on the mma.sync limb GEMM
 # and on the IMAD GEMM: all must give the reference's bits
-PATHS = {"umma": (0, 0, 0), "umma3": (0, 3, 0), "umma4": (0, 4, 0), "umma_1x2": (0, 0, 2), "umma_2x2": (0, 0, 4), "umma4_2x2": (0, 4, 4),
-         "mma": (2, 0, 0), "mma4": (2, 4, 0), "imad": (1, 0, 0)}
+# "pair" = tcgen05 cta_group::2 (two SMs per 256 x 128 tile); fourth entry = option "pairwise_pair" (2 = single CTAs)
+PATHS = {"umma": (0, 0, 0, 2), "umma3": (0, 3, 0, 2), "umma4": (0, 4, 0, 2), "umma_1x2": (0, 0, 2, 2), "umma_2x2": (0, 0, 4, 2),
+         "umma4_2x2": (0, 4, 4, 2), "pair": (0, 0, 0, 1), "pair3": (0, 3, 0, 1), "pair4": (0, 4, 0, 1),
+         "mma": (2, 0, 0, 0), "mma4": (2, 4, 0, 0), "imad": (1, 0, 0, 0)}
 
 
 @pytest.fixture(scope="module", params=list(PATHS))
@@ -26,6 +28,7 @@ def sk(request):
     s.set_option("pairwise_path", PATHS[request.param][0])
     s.set_option("pairwise_limbs", PATHS[request.param][1])
     s.set_option("pairwise_cluster", PATHS[request.param][2])
+    s.set_option("pairwise_pair", PATHS[request.param][3])
     yield s
     s.close()
 
