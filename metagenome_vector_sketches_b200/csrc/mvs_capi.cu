@@ -28,6 +28,7 @@ constexpr int kSlots = 3;                        // slices in flight in mvs_proj
 constexpr int kAbiVersion = 1;
 constexpr int kTimingRing = 64;
 
+constexpr int kPairwiseSlots = 16;
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
@@ -80,6 +81,9 @@ struct mvs_ctx {
     int pairwise_stream = 0;                     // 1 = tcgen05 path streams limb pairs even when the planes would fit one stage
     int pairwise_limbs = 0;                      // 0 = from the operands' min/max, 1..4 = force at least that many limbs
     uint32_t* d_sink = nullptr;
+    DevBuf pw_ws[kPairwiseSlots];                // grow-only device workspace of the pairwise entry points (freed by mvs_destroy
+                                                 // or option "release_workspace"): no cudaMalloc / cudaFree in the steady state
+    void* pw_pinned = nullptr;                   // 256 bytes of pinned host memory for small read-backs
 };
 
 namespace {
@@ -366,6 +370,29 @@ int mvs_internal_pairwise_limbs(const mvs_ctx* ctx) { return ctx->pairwise_limbs
 int mvs_internal_pairwise_stream(const mvs_ctx* ctx) { return ctx->pairwise_stream; }
 int mvs_internal_pairwise_cluster(const mvs_ctx* ctx) { return ctx->pairwise_cluster; }
 int mvs_internal_pairwise_pair(const mvs_ctx* ctx) { return ctx->pairwise_pair; }
+int mvs_internal_workspace(mvs_ctx* ctx, int slot, size_t bytes, void** out)
+{
+    if (slot < 0 || slot >= kPairwiseSlots) return MVS_ERR_INVALID_ARG;
+    const int rc = ensure_dev(ctx, ctx->pw_ws[slot], bytes ? bytes : 16);
+    *out = rc == MVS_OK ? ctx->pw_ws[slot].p : nullptr;
+    return rc;
+}
+void* mvs_internal_pinned_scratch(mvs_ctx* ctx)
+{
+    if (!ctx->pw_pinned && cudaHostAlloc(&ctx->pw_pinned, 256, cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        ctx->pw_pinned = nullptr;
+    }
+    return ctx->pw_pinned;
+}
+static void release_workspace(mvs_ctx* ctx)
+{
+    for (auto& b : ctx->pw_ws) {
+        if (b.p) cudaFree(b.p);
+        b.p = nullptr;
+        b.cap = 0;
+    }
+}
 extern "C" {
 
 int mvs_create(mvs_ctx** out, int device)
@@ -429,6 +456,8 @@ void mvs_destroy(mvs_ctx* ctx)
         for (auto& e : e3)
             if (e) cudaEventDestroy(e);
     if (ctx->d_sink) cudaFree(ctx->d_sink);
+    release_workspace(ctx);
+    if (ctx->pw_pinned) cudaFreeHost(ctx->pw_pinned);
     cudaGetLastError();
     delete ctx;
 }
@@ -709,6 +738,7 @@ int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value)
     else if (!std::strcmp(key, "slice_rows_bytes") && value > 0) ctx->slice_rows_bytes = static_cast<uint64_t>(value);
     else if (!std::strcmp(key, "task_cap") && value >= 0) ctx->task_cap = static_cast<uint64_t>(value);
     else if (!std::strcmp(key, "pairwise_path") && value >= 0 && value <= 2) ctx->pairwise_path = static_cast<int>(value);
+    else if (!std::strcmp(key, "release_workspace")) { cudaSetDevice(ctx->device); cudaDeviceSynchronize(); release_workspace(ctx); }
     else if (!std::strcmp(key, "pairwise_pair") && value >= 0 && value <= 2) ctx->pairwise_pair = static_cast<int>(value);
     else if (!std::strcmp(key, "pairwise_cluster") && (value == 0 || value == 1 || value == 2 || value == 4)) ctx->pairwise_cluster = static_cast<int>(value);
     else if (!std::strcmp(key, "pairwise_stream") && value >= 0 && value <= 1) ctx->pairwise_stream = static_cast<int>(value);

@@ -17,17 +17,28 @@
 
 namespace {
 
-struct Dev {                                     // device allocation freed on scope exit
+// Device buffers live in the context's grow-only workspace (mvs_internal_workspace): repeated calls -- the reference
+// calls its function once per block pair -- allocate nothing.  Slots:
+enum Slot { kWsA = 0, kWsB, kWsNi, kWsNj, kWsC, kWsSeg, kWsRowoff, kWsMinmax, kWsPlanesA, kWsPlanesB, kWsRows, kWsCols, kWsVals };
+
+struct Dev {                                     // a view of one workspace slot
     void* p = nullptr;
-    ~Dev() { release(); }
-    void release() { if (p) cudaFree(p); p = nullptr; }
-    cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 16); }
+    int alloc(mvs_ctx* ctx, int slot, size_t bytes) { return mvs_internal_workspace(ctx, slot, bytes, &p); }
     template <typename T> T* as() const { return static_cast<T*>(p); }
 };
+#define PW_RC(call) do { const int rc_ = (call); if (rc_ != MVS_OK) return rc_; } while (0)
 
 struct OutBuf {                                  // device triples of one row block, reused across blocks
     Dev rows, cols, vals;
     unsigned long long cap = 0;
+    int reserve(mvs_ctx* ctx, unsigned long long n)
+    {
+        PW_RC(rows.alloc(ctx, kWsRows, n * sizeof(int32_t)));
+        PW_RC(cols.alloc(ctx, kWsCols, n * sizeof(int32_t)));
+        PW_RC(vals.alloc(ctx, kWsVals, n * sizeof(int64_t)));
+        cap = n;
+        return MVS_OK;
+    }
 };
 
 struct Triples {
@@ -189,20 +200,21 @@ int limbs_for_range(int lo, int hi)
     return 4;
 }
 
-int prepare_operand(mvs_ctx* ctx, cudaStream_t st, Operand& op, int d, int* d_mm)
+int prepare_operand(mvs_ctx* ctx, cudaStream_t st, Operand& op, int planes_slot, int d, int* d_mm, int* h_pinned)
 {
-    const int init[2] = {2147483647, -2147483647 - 1};
-    PW_CUDA(ctx, cudaMemcpyAsync(d_mm, init, sizeof init, cudaMemcpyHostToDevice, st));
+    int* mm = h_pinned;                          // pinned: the two small copies are truly asynchronous
+    mm[0] = 2147483647;
+    mm[1] = -2147483647 - 1;
+    PW_CUDA(ctx, cudaMemcpyAsync(d_mm, mm, 2 * sizeof(int), cudaMemcpyHostToDevice, st));
     mvs::pairwise_minmax_kernel<<<1184, 256, 0, st>>>(op.v, op.n * d, d_mm);
     PW_CUDA(ctx, cudaGetLastError());
-    int mm[2];
-    PW_CUDA(ctx, cudaMemcpyAsync(mm, d_mm, sizeof mm, cudaMemcpyDeviceToHost, st));
+    PW_CUDA(ctx, cudaMemcpyAsync(mm, d_mm, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
     PW_CUDA(ctx, cudaStreamSynchronize(st));
     op.P = std::max(limbs_for_range(mm[0], mm[1]), mvs_internal_pairwise_limbs(ctx));
     // one extra zero tile of rows: a row block may start at any row (shards), its last tile then reads past n
     op.n_pad = (op.n + mvs::kImBM - 1) / mvs::kImBM * mvs::kImBM + mvs::kImBM;
     op.k_pad = (d + mvs::kUmBKB - 1) / mvs::kUmBKB * mvs::kUmBKB;      // 128: a multiple of both paths' k-slices
-    PW_CUDA(ctx, op.planes.alloc(static_cast<size_t>(op.P) * op.n_pad * op.k_pad));
+    PW_RC(op.planes.alloc(ctx, planes_slot, static_cast<size_t>(op.P) * op.n_pad * op.k_pad));
     const int64_t threads = op.n_pad * (op.k_pad / 4);
     mvs::pairwise_split_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, st>>>(
         op.v, op.n, d, op.P, op.planes.as<int8_t>(), op.n_pad, op.k_pad);
@@ -234,7 +246,7 @@ mvs::ImmaPlan make_plan(int PA, int PB)
 // (row_base + i, col_base + j, dot) in (i, j) order to `out`; adds the CUDA-event times.
 int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, int64_t mi, const Operand& B, int d,
                   const double* d_ni, const double* d_nj, int32_t row_base, int32_t col_base, int32_t* d_C,
-                  uint32_t* d_segcount, unsigned long long* d_rowoff, OutBuf& ob, Triples& out, double& gemm_ms,
+                  uint32_t* d_segcount, unsigned long long* d_rowoff, OutBuf& ob, void* h_pinned, Triples& out, double& gemm_ms,
                   double& filter_ms, uint64_t& d2h_bytes)
 {
     const int64_t mj = B.n;
@@ -248,7 +260,7 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
     const int64_t ldc = (mj + 3) & ~int64_t{3};
     const int32_t* d_A = A.v + r0 * d;
     const int nseg = static_cast<int>((mj + mvs::kPwSeg - 1) / mvs::kPwSeg);
-    const unsigned seg_ctas = static_cast<unsigned>((mi * nseg + 7) / 8);
+    const unsigned seg_ctas = static_cast<unsigned>(((mi + mvs::kPwRows - 1) / mvs::kPwRows * nseg + 7) / 8);   // 8 warps per CTA
     PW_CUDA(ctx, cudaEventRecord(e0, st));
     if (A.P > 0 && mvs_internal_pairwise_path(ctx) == 0) {   // tcgen05 limb GEMM (TMA + TMEM)
         mvs::UmmaPlan plan = make_umma_plan(A.P, B.P, mvs_internal_pairwise_stream(ctx) == 0);
@@ -266,7 +278,9 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
         int cshape = mvs_internal_pairwise_cluster(ctx);
         if (cshape == 0) cshape = 1;
         const int cm = cshape == 4 ? 2 : 1, cn = cshape >= 2 ? 2 : 1;
-        if (mvs_internal_pairwise_pair(ctx) == 1 && cshape == 1) {
+        // default: CTA pairs (tcgen05 cta_group::2, 256 x 128 super-tiles) whenever there are two tile rows to pair
+        const int pair_opt = mvs_internal_pairwise_pair(ctx);
+        if (cshape == 1 && (pair_opt == 1 || (pair_opt == 0 && tiles_m >= 2))) {
             CUtensorMap tmA, tmB;
             if (!make_tensor_map(A, mvs::kUmBM, &tmA) || !make_tensor_map(B, mvs::kUmBN / 2, &tmB)) return MVS_ERR_CUDA;
             PW_CUDA(ctx, launch_umma_pair(st, sms, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), static_cast<int>(A.n_pad - mvs::kUmBM), mi,
@@ -315,40 +329,36 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
     mvs::pairwise_scan_kernel<<<1, 1024, 0, st>>>(d_rowoff, mi);
     PW_CUDA(ctx, cudaGetLastError());
     mvs_internal_count_launches(ctx, 1);
-    unsigned long long total = 0;
-    PW_CUDA(ctx, cudaMemcpyAsync(&total, d_rowoff + mi, sizeof total, cudaMemcpyDeviceToHost, st));
+    // emit is launched without knowing the total: it writes nothing if the triples do not fit the output buffers, the
+    // host then grows them and launches it again (rare: the buffers start at 4 Mi triples)
+    unsigned long long* h_total = static_cast<unsigned long long*>(h_pinned);
+    auto emit = [&]() {
+        mvs::pairwise_emit_kernel<<<seg_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_segcount, nseg, d_rowoff, row_base, col_base,
+                                                           ob.cap, ob.rows.as<int32_t>(), ob.cols.as<int32_t>(), ob.vals.as<long long>());
+        mvs_internal_count_launches(ctx, 1);
+        return cudaGetLastError();
+    };
+    PW_CUDA(ctx, emit());
+    PW_CUDA(ctx, cudaEventRecord(e2, st));
+    PW_CUDA(ctx, cudaMemcpyAsync(h_total, d_rowoff + mi, sizeof *h_total, cudaMemcpyDeviceToHost, st));
     PW_CUDA(ctx, cudaStreamSynchronize(st));
     mvs_internal_count_launches(ctx, 2);
+    const unsigned long long total = *h_total;
     d2h_bytes += sizeof total;
-
+    if (total > ob.cap) {
+        PW_RC(ob.reserve(ctx, total + total / 4));
+        PW_CUDA(ctx, emit());
+    }
     if (total) {
-        if (total > ob.cap) {                    // grow (rare: the buffers start at 4 Mi triples)
-            ob.rows.release();
-            ob.cols.release();
-            ob.vals.release();
-            ob.cap = total + total / 4;
-            PW_CUDA(ctx, ob.rows.alloc(ob.cap * sizeof(int32_t)));
-            PW_CUDA(ctx, ob.cols.alloc(ob.cap * sizeof(int32_t)));
-            PW_CUDA(ctx, ob.vals.alloc(ob.cap * sizeof(int64_t)));
-        }
-        Dev &rows = ob.rows, &cols = ob.cols, &vals = ob.vals;
-        mvs::pairwise_emit_kernel<<<seg_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_segcount, nseg, d_rowoff, row_base,
-                                                           col_base, rows.as<int32_t>(), cols.as<int32_t>(), vals.as<long long>());
-        PW_CUDA(ctx, cudaGetLastError());
-        mvs_internal_count_launches(ctx, 1);
-        PW_CUDA(ctx, cudaEventRecord(e2, st));
         const size_t at = out.rows.size();
         out.rows.resize(at + total);
         out.cols.resize(at + total);
         out.values.resize(at + total);
-        PW_CUDA(ctx, cudaMemcpyAsync(out.rows.data() + at, rows.p, total * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-        PW_CUDA(ctx, cudaMemcpyAsync(out.cols.data() + at, cols.p, total * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-        PW_CUDA(ctx, cudaMemcpyAsync(out.values.data() + at, vals.p, total * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        PW_CUDA(ctx, cudaMemcpyAsync(out.rows.data() + at, ob.rows.p, total * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        PW_CUDA(ctx, cudaMemcpyAsync(out.cols.data() + at, ob.cols.p, total * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        PW_CUDA(ctx, cudaMemcpyAsync(out.values.data() + at, ob.vals.p, total * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
         PW_CUDA(ctx, cudaStreamSynchronize(st));
         d2h_bytes += total * 16;
-    } else {
-        PW_CUDA(ctx, cudaEventRecord(e2, st));
-        PW_CUDA(ctx, cudaStreamSynchronize(st));
     }
     float a = 0.f, b = 0.f;
     PW_CUDA(ctx, cudaEventElapsedTime(&a, e0, e1));
@@ -370,23 +380,18 @@ int run_blocks(mvs_ctx* ctx, cudaStream_t st, Operand& A, int64_t begin, int64_t
     const int nseg = static_cast<int>((mj + mvs::kPwSeg - 1) / mvs::kPwSeg);
     Dev C, segcount, rowoff, mm;
     OutBuf ob;
-    ob.cap = 4ull << 20;
-    PW_CUDA(ctx, ob.rows.alloc(ob.cap * sizeof(int32_t)));
-    PW_CUDA(ctx, ob.cols.alloc(ob.cap * sizeof(int32_t)));
-    PW_CUDA(ctx, ob.vals.alloc(ob.cap * sizeof(int64_t)));
-    PW_CUDA(ctx, C.alloc(static_cast<size_t>(rb) * ldc * 4));
-    PW_CUDA(ctx, segcount.alloc(static_cast<size_t>(rb) * nseg * 4));
-    PW_CUDA(ctx, rowoff.alloc(static_cast<size_t>(rb + 1) * 8));
+    void* h_pinned = mvs_internal_pinned_scratch(ctx);
+    if (!h_pinned) return MVS_ERR_OOM;
+    PW_RC(ob.reserve(ctx, 4ull << 20));
+    PW_RC(C.alloc(ctx, kWsC, static_cast<size_t>(rb) * ldc * 4));
+    PW_RC(segcount.alloc(ctx, kWsSeg, static_cast<size_t>(rb) * nseg * 4));
+    PW_RC(rowoff.alloc(ctx, kWsRowoff, static_cast<size_t>(rb + 1) * 8));
     if (mvs_internal_pairwise_path(ctx) != 1) {
         const auto t0 = std::chrono::steady_clock::now();
-        PW_CUDA(ctx, mm.alloc(8));
+        PW_RC(mm.alloc(ctx, kWsMinmax, 8));
         PW_CUDA(ctx, cudaFuncSetAttribute(mvs::pairwise_dot_imma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mvs::kImSmemBytes));
-        int rc = prepare_operand(ctx, st, B, d, mm.as<int>());
-        if (rc != MVS_OK) return rc;
-        if (!same) {
-            rc = prepare_operand(ctx, st, A, d, mm.as<int>());
-            if (rc != MVS_OK) return rc;
-        }
+        PW_RC(prepare_operand(ctx, st, B, kWsPlanesB, d, mm.as<int>(), static_cast<int*>(h_pinned)));
+        if (!same) PW_RC(prepare_operand(ctx, st, A, kWsPlanesA, d, mm.as<int>(), static_cast<int*>(h_pinned)));
         PW_CUDA(ctx, cudaStreamSynchronize(st));
         prep_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     }
@@ -394,7 +399,7 @@ int run_blocks(mvs_ctx* ctx, cudaStream_t st, Operand& A, int64_t begin, int64_t
     for (int64_t r0 = begin; r0 < end; r0 += rb) {
         const int64_t m = std::min(rb, end - r0);
         const int rc = pairwise_core(ctx, st, Aref, r0, m, B, d, d_ni + r0, d_nj, static_cast<int32_t>(r0), 0, C.as<int32_t>(),
-                                     segcount.as<uint32_t>(), rowoff.as<unsigned long long>(), ob, t, gemm_ms, filter_ms, d2h);
+                                     segcount.as<uint32_t>(), rowoff.as<unsigned long long>(), ob, h_pinned, t, gemm_ms, filter_ms, d2h);
         if (rc != MVS_OK) return rc;
     }
     return MVS_OK;
@@ -458,10 +463,10 @@ int mvs_pairwise_block(mvs_ctx* ctx, const int32_t* block_i, int64_t mi, const i
     if (mi > 0 && mj > 0) {
         Dev A, B, ni, nj;
         const size_t ab = static_cast<size_t>(mi) * d * 4, bb = static_cast<size_t>(mj) * d * 4;
-        PW_CUDA(ctx, A.alloc(ab));
-        PW_CUDA(ctx, B.alloc(bb));
-        PW_CUDA(ctx, ni.alloc(static_cast<size_t>(mi) * 8));
-        PW_CUDA(ctx, nj.alloc(static_cast<size_t>(mj) * 8));
+        PW_RC(A.alloc(ctx, kWsA, ab));
+        PW_RC(B.alloc(ctx, kWsB, bb));
+        PW_RC(ni.alloc(ctx, kWsNi, static_cast<size_t>(mi) * 8));
+        PW_RC(nj.alloc(ctx, kWsNj, static_cast<size_t>(mj) * 8));
         PW_CUDA(ctx, cudaMemcpyAsync(A.p, block_i, ab, cudaMemcpyHostToDevice, st));
         PW_CUDA(ctx, cudaMemcpyAsync(B.p, block_j, bb, cudaMemcpyHostToDevice, st));
         PW_CUDA(ctx, cudaMemcpyAsync(ni.p, norms_i, static_cast<size_t>(mi) * 8, cudaMemcpyHostToDevice, st));
@@ -498,8 +503,8 @@ int mvs_pairwise_shard(mvs_ctx* ctx, const int32_t* vectors, int64_t n_total, in
         // the whole db stays resident (n_total x d x 4 bytes: 8 GB per million vectors at d = 2048)
         Dev V, nrm;
         const size_t vb = static_cast<size_t>(n_total) * d * 4;
-        PW_CUDA(ctx, V.alloc(vb));
-        PW_CUDA(ctx, nrm.alloc(static_cast<size_t>(n_total) * 8));
+        PW_RC(V.alloc(ctx, kWsB, vb));
+        PW_RC(nrm.alloc(ctx, kWsNj, static_cast<size_t>(n_total) * 8));
         PW_CUDA(ctx, cudaMemcpyAsync(V.p, vectors, vb, cudaMemcpyHostToDevice, st));
         PW_CUDA(ctx, cudaMemcpyAsync(nrm.p, norms_sq, static_cast<size_t>(n_total) * 8, cudaMemcpyHostToDevice, st));
         h2d = vb + static_cast<uint64_t>(n_total) * 8;

@@ -25,18 +25,26 @@ constexpr int kPwBM = 128, kPwBN = 128, kPwBK = 16;
 constexpr int kPwThreads = 256;
 
 // keep-test of the reference (:140-143); norms are squared norms.  `(int64)dot / d > threshold` with the
-// truncating quotient q.  For threshold >= 0 (always, with real norms) q > threshold <=> q >= floor(threshold) + 1
-// <=> dot >= (floor(threshold) + 1) * d, which needs no division; a negative threshold takes the division.
+// truncating quotient q.  For 0 <= threshold < 2^31 (always, with real norms) q > threshold <=> q >= floor(threshold) + 1
+// <=> dot >= (floor(threshold) + 1) * d: no division, and floor() without the conversion pipe -- adding 2^52 with
+// round-down leaves floor(threshold) in the low mantissa word.  Per element that is 2 FP64 ops for the threshold
+// (exactly the reference's expression), one round-down add, one wide multiply-add and a 64-bit compare.
+// Anything else (negative, -0, NaN, huge thresholds) takes the literal path.
+__device__ __noinline__ bool pw_keep_literal(int32_t dot, int d, double threshold)
+{
+    if (threshold >= 2147483648.0) return false;                      // |q| <= 2^31
+    const int q = dot / d;                                            // same truncation as int64 / int
+    return static_cast<double>(q) > threshold;                        // NaN thresholds keep nothing, as in C++
+}
 __device__ __forceinline__ bool pw_keep(int32_t dot, int d, double ni, double nj)
 {
     const double threshold = 0.05 * (ni + nj);
-    if (threshold >= 0.0) {
-        if (threshold >= 2147483647.0) return false;                  // |q| <= 2^31
-        const long long need = (static_cast<long long>(__double2int_rd(threshold)) + 1) * d;   // one F2I instead of a 64-bit conversion
+    if (static_cast<unsigned>(__double2hiint(threshold)) < 0x41E00000u) {       // +0 <= threshold < 2^31
+        const int fl = __double2loint(__dadd_rd(threshold, 4503599627370496.0));
+        const long long need = static_cast<long long>(fl) * d + d;
         return static_cast<long long>(dot) >= need;
     }
-    const int q = dot / d;                                            // same truncation as int64 / int
-    return static_cast<double>(q) > threshold;                        // NaN thresholds keep nothing, as in C++
+    return pw_keep_literal(dot, d, threshold);
 }
 
 // One 16-byte (4 x int32) slice of a row starting at column k (p = row + k); zero past the row end / for rows
@@ -387,21 +395,67 @@ __device__ __forceinline__ unsigned pw_keep_mask4(const int32_t* __restrict__ cr
     return m;
 }
 
+// keep-mask of four columns whose squared norms are already in registers (`valid` = columns that exist)
+__device__ __forceinline__ unsigned pw_keep_mask4r(const int4& v, int d, double ni, const double (&nj)[4], unsigned valid)
+{
+    unsigned m = 0;
+    m |= pw_keep(v.x, d, ni, nj[0]) ? 1u : 0u;
+    m |= pw_keep(v.y, d, ni, nj[1]) ? 2u : 0u;
+    m |= pw_keep(v.z, d, ni, nj[2]) ? 4u : 0u;
+    m |= pw_keep(v.w, d, ni, nj[3]) ? 8u : 0u;
+    return m & valid;
+}
+
+// four columns of one row of C starting at column j (zeros past the row end); ldc % 4 == 0, C 16-byte aligned (host)
+__device__ __forceinline__ int4 pw_load_c4(const int32_t* __restrict__ crow, int64_t j, int64_t mj)
+{
+    if (j + 3 < mj) return *reinterpret_cast<const int4*>(crow + j);
+    int4 v = make_int4(0, 0, 0, 0);
+    if (j + 0 < mj) v.x = crow[j + 0];
+    if (j + 1 < mj) v.y = crow[j + 1];
+    if (j + 2 < mj) v.z = crow[j + 2];
+    return v;
+}
+
+// One warp = one 128-column segment of kPwRows consecutive rows: the lane keeps its four column norms in registers,
+// has all kPwRows 16-byte loads of C in flight at once (the pass is HBM-bound: C is read exactly once), and the
+// per-row counts are reduced with one redux each.
+constexpr int kPwRows = 8;
+
 __global__ void __launch_bounds__(256)
 pairwise_count_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int64_t ldc, int d,
                       const double* __restrict__ norms_i, const double* __restrict__ norms_j,
                       uint32_t* __restrict__ segcount, int nseg)
 {
     const int64_t w = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (w >= mi * nseg) return;
-    const int64_t row = w / nseg;
-    const int seg = static_cast<int>(w - row * nseg);
+    const int64_t groups = (mi + kPwRows - 1) / kPwRows;
+    if (w >= groups * nseg) return;
+    const int64_t row0 = (w / nseg) * kPwRows;
+    const int seg = static_cast<int>(w % nseg);
     const int lane = threadIdx.x & 31;
-    int4 v;
-    unsigned n = __popc(pw_keep_mask4(C + row * ldc, static_cast<int64_t>(seg) * kPwSeg + lane * 4, mj, d, norms_i[row], norms_j, v));
+    const int64_t j = static_cast<int64_t>(seg) * kPwSeg + lane * 4;
+    double nj[4];
+    unsigned valid = 0;
 #pragma unroll
-    for (int m = 16; m; m >>= 1) n += __shfl_xor_sync(0xffffffffu, n, m);
-    if (lane == 0) segcount[w] = n;
+    for (int t = 0; t < 4; ++t) {
+        nj[t] = j + t < mj ? norms_j[j + t] : 0.0;
+        valid |= j + t < mj ? (1u << t) : 0u;
+    }
+    int4 v[kPwRows];
+    const int32_t* p = C + row0 * ldc + j;
+    if (row0 + kPwRows <= mi && j + 3 < mj) {                        // everywhere but the last row group / last columns
+#pragma unroll
+        for (int r = 0; r < kPwRows; ++r) v[r] = *reinterpret_cast<const int4*>(p + r * ldc);
+    } else {
+#pragma unroll
+        for (int r = 0; r < kPwRows; ++r) v[r] = row0 + r < mi ? pw_load_c4(C + (row0 + r) * ldc, j, mj) : make_int4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int r = 0; r < kPwRows; ++r) {
+        if (row0 + r >= mi) break;                                   // warp-uniform
+        const unsigned n = __reduce_add_sync(0xffffffffu, static_cast<unsigned>(__popc(pw_keep_mask4r(v[r], d, norms_i[row0 + r], nj, valid))));
+        if (lane == 0) segcount[(row0 + r) * nseg + seg] = n;
+    }
 }
 
 // rowoff[row] = kept columns of the row = sum of its segment counts.  One warp per row.
@@ -461,38 +515,46 @@ __global__ void __launch_bounds__(256)
 pairwise_emit_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int64_t ldc, int d,
                      const double* __restrict__ norms_i, const double* __restrict__ norms_j,
                      const uint32_t* __restrict__ segcount, int nseg, const unsigned long long* __restrict__ rowoff,
-                     int32_t row_base, int32_t col_base,
+                     int32_t row_base, int32_t col_base, unsigned long long cap,
                      int32_t* __restrict__ rows, int32_t* __restrict__ cols, long long* __restrict__ values)
 {
+    // same warp -> (row group, segment) mapping as the count kernel; almost every warp finds eight zero counts and leaves
     const int64_t w = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (w >= mi * nseg) return;
-    if (segcount[w] == 0) return;                                    // warp-uniform
-    const int64_t row = w / nseg;
-    const int seg = static_cast<int>(w - row * nseg);
+    const int64_t groups = (mi + kPwRows - 1) / kPwRows;
+    if (w >= groups * nseg) return;
+    if (rowoff[mi] > cap) return;                                    // output buffers too small: the host grows them and re-launches
+    const int64_t row0 = (w / nseg) * kPwRows;
+    const int seg = static_cast<int>(w % nseg);
     const int lane = threadIdx.x & 31;
-    unsigned long long before = 0;                                    // kept columns of the row left of this segment
-    for (int t = lane; t < seg; t += 32) before += segcount[row * nseg + t];
-#pragma unroll
-    for (int m = 16; m; m >>= 1) before += __shfl_xor_sync(0xffffffffu, before, m);
-    int4 v;
+    const bool mine_nonzero = lane < kPwRows && row0 + lane < mi && segcount[(row0 + lane) * nseg + seg] != 0;
+    unsigned todo = __ballot_sync(0xffffffffu, mine_nonzero);
     const int64_t j = static_cast<int64_t>(seg) * kPwSeg + lane * 4;
-    const unsigned m4 = pw_keep_mask4(C + row * ldc, j, mj, d, norms_i[row], norms_j, v);
-    unsigned mine = __popc(m4), incl = mine;
+    while (todo) {                                                   // warp-uniform
+        const int64_t row = row0 + (__ffs(todo) - 1);
+        todo &= todo - 1;
+        unsigned long long before = 0;                                // kept columns of the row left of this segment
+        for (int t = lane; t < seg; t += 32) before += segcount[row * nseg + t];
 #pragma unroll
-    for (int m = 1; m < 32; m <<= 1) {
-        const unsigned y = __shfl_up_sync(0xffffffffu, incl, m);
-        if (lane >= m) incl += y;
-    }
-    unsigned long long at = rowoff[row] + before + (incl - mine);
-    const int32_t e[4] = {v.x, v.y, v.z, v.w};
+        for (int m = 16; m; m >>= 1) before += __shfl_xor_sync(0xffffffffu, before, m);
+        int4 v;
+        const unsigned m4 = pw_keep_mask4(C + row * ldc, j, mj, d, norms_i[row], norms_j, v);
+        unsigned mine = __popc(m4), incl = mine;
 #pragma unroll
-    for (int t = 0; t < 4; ++t)
-        if (m4 & (1u << t)) {
-            rows[at] = row_base + static_cast<int32_t>(row);
-            cols[at] = col_base + static_cast<int32_t>(j + t);
-            values[at] = static_cast<long long>(e[t]);
-            ++at;
+        for (int m = 1; m < 32; m <<= 1) {
+            const unsigned y = __shfl_up_sync(0xffffffffu, incl, m);
+            if (lane >= m) incl += y;
         }
+        unsigned long long at = rowoff[row] + before + (incl - mine);
+        const int32_t e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+            if (m4 & (1u << t)) {
+                rows[at] = row_base + static_cast<int32_t>(row);
+                cols[at] = col_base + static_cast<int32_t>(j + t);
+                values[at] = static_cast<long long>(e[t]);
+                ++at;
+            }
+    }
 }
 
 }  // namespace mvs

@@ -17,7 +17,7 @@ pytestmark = pytest.mark.gpu
 # products streamed pair by pair; also as clusters of 1 x 2 and 2 x 2 CTAs with TMA multicast), on the mma.sync limb GEMM
 # and on the IMAD GEMM: all must give the reference's bits
 # "pair" = tcgen05 cta_group::2 (two SMs per 256 x 128 tile); fourth entry = option "pairwise_pair" (2 = single CTAs)
-PATHS = {"umma": (0, 0, 0, 2), "umma3": (0, 3, 0, 2), "umma4": (0, 4, 0, 2), "umma_1x2": (0, 0, 2, 2), "umma_2x2": (0, 0, 4, 2),
+PATHS = {"default": (0, 0, 0, 0), "umma": (0, 0, 0, 2), "umma3": (0, 3, 0, 2), "umma4": (0, 4, 0, 2), "umma_1x2": (0, 0, 2, 2), "umma_2x2": (0, 0, 4, 2),
          "umma4_2x2": (0, 4, 4, 2), "pair": (0, 0, 0, 1), "pair3": (0, 3, 0, 1), "pair4": (0, 4, 0, 1),
          "mma": (2, 0, 0, 0), "mma4": (2, 4, 0, 0), "imad": (1, 0, 0, 0)}
 
@@ -128,3 +128,14 @@ def test_shard_of_projected_synthetic_db_matches_blockwise_oracle(sk):
     want = oracle_pairwise(vec, vec, 2048, nrm, nrm)
     assert len(want[0]) > 600 * 5 and same(got, want)
     assert got.gemm_ms > 0 and got.h2d_bytes == vec.nbytes + 8 * 600
+
+
+def test_more_triples_than_the_initial_output_buffers(sk):
+    """2200 identical vectors: every pair is kept (4.84 M triples > the 4 Mi the device buffers start with), so the
+    emit kernel first declines, the host grows the buffers and launches it again."""
+    n, d = 2200, 8
+    v = np.tile(np.arange(1, d + 1, dtype=np.int32) * 3, (n, 1))
+    nrm = norms_sq_like_reference(v, d)
+    got = pw.compute_sparse_dot_products(sk, v, v, nrm, nrm)
+    want = oracle_pairwise(v, v, d, nrm, nrm)
+    assert len(want[0]) == n * n and same(got, want)
