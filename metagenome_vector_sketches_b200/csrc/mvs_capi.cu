@@ -77,6 +77,7 @@ struct mvs_ctx {
     uint64_t task_cap = 0;                       // experiment knob: rounds per warp task (0 = planner's choice)
     int pairwise_path = 0;                       // 0 = tcgen05 limb GEMM, 1 = IMAD GEMM, 2 = mma.sync limb GEMM
     int pairwise_pair = 0;                       // tcgen05 path: 0 = default, 1 = CTA pairs (cta_group::2, 256 x 128 tiles), 2 = single CTAs
+    int pairwise_fuse = 0;                       // tcgen05 path: 0 = keep-test fused into the GEMM epilogue (default), 2 = separate count pass
     int pairwise_cluster = 0;                    // tcgen05 path: CTAs per cluster: 0 / 1 = 1 x 1 (default), 2 = 1 x 2, 4 = 2 x 2 (TMA multicast)
     int pairwise_stream = 0;                     // 1 = tcgen05 path streams limb pairs even when the planes would fit one stage
     int pairwise_limbs = 0;                      // 0 = from the operands' min/max, 1..4 = force at least that many limbs
@@ -370,6 +371,7 @@ int mvs_internal_pairwise_limbs(const mvs_ctx* ctx) { return ctx->pairwise_limbs
 int mvs_internal_pairwise_stream(const mvs_ctx* ctx) { return ctx->pairwise_stream; }
 int mvs_internal_pairwise_cluster(const mvs_ctx* ctx) { return ctx->pairwise_cluster; }
 int mvs_internal_pairwise_pair(const mvs_ctx* ctx) { return ctx->pairwise_pair; }
+int mvs_internal_pairwise_fuse(const mvs_ctx* ctx) { return ctx->pairwise_fuse; }
 int mvs_internal_workspace(mvs_ctx* ctx, int slot, size_t bytes, void** out)
 {
     if (slot < 0 || slot >= kPairwiseSlots) return MVS_ERR_INVALID_ARG;
@@ -739,6 +741,7 @@ int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value)
     else if (!std::strcmp(key, "task_cap") && value >= 0) ctx->task_cap = static_cast<uint64_t>(value);
     else if (!std::strcmp(key, "pairwise_path") && value >= 0 && value <= 2) ctx->pairwise_path = static_cast<int>(value);
     else if (!std::strcmp(key, "release_workspace")) { cudaSetDevice(ctx->device); cudaDeviceSynchronize(); release_workspace(ctx); }
+    else if (!std::strcmp(key, "pairwise_fuse") && (value == 0 || value == 2)) ctx->pairwise_fuse = static_cast<int>(value);
     else if (!std::strcmp(key, "pairwise_pair") && value >= 0 && value <= 2) ctx->pairwise_pair = static_cast<int>(value);
     else if (!std::strcmp(key, "pairwise_cluster") && (value == 0 || value == 1 || value == 2 || value == 4)) ctx->pairwise_cluster = static_cast<int>(value);
     else if (!std::strcmp(key, "pairwise_stream") && value >= 0 && value <= 1) ctx->pairwise_stream = static_cast<int>(value);

@@ -15,6 +15,7 @@ int mvs_internal_pairwise_limbs(const mvs_ctx* ctx);              // option "pai
 int mvs_internal_pairwise_stream(const mvs_ctx* ctx);             // option "pairwise_stream"
 int mvs_internal_pairwise_cluster(const mvs_ctx* ctx);            // option "pairwise_cluster"
 int mvs_internal_pairwise_pair(const mvs_ctx* ctx);               // option "pairwise_pair"
+int mvs_internal_pairwise_fuse(const mvs_ctx* ctx);               // option "pairwise_fuse"
 // grow-only device buffer number `slot` (0..15) of at least `bytes` bytes, kept until mvs_destroy / option "release_workspace"
 int mvs_internal_workspace(mvs_ctx* ctx, int slot, size_t bytes, void** out);
 void* mvs_internal_pinned_scratch(mvs_ctx* ctx);                 // 256 bytes of pinned host memory (nullptr on failure)

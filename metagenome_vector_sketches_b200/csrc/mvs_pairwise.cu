@@ -95,7 +95,8 @@ bool make_tensor_map(const Operand& op, int box_rows, CUtensorMap* tm)
 
 template <int CM, int CN, bool F22>
 cudaError_t launch_umma(cudaStream_t st, int sms, size_t smem, const CUtensorMap& tmA, const CUtensorMap& tmB, const mvs::UmmaPlan& plan,
-                        int k_pad, int a_row0, int64_t mi, int64_t mj, int32_t* d_C, int64_t ldc, int tiles_m, int tiles_n)
+                        int k_pad, int a_row0, int64_t mi, int64_t mj, int32_t* d_C, int64_t ldc, int tiles_m, int tiles_n,
+                        const mvs::UmFilter& filt)
 {
     auto kernel = mvs::pairwise_dot_umma_kernel<CM, CN, F22>;
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
@@ -124,16 +125,17 @@ cudaError_t launch_umma(cudaStream_t st, int sms, size_t smem, const CUtensorMap
     const int nclusters = static_cast<int>(std::min<int64_t>(nsuper, max_clusters));
     if (CS == 1) {                               // plain launch, no cluster attribute
         kernel<<<static_cast<unsigned>(nclusters), mvs::kUmThreads, smem, st>>>(tmA, tmB, plan, k_pad, a_row0, mi, mj, d_C, ldc, super_n,
-                                                                              static_cast<int>(nsuper));
+                                                                              static_cast<int>(nsuper), filt);
         return cudaGetLastError();
     }
     cfg.gridDim = dim3(static_cast<unsigned>(nclusters * CS));
-    return cudaLaunchKernelEx(&cfg, kernel, tmA, tmB, plan, k_pad, a_row0, mi, mj, d_C, ldc, super_n, static_cast<int>(nsuper));
+    return cudaLaunchKernelEx(&cfg, kernel, tmA, tmB, plan, k_pad, a_row0, mi, mj, d_C, ldc, super_n, static_cast<int>(nsuper), filt);
 }
 
 // CTA pairs (tcgen05 cta_group::2): one cluster of two CTAs per 256 x 128 super-tile
 cudaError_t launch_umma_pair(cudaStream_t st, int sms, const CUtensorMap& tmA, const CUtensorMap& tmB, mvs::UmmaPlan plan, int k_pad,
-                             int a_row0, int a_row_last, int64_t mi, int64_t mj, int32_t* d_C, int64_t ldc, int tiles_m, int tiles_n)
+                             int a_row0, int a_row_last, int64_t mi, int64_t mj, int32_t* d_C, int64_t ldc, int tiles_m, int tiles_n,
+                             const mvs::UmFilter& filt)
 {
     const bool f22 = plan.ngroups == 1 && plan.a_count == 2 && plan.b_count == 2;
     auto kernel = f22 ? mvs::pairwise_dot_umma_pair_kernel<true> : mvs::pairwise_dot_umma_pair_kernel<false>;
@@ -160,7 +162,7 @@ cudaError_t launch_umma_pair(cudaStream_t st, int sms, const CUtensorMap& tmA, c
     else cudaGetLastError();
     const int npairs = static_cast<int>(std::min<int64_t>(nsuper, max_pairs));
     cfg.gridDim = dim3(static_cast<unsigned>(npairs * 2));
-    return cudaLaunchKernelEx(&cfg, kernel, tmA, tmB, plan, k_pad, a_row0, a_row_last, mi, mj, d_C, ldc, tiles_n, static_cast<int>(nsuper));
+    return cudaLaunchKernelEx(&cfg, kernel, tmA, tmB, plan, k_pad, a_row0, a_row_last, mi, mj, d_C, ldc, tiles_n, static_cast<int>(nsuper), filt);
 }
 
 mvs::UmmaPlan make_umma_plan(int PA, int PB, bool allow_fused)
@@ -261,6 +263,7 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
     const int32_t* d_A = A.v + r0 * d;
     const int nseg = static_cast<int>((mj + mvs::kPwSeg - 1) / mvs::kPwSeg);
     const unsigned seg_ctas = static_cast<unsigned>(((mi + mvs::kPwRows - 1) / mvs::kPwRows * nseg + 7) / 8);   // 8 warps per CTA
+    bool fused = false;
     PW_CUDA(ctx, cudaEventRecord(e0, st));
     if (A.P > 0 && mvs_internal_pairwise_path(ctx) == 0) {   // tcgen05 limb GEMM (TMA + TMEM)
         mvs::UmmaPlan plan = make_umma_plan(A.P, B.P, mvs_internal_pairwise_stream(ctx) == 0);
@@ -272,6 +275,10 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
         if (static_cast<int64_t>(tiles_n) * tiles_m > 0x3fffffffLL) return MVS_ERR_TOO_LARGE;
         int sms = 0;
         PW_CUDA(ctx, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, mvs_internal_device(ctx)));
+        // pre-filter fused into the epilogue (option "pairwise_fuse" = 2 switches it off): only rows x 128-column segments
+        // that may keep something are stored and marked; the recount kernel below visits those instead of all of C
+        fused = mvs_internal_pairwise_fuse(ctx) != 2;
+        const mvs::UmFilter filt{fused ? d_ni : nullptr, d_nj, d_segcount, nseg, d};
         // cluster shape: 1 x 1 by default.  Clusters of 1 x 2 / 2 x 2 CTAs sharing operand tiles by TMA multicast (option
         // "pairwise_cluster" = 2 / 4) halve the L2 reads but are NOT faster: the main loop is bound by the bytes an SM
         // can take in (~32 B/clk, the same with multicast), see DESIGN.md section 9
@@ -284,26 +291,26 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
             CUtensorMap tmA, tmB;
             if (!make_tensor_map(A, mvs::kUmBM, &tmA) || !make_tensor_map(B, mvs::kUmBN / 2, &tmB)) return MVS_ERR_CUDA;
             PW_CUDA(ctx, launch_umma_pair(st, sms, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), static_cast<int>(A.n_pad - mvs::kUmBM), mi,
-                                          mj, d_C, ldc, tiles_m, tiles_n));
+                                          mj, d_C, ldc, tiles_m, tiles_n, filt));
         } else {
         CUtensorMap tmA, tmB;
         if (!make_tensor_map(A, mvs::kUmBM / cn, &tmA) || !make_tensor_map(B, mvs::kUmBN / cm, &tmB)) return MVS_ERR_CUDA;
         cudaError_t le;
         const bool f22 = plan.ngroups == 1 && plan.a_count == 2 && plan.b_count == 2;
-        if (cshape == 4) le = launch_umma<2, 2, false>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
-        else if (cshape == 2) le = launch_umma<1, 2, false>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
-        else if (f22) le = launch_umma<1, 1, true>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
-        else le = launch_umma<1, 1, false>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n);
+        if (cshape == 4) le = launch_umma<2, 2, false>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n, filt);
+        else if (cshape == 2) le = launch_umma<1, 2, false>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n, filt);
+        else if (f22) le = launch_umma<1, 1, true>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n, filt);
+        else le = launch_umma<1, 1, false>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n, filt);
         PW_CUDA(ctx, le);
 #ifdef MVS_UMMA_PROBE
         if (cshape == 1 && std::getenv("MVS_UMMA_PROBE_PRINT")) {
-            static unsigned long long h[1024][4];
+            static unsigned long long h[1024][8];
             PW_CUDA(ctx, cudaStreamSynchronize(st));
             PW_CUDA(ctx, cudaMemcpyFromSymbol(h, mvs::um_probe_cycles, sizeof h));
-            double a[4] = {0, 0, 0, 0};
+            double a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
             const int n = static_cast<int>(std::min<int64_t>(static_cast<int64_t>(tiles_m) * tiles_n, sms));
-            for (int b = 0; b < n; ++b) for (int k = 0; k < 4; ++k) a[k] += static_cast<double>(h[b][k]) / n;
-            std::fprintf(stderr, "[umma probe] per CTA: wait tmem_empty %.0f clk, wait full %.0f clk, total %.0f clk, tiles %.1f\n", a[0], a[1], a[2], a[3]);
+            for (int b = 0; b < n; ++b) for (int k = 0; k < 8; ++k) a[k] += static_cast<double>(h[b][k]) / n;
+            std::fprintf(stderr, "[umma probe] per CTA: MMA warp: wait tmem_empty %.0f clk, wait full %.0f clk, total %.0f clk, tiles %.1f; epilogue warp: wait tmem_full %.0f, drain %.0f, test+store %.0f clk\n", a[0], a[1], a[2], a[3], a[4], a[5], a[6]);
         }
 #endif
         }
@@ -321,7 +328,8 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
     }
     PW_CUDA(ctx, cudaGetLastError());
     PW_CUDA(ctx, cudaEventRecord(e1, st));
-    mvs::pairwise_count_kernel<<<seg_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_segcount, nseg);
+    if (fused) mvs::pairwise_recount_kernel<<<seg_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_segcount, nseg, mvs::kUmMaybe);
+    else mvs::pairwise_count_kernel<<<seg_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_segcount, nseg);
     PW_CUDA(ctx, cudaGetLastError());
     mvs_internal_count_launches(ctx, 1);
     mvs::pairwise_rowsum_kernel<<<static_cast<unsigned>((mi + 7) / 8), 256, 0, st>>>(d_segcount, nseg, d_rowoff, mi);

@@ -40,9 +40,9 @@ __device__ __forceinline__ bool pw_keep(int32_t dot, int d, double ni, double nj
 {
     const double threshold = 0.05 * (ni + nj);
     if (static_cast<unsigned>(__double2hiint(threshold)) < 0x41E00000u) {       // +0 <= threshold < 2^31
-        const int fl = __double2loint(__dadd_rd(threshold, 4503599627370496.0));
-        const long long need = static_cast<long long>(fl) * d + d;
-        return static_cast<long long>(dot) >= need;
+        const unsigned fl = static_cast<unsigned>(__double2loint(__dadd_rd(threshold, 4503599627370496.0)));
+        const unsigned long long need = static_cast<unsigned long long>(fl) * static_cast<unsigned>(d) + static_cast<unsigned>(d);
+        return dot >= 0 && static_cast<unsigned long long>(static_cast<unsigned>(dot)) >= need;
     }
     return pw_keep_literal(dot, d, threshold);
 }
@@ -455,6 +455,31 @@ pairwise_count_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int
         if (row0 + r >= mi) break;                                   // warp-uniform
         const unsigned n = __reduce_add_sync(0xffffffffu, static_cast<unsigned>(__popc(pw_keep_mask4r(v[r], d, norms_i[row0 + r], nj, valid))));
         if (lane == 0) segcount[(row0 + r) * nseg + seg] = n;
+    }
+}
+
+// After a GEMM with the fused pre-filter (mvs_pairwise_umma.cuh): segments marked `maybe` were stored and get their
+// exact count here; all others are already 0 and were never written to C.  Same warp mapping as the count kernel.
+__global__ void __launch_bounds__(256)
+pairwise_recount_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int64_t ldc, int d,
+                        const double* __restrict__ norms_i, const double* __restrict__ norms_j,
+                        uint32_t* __restrict__ segcount, int nseg, uint32_t maybe)
+{
+    const int64_t w = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t groups = (mi + kPwRows - 1) / kPwRows;
+    if (w >= groups * nseg) return;
+    const int64_t row0 = (w / nseg) * kPwRows;
+    const int seg = static_cast<int>(w % nseg);
+    const int lane = threadIdx.x & 31;
+    const bool marked = lane < kPwRows && row0 + lane < mi && segcount[(row0 + lane) * nseg + seg] == maybe;
+    unsigned todo = __ballot_sync(0xffffffffu, marked);
+    const int64_t j = static_cast<int64_t>(seg) * kPwSeg + lane * 4;
+    while (todo) {                                                   // warp-uniform
+        const int64_t row = row0 + (__ffs(todo) - 1);
+        todo &= todo - 1;
+        int4 v;
+        const unsigned n = __reduce_add_sync(0xffffffffu, static_cast<unsigned>(__popc(pw_keep_mask4(C + row * ldc, j, mj, d, norms_i[row], norms_j, v))));
+        if (lane == 0) segcount[row * nseg + seg] = n;
     }
 }
 

@@ -112,8 +112,71 @@ __device__ __forceinline__ void um_cluster_sync()
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
+
+// Pre-filter fused into the epilogue.  The thread holds one row x 128 columns = one segment of the compaction pass in
+// registers.  An entry is kept iff dot >= need(i, j) = (floor(0.05 * (n_i + n_j)) + 1) * d (see pw_keep), and
+//     need(i, j) > 0.05 * (n_i + n_j) * d * (1 - 2^-51) >= lo_i + lo_j,   lo_x = floor(0.05 * n_x * d * (1 - 2^-40)),
+// so "dot < lo_i + lo_j" (one add, one compare) proves that an entry is dropped.  A row none of whose 128 entries
+// passes that test is not stored at all and gets segcount 0; the others (about 1 % of the segments for sketches)
+// are stored and marked kUmMaybe, and pairwise_recount_kernel applies the exact test to those segments only.  That
+// removes the dense C round trip through HBM (4 B written + 4 B read per pair) and the full count pass.  Rows or
+// columns whose norm is negative or NaN (no valid bound) are always marked.  norms_i == nullptr: plain GEMM.
+constexpr uint32_t kUmMaybe = 0xFFFFFFFFu;
+constexpr int kUmLoMax = (1 << 30) - 1;          // bounds are clamped (still lower bounds), their sum fits int32
+
+struct UmFilter {
+    const double* norms_i;                       // squared norms of the block's rows (block-local index)
+    const double* norms_j;
+    uint32_t* segcount;                          // [mi][nseg], nseg = tiles of 128 columns
+    int nseg;
+    int d;
+};
+
+// lower bound lo_x of the contribution of one squared norm to need(i, j); false if there is none (negative / NaN norm)
+__device__ __forceinline__ bool um_lower_bound(double norm_sq, int d, int& lo)
+{
+    const double x = 0.05 * norm_sq * static_cast<double>(d) * (1.0 - 0x1p-40);
+    lo = __double2int_rd(fmin(x, static_cast<double>(kUmLoMax)));
+    return x >= 0.0;
+}
+
+// Called by all 128 epilogue threads of the CTA (warps 2..5) once per tile; lo_tile = 128 ints + 1 flag of shared memory.
+__device__ __forceinline__ void um_store_row(const uint32_t (&v)[kUmBN], int64_t row, int64_t col, int tile_n, int64_t mi, int64_t mj,
+                                             int32_t* __restrict__ C, int64_t ldc, const UmFilter& f, int* lo_tile)
+{
+    const int ncols = static_cast<int>(max(int64_t{0}, min(static_cast<int64_t>(kUmBN), mj - col)));
+    if (f.norms_i) {                             // stage the tile's column bounds: every thread needs all 128 of them
+        const int t = static_cast<int>(threadIdx.x) - 64;
+        asm volatile("bar.sync 1, 128;" ::: "memory");                 // the previous tile's readers are done
+        if (t == 0) lo_tile[kUmBN] = 0;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        int lo = kUmLoMax;                                           // columns past the end: never "maybe" (their dot is 0)
+        if (t < ncols && !um_lower_bound(f.norms_j[col + t], f.d, lo)) lo_tile[kUmBN] = 1;
+        lo_tile[t] = lo;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
+    if (row >= mi || ncols == 0) return;
+    if (f.norms_i) {
+        int lo_i;
+        bool maybe = !um_lower_bound(f.norms_i[row], f.d, lo_i) || lo_tile[kUmBN] != 0;
+#pragma unroll
+        for (int e = 0; e < kUmBN; ++e) maybe |= static_cast<int32_t>(v[e]) >= lo_i + lo_tile[e];
+        f.segcount[row * f.nseg + tile_n] = maybe ? kUmMaybe : 0u;
+        if (!maybe) return;
+    }
+    int32_t* dst = C + row * ldc + col;
+    if (ncols == kUmBN) {                        // ldc % 4 == 0, C 16-byte aligned (host)
+#pragma unroll
+        for (int e = 0; e < kUmBN; e += 4) *reinterpret_cast<int4*>(dst + e) = make_int4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+    } else {
+#pragma unroll
+        for (int e = 0; e < kUmBN; ++e)
+            if (e < ncols) dst[e] = static_cast<int32_t>(v[e]);
+    }
+}
+
 #ifdef MVS_UMMA_PROBE
-__device__ unsigned long long um_probe_cycles[1024][4];                // per CTA: MMA thread waits (tmem_empty, full), total, tiles
+__device__ unsigned long long um_probe_cycles[1024][8];                // per CTA: MMA thread waits (tmem_empty, full), total, tiles; epilogue wait, drain, rest
 #define UM_PROBE_T(var) const long long var = clock64()
 #else
 #define UM_PROBE_T(var)
@@ -134,11 +197,12 @@ __device__ unsigned long long um_probe_cycles[1024][4];                // per CT
 template <int CM, int CN, bool F22>
 __global__ void __launch_bounds__(kUmThreads, 1)
 pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, UmmaPlan plan, int k_pad,
-                         int a_row0, int64_t mi, int64_t mj, int32_t* __restrict__ C, int64_t ldc, int super_n, int nsuper)
+                         int a_row0, int64_t mi, int64_t mj, int32_t* __restrict__ C, int64_t ldc, int super_n, int nsuper, UmFilter filt)
 {
     constexpr int CS = CM * CN;
     constexpr int kARows = kUmBM / CN, kBRows = kUmBN / CM;            // rows of a tile this CTA fetches
     extern __shared__ uint8_t um_smem_raw[];
+    __shared__ int um_lo_tile[kUmBN + 1];                              // column bounds of the epilogue's current tile + "no bound" flag
     const uint32_t base = (um_smem(um_smem_raw) + 1023u) & ~1023u;     // SW128 tiles need 1024-byte alignment
     uint8_t* gen = um_smem_raw + (base - um_smem(um_smem_raw));
     const int stage_bytes = (plan.a_count + plan.b_count) * kUmTile;
@@ -309,11 +373,16 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     } else {                                                           // ---- epilogue: TMEM -> Horner -> registers -> C ----
         const int q = warp & 3;                                        // TMEM lane quarter this warp may read
         uint32_t tile_phase = 0;
+#ifdef MVS_UMMA_PROBE
+        long long e_wait = 0, e_drain = 0, e_rest = 0;
+#endif
         for (int st_id = cluster_id; st_id < nsuper; st_id += nclusters, tile_phase ^= 1) {
             const int sm_ = st_id / super_n, sn_ = st_id - sm_ * super_n;
             const int tile_m = sm_ * CM + rm, tile_n = sn_ * CN + rn;
+            UM_PROBE_T(te0);
             um_mbar_wait(bar_tmem_full, tile_phase);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            UM_PROBE_T(te1);
             uint32_t v[kUmBN];                                         // this thread's row of the tile: 128 registers
 #pragma unroll
             for (int c0 = 0; c0 < kUmBN; c0 += 32) {
@@ -329,20 +398,23 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) um_mbar_arrive(bar_tmem_empty);             // TMEM may be overwritten; the stores below overlap the next tile
+            UM_PROBE_T(te2);
             const int64_t row = static_cast<int64_t>(tile_m) * kUmBM + q * 32 + lane;
             const int64_t col = static_cast<int64_t>(tile_n) * kUmBN;
-            if (row < mi && col < mj && !(plan.probe & 4)) {
-                int32_t* dst = C + row * ldc + col;
-                if (col + kUmBN <= mj) {                               // ldc % 4 == 0, C 16-byte aligned (host)
-#pragma unroll
-                    for (int e = 0; e < kUmBN; e += 4) *reinterpret_cast<int4*>(dst + e) = make_int4(v[e], v[e + 1], v[e + 2], v[e + 3]);
-                } else {
-#pragma unroll
-                    for (int e = 0; e < kUmBN; ++e)
-                        if (col + e < mj) dst[e] = static_cast<int32_t>(v[e]);
-                }
-            }
+            if (!(plan.probe & 4)) um_store_row(v, row, col, tile_n, mi, mj, C, ldc, filt, um_lo_tile);
+#ifdef MVS_UMMA_PROBE
+            e_wait += te1 - te0;
+            e_drain += te2 - te1;
+            e_rest += clock64() - te2;
+#endif
         }
+#ifdef MVS_UMMA_PROBE
+        if (threadIdx.x == 64) {
+            um_probe_cycles[blockIdx.x][4] = e_wait;
+            um_probe_cycles[blockIdx.x][5] = e_drain;
+            um_probe_cycles[blockIdx.x][6] = e_rest;
+        }
+#endif
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -407,9 +479,10 @@ template <bool F22>
 __global__ void __launch_bounds__(kUmThreads, 1)
 pairwise_dot_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, UmmaPlan plan, int k_pad,
                               int a_row0, int a_row_last, int64_t mi, int64_t mj, int32_t* __restrict__ C, int64_t ldc, int tiles_n,
-                              int nsuper)
+                              int nsuper, UmFilter filt)
 {
     extern __shared__ uint8_t um_smem_raw[];
+    __shared__ int um_lo_tile[kUmBN + 1];                              // column bounds of the epilogue's current tile + "no bound" flag
     const uint32_t base = (um_smem(um_smem_raw) + 1023u) & ~1023u;
     uint8_t* gen = um_smem_raw + (base - um_smem(um_smem_raw));
     const int stage_bytes = plan.a_count * kUmTile + plan.b_count * kUmPairBTile;
@@ -557,17 +630,7 @@ pairwise_dot_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __g
             if (lane == 0) um_mbar_arrive_remote(leader_tmem_empty);
             const int64_t row = static_cast<int64_t>(tile_m) * kUmBM + q * 32 + lane;
             const int64_t col = static_cast<int64_t>(tile_n) * kUmBN;
-            if (row < mi && col < mj && !(plan.probe & 4)) {
-                int32_t* dst = C + row * ldc + col;
-                if (col + kUmBN <= mj) {
-#pragma unroll
-                    for (int e = 0; e < kUmBN; e += 4) *reinterpret_cast<int4*>(dst + e) = make_int4(v[e], v[e + 1], v[e + 2], v[e + 3]);
-                } else {
-#pragma unroll
-                    for (int e = 0; e < kUmBN; ++e)
-                        if (col + e < mj) dst[e] = static_cast<int32_t>(v[e]);
-                }
-            }
+            if (!(plan.probe & 4)) um_store_row(v, row, col, tile_n, mi, mj, C, ldc, filt, um_lo_tile);
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");

@@ -42,6 +42,7 @@ def main():
     ap.add_argument("--path", type=int, default=0, help="0 = tcgen05 limb GEMM, 1 = IMAD GEMM, 2 = mma.sync limb GEMM")
     ap.add_argument("--cluster", type=int, default=0, help="tcgen05 path, CTAs per cluster: 0/1 = 1x1 (default), 2 = 1x2, 4 = 2x2 with TMA multicast")
     ap.add_argument("--pair", type=int, default=0, help="tcgen05 path: 1 = CTA pairs (cta_group::2), 2 = single CTAs, 0 = library default")
+    ap.add_argument("--fuse", type=int, default=0, help="tcgen05 path: 0 = keep-test in the GEMM epilogue (default), 2 = separate count pass")
     ap.add_argument("--stream", type=int, default=0, help="1 = tcgen05 path streams limb pairs instead of fused stages")
     ap.add_argument("--limbs", type=int, default=0, help="force at least this many base-256 limbs (0 = from the data)")
     a = ap.parse_args()
@@ -53,6 +54,7 @@ def main():
     sk.set_option("pairwise_stream", a.stream)
     sk.set_option("pairwise_cluster", a.cluster)
     sk.set_option("pairwise_pair", a.pair)
+    sk.set_option("pairwise_fuse", a.fuse)
     pw.pairwise_shard(sk, v[:256], nrm[:256])                         # warm-up (module load, clocks)
     runs = []
     for _ in range(a.steps):
@@ -66,7 +68,7 @@ def main():
     out = {
         "metric": "pairs_compared_per_sec_d%d" % a.d, "unit": "pairs/s", "n_vectors": a.n, "d": a.d,
         "kept_pairs": best[4], "value": pairs / k_s, "kernel_ms": k_s * 1e3, "gemm_ms": best[1],
-        "filter_ms": best[2], "prep_ms": best[7], "path": {0: "tcgen05-limbs", 1: "imad", 2: "mma.sync-limbs"}[a.path], "forced_limbs": a.limbs, "stream": a.stream, "cluster": a.cluster, "pair": a.pair,
+        "filter_ms": best[2], "prep_ms": best[7], "path": {0: "tcgen05-limbs", 1: "imad", 2: "mma.sync-limbs"}[a.path], "forced_limbs": a.limbs, "stream": a.stream, "cluster": a.cluster, "pair": a.pair, "fuse": a.fuse,
         "max_abs_entry": int(np.abs(v).max()),
         "e2e": {"value": pairs / (min(x[3] for x in runs) * 1e-3), "unit": "pairs/s", "wall_ms": min(x[3] for x in runs),
                 "h2d_bytes": best[5], "d2h_bytes": best[6], "api": "mvs_pairwise_shard (host vectors in, host triples out)"},

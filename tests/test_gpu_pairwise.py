@@ -16,10 +16,11 @@ pytestmark = pytest.mark.gpu
 # every test runs on the tcgen05 limb GEMM (limbs from the data = FUSED stages, forced to 3 and 4 limbs = 8 and 10 limb
 # products streamed pair by pair; also as clusters of 1 x 2 and 2 x 2 CTAs with TMA multicast), on the mma.sync limb GEMM
 # and on the IMAD GEMM: all must give the reference's bits
-# "pair" = tcgen05 cta_group::2 (two SMs per 256 x 128 tile); fourth entry = option "pairwise_pair" (2 = single CTAs)
-PATHS = {"default": (0, 0, 0, 0), "umma": (0, 0, 0, 2), "umma3": (0, 3, 0, 2), "umma4": (0, 4, 0, 2), "umma_1x2": (0, 0, 2, 2), "umma_2x2": (0, 0, 4, 2),
-         "umma4_2x2": (0, 4, 4, 2), "pair": (0, 0, 0, 1), "pair3": (0, 3, 0, 1), "pair4": (0, 4, 0, 1),
-         "mma": (2, 0, 0, 0), "mma4": (2, 4, 0, 0), "imad": (1, 0, 0, 0)}
+# "pair" = tcgen05 cta_group::2 (two SMs per 256 x 128 tile); entries: options pairwise_path, pairwise_limbs, pairwise_cluster,
+# pairwise_pair (2 = single CTAs), pairwise_fuse (2 = separate count pass instead of the keep-test in the GEMM epilogue)
+PATHS = {"default": (0, 0, 0, 0, 0), "umma": (0, 0, 0, 2, 0), "umma3": (0, 3, 0, 2, 0), "umma4": (0, 4, 0, 2, 0), "umma_1x2": (0, 0, 2, 2, 0),
+         "umma_2x2": (0, 0, 4, 2, 0), "umma4_2x2": (0, 4, 4, 2, 0), "pair": (0, 0, 0, 1, 0), "pair3": (0, 3, 0, 1, 0), "pair4": (0, 4, 0, 1, 0),
+         "umma_nofuse": (0, 0, 0, 2, 2), "pair_nofuse": (0, 0, 0, 1, 2), "mma": (2, 0, 0, 0, 0), "mma4": (2, 4, 0, 0, 0), "imad": (1, 0, 0, 0, 0)}
 
 
 @pytest.fixture(scope="module", params=list(PATHS))
@@ -29,6 +30,7 @@ def sk(request):
     s.set_option("pairwise_limbs", PATHS[request.param][1])
     s.set_option("pairwise_cluster", PATHS[request.param][2])
     s.set_option("pairwise_pair", PATHS[request.param][3])
+    s.set_option("pairwise_fuse", PATHS[request.param][4])
     yield s
     s.close()
 
@@ -94,7 +96,10 @@ def test_threshold_edges_and_negative_quotients(sk):
     a = np.array([[1, 0, 0, 0, 0, 0, 0, 0], [8, 0, 0, 0, 0, 0, 0, 0], [-1, 0, 0, 0, 0, 0, 0, 0]], dtype=np.int32)
     b = np.array([[1, 0, 0, 0, 0, 0, 0, 0], [7, 0, 0, 0, 0, 0, 0, 0], [9, 0, 0, 0, 0, 0, 0, 0]], dtype=np.int32)
     for ni, nj in ((np.zeros(3), np.zeros(3)), (np.full(3, -1.0), np.zeros(3)), (np.full(3, 10.0), np.full(3, 10.0)),
-                   (np.array([0.0, 20.0, 0.0]), np.array([0.0, 0.0, 100.0]))):
+                   (np.array([0.0, 20.0, 0.0]), np.array([0.0, 0.0, 100.0])),
+                   # thresholds the division-free test does not cover: NaN, +-inf, >= 2^31, -0.0
+                   (np.array([np.nan, np.inf, -np.inf]), np.zeros(3)), (np.array([1e12, 4.2e10, -0.0]), np.array([-0.0, 4.3e10, -0.0])),
+                   (np.array([-0.0, 4.2949e10, 4.29496e10]), np.array([-0.0, 0.0, 1.0]))):
         got = pw.compute_sparse_dot_products(sk, a, b, ni, nj)
         assert same(got, oracle_pairwise(a, b, 8, ni, nj))
 
