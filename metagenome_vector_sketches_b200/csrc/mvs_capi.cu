@@ -85,6 +85,8 @@ struct mvs_ctx {
     DevBuf pw_ws[kPairwiseSlots];                // grow-only device workspace of the pairwise entry points (freed by mvs_destroy
                                                  // or option "release_workspace"): no cudaMalloc / cudaFree in the steady state
     void* pw_pinned = nullptr;                   // 256 bytes of pinned host memory for small read-backs
+    void* pw_stage = nullptr;                    // pinned staging ring for uploads from pageable caller memory
+    size_t pw_stage_bytes = 0;
 };
 
 namespace {
@@ -387,8 +389,26 @@ void* mvs_internal_pinned_scratch(mvs_ctx* ctx)
     }
     return ctx->pw_pinned;
 }
+void* mvs_internal_pinned_stage(mvs_ctx* ctx, size_t bytes)
+{
+    if (ctx->pw_stage_bytes < bytes) {
+        if (ctx->pw_stage) cudaFreeHost(ctx->pw_stage);
+        ctx->pw_stage = nullptr;
+        ctx->pw_stage_bytes = 0;
+        if (cudaHostAlloc(&ctx->pw_stage, bytes, cudaHostAllocDefault) != cudaSuccess) {
+            cudaGetLastError();
+            ctx->pw_stage = nullptr;
+            return nullptr;
+        }
+        ctx->pw_stage_bytes = bytes;
+    }
+    return ctx->pw_stage;
+}
 static void release_workspace(mvs_ctx* ctx)
 {
+    if (ctx->pw_stage) cudaFreeHost(ctx->pw_stage);
+    ctx->pw_stage = nullptr;
+    ctx->pw_stage_bytes = 0;
     for (auto& b : ctx->pw_ws) {
         if (b.p) cudaFree(b.p);
         b.p = nullptr;

@@ -19,3 +19,4 @@ int mvs_internal_pairwise_fuse(const mvs_ctx* ctx);               // option "pai
 // grow-only device buffer number `slot` (0..15) of at least `bytes` bytes, kept until mvs_destroy / option "release_workspace"
 int mvs_internal_workspace(mvs_ctx* ctx, int slot, size_t bytes, void** out);
 void* mvs_internal_pinned_scratch(mvs_ctx* ctx);                 // 256 bytes of pinned host memory (nullptr on failure)
+void* mvs_internal_pinned_stage(mvs_ctx* ctx, size_t bytes);      // persistent pinned staging buffer (nullptr on failure)

@@ -458,43 +458,38 @@ pairwise_count_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int
     }
 }
 
-// After a GEMM with the fused pre-filter (mvs_pairwise_umma.cuh): segments marked `maybe` were stored and get their
-// exact count here; all others are already 0 and were never written to C.  Same warp mapping as the count kernel.
+// One warp per row: reads the row's segment counts (coalesced), replaces every count marked `maybe` -- a segment the
+// GEMM's fused pre-filter (mvs_pairwise_umma.cuh) stored without deciding it -- by the exact count, and writes the
+// row total to rowoff[row].  After the separate count pass nothing is marked and this is just the row sum.
 __global__ void __launch_bounds__(256)
-pairwise_recount_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int64_t ldc, int d,
-                        const double* __restrict__ norms_i, const double* __restrict__ norms_j,
-                        uint32_t* __restrict__ segcount, int nseg, uint32_t maybe)
+pairwise_rowsum_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int64_t ldc, int d,
+                       const double* __restrict__ norms_i, const double* __restrict__ norms_j,
+                       uint32_t* __restrict__ segcount, int nseg, uint32_t maybe, unsigned long long* __restrict__ rowoff)
 {
-    const int64_t w = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int64_t groups = (mi + kPwRows - 1) / kPwRows;
-    if (w >= groups * nseg) return;
-    const int64_t row0 = (w / nseg) * kPwRows;
-    const int seg = static_cast<int>(w % nseg);
+    const int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= mi) return;
     const int lane = threadIdx.x & 31;
-    const bool marked = lane < kPwRows && row0 + lane < mi && segcount[(row0 + lane) * nseg + seg] == maybe;
-    unsigned todo = __ballot_sync(0xffffffffu, marked);
-    const int64_t j = static_cast<int64_t>(seg) * kPwSeg + lane * 4;
-    while (todo) {                                                   // warp-uniform
-        const int64_t row = row0 + (__ffs(todo) - 1);
-        todo &= todo - 1;
-        int4 v;
-        const unsigned n = __reduce_add_sync(0xffffffffu, static_cast<unsigned>(__popc(pw_keep_mask4(C + row * ldc, j, mj, d, norms_i[row], norms_j, v))));
-        if (lane == 0) segcount[row * nseg + seg] = n;
+    unsigned long long total = 0;
+    for (int base = 0; base < nseg; base += 32) {
+        const int seg = base + lane;
+        unsigned c = seg < nseg ? segcount[row * nseg + seg] : 0u;
+        unsigned todo = __ballot_sync(0xffffffffu, c == maybe);
+        while (todo) {                                               // warp-uniform
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            int4 v;
+            const int64_t j = static_cast<int64_t>(base + src) * kPwSeg + lane * 4;
+            const unsigned n = __reduce_add_sync(0xffffffffu, static_cast<unsigned>(__popc(pw_keep_mask4(C + row * ldc, j, mj, d, norms_i[row], norms_j, v))));
+            if (lane == src) {
+                c = n;
+                segcount[row * nseg + seg] = n;
+            }
+        }
+        total += c;
     }
-}
-
-// rowoff[row] = kept columns of the row = sum of its segment counts.  One warp per row.
-__global__ void __launch_bounds__(256)
-pairwise_rowsum_kernel(const uint32_t* __restrict__ segcount, int nseg, unsigned long long* __restrict__ rowoff, int64_t n)
-{
-    const int64_t r = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (r >= n) return;
-    const int lane = threadIdx.x & 31;
-    unsigned long long t = 0;
-    for (int k = lane; k < nseg; k += 32) t += segcount[r * nseg + k];
 #pragma unroll
-    for (int m = 16; m; m >>= 1) t += __shfl_xor_sync(0xffffffffu, t, m);
-    if (lane == 0) rowoff[r] = t;
+    for (int m = 16; m; m >>= 1) total += __shfl_xor_sync(0xffffffffu, total, m);
+    if (lane == 0) rowoff[row] = total;
 }
 
 // In-place exclusive scan of rowoff[0..n), total in rowoff[n].  One CTA of 1024 threads (n <= 8192 rows per call).
@@ -536,6 +531,8 @@ pairwise_scan_kernel(unsigned long long* __restrict__ rowoff, int64_t n)
     if (threadIdx.x == 0) rowoff[n] = carry;
 }
 
+// One warp per row: walks the row's segment counts and writes the triples of the non-empty segments (about 1 % of
+// them) at rowoff[row] + kept entries to the left: (row, col) order, no atomics.
 __global__ void __launch_bounds__(256)
 pairwise_emit_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int64_t ldc, int d,
                      const double* __restrict__ norms_i, const double* __restrict__ norms_j,
@@ -543,42 +540,47 @@ pairwise_emit_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int6
                      int32_t row_base, int32_t col_base, unsigned long long cap,
                      int32_t* __restrict__ rows, int32_t* __restrict__ cols, long long* __restrict__ values)
 {
-    // same warp -> (row group, segment) mapping as the count kernel; almost every warp finds eight zero counts and leaves
-    const int64_t w = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int64_t groups = (mi + kPwRows - 1) / kPwRows;
-    if (w >= groups * nseg) return;
+    const int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= mi) return;
     if (rowoff[mi] > cap) return;                                    // output buffers too small: the host grows them and re-launches
-    const int64_t row0 = (w / nseg) * kPwRows;
-    const int seg = static_cast<int>(w % nseg);
     const int lane = threadIdx.x & 31;
-    const bool mine_nonzero = lane < kPwRows && row0 + lane < mi && segcount[(row0 + lane) * nseg + seg] != 0;
-    unsigned todo = __ballot_sync(0xffffffffu, mine_nonzero);
-    const int64_t j = static_cast<int64_t>(seg) * kPwSeg + lane * 4;
-    while (todo) {                                                   // warp-uniform
-        const int64_t row = row0 + (__ffs(todo) - 1);
-        todo &= todo - 1;
-        unsigned long long before = 0;                                // kept columns of the row left of this segment
-        for (int t = lane; t < seg; t += 32) before += segcount[row * nseg + t];
-#pragma unroll
-        for (int m = 16; m; m >>= 1) before += __shfl_xor_sync(0xffffffffu, before, m);
-        int4 v;
-        const unsigned m4 = pw_keep_mask4(C + row * ldc, j, mj, d, norms_i[row], norms_j, v);
-        unsigned mine = __popc(m4), incl = mine;
+    unsigned long long run = rowoff[row];                             // position of the next triple of this row
+    for (int base = 0; base < nseg; base += 32) {
+        const int seg = base + lane;
+        const unsigned c = seg < nseg ? segcount[row * nseg + seg] : 0u;
+        unsigned todo = __ballot_sync(0xffffffffu, c != 0);
+        if (todo == 0) continue;
+        unsigned incl = c;                                            // inclusive scan of the 32 counts
 #pragma unroll
         for (int m = 1; m < 32; m <<= 1) {
             const unsigned y = __shfl_up_sync(0xffffffffu, incl, m);
             if (lane >= m) incl += y;
         }
-        unsigned long long at = rowoff[row] + before + (incl - mine);
-        const int32_t e[4] = {v.x, v.y, v.z, v.w};
+        while (todo) {                                               // warp-uniform
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const unsigned before = __shfl_sync(0xffffffffu, incl - c, src);
+            int4 v;
+            const int64_t j = static_cast<int64_t>(base + src) * kPwSeg + lane * 4;
+            const unsigned m4 = pw_keep_mask4(C + row * ldc, j, mj, d, norms_i[row], norms_j, v);
+            unsigned mine = __popc(m4), inc2 = mine;
 #pragma unroll
-        for (int t = 0; t < 4; ++t)
-            if (m4 & (1u << t)) {
-                rows[at] = row_base + static_cast<int32_t>(row);
-                cols[at] = col_base + static_cast<int32_t>(j + t);
-                values[at] = static_cast<long long>(e[t]);
-                ++at;
+            for (int m = 1; m < 32; m <<= 1) {
+                const unsigned y = __shfl_up_sync(0xffffffffu, inc2, m);
+                if (lane >= m) inc2 += y;
             }
+            unsigned long long at = run + before + (inc2 - mine);
+            const int32_t e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                if (m4 & (1u << t)) {
+                    rows[at] = row_base + static_cast<int32_t>(row);
+                    cols[at] = col_base + static_cast<int32_t>(j + t);
+                    values[at] = static_cast<long long>(e[t]);
+                    ++at;
+                }
+        }
+        run += __shfl_sync(0xffffffffu, incl, 31);
     }
 }
 

@@ -118,7 +118,7 @@ __device__ __forceinline__ void um_cluster_sync()
 //     need(i, j) > 0.05 * (n_i + n_j) * d * (1 - 2^-51) >= lo_i + lo_j,   lo_x = floor(0.05 * n_x * d * (1 - 2^-40)),
 // so "dot < lo_i + lo_j" (one add, one compare) proves that an entry is dropped.  A row none of whose 128 entries
 // passes that test is not stored at all and gets segcount 0; the others (about 1 % of the segments for sketches)
-// are stored and marked kUmMaybe, and pairwise_recount_kernel applies the exact test to those segments only.  That
+// are stored and marked kUmMaybe, and pairwise_rowsum_kernel applies the exact test to those segments only.  That
 // removes the dense C round trip through HBM (4 B written + 4 B read per pair) and the full count pass.  Rows or
 // columns whose norm is negative or NaN (no valid bound) are always marked.  norms_i == nullptr: plain GEMM.
 constexpr uint32_t kUmMaybe = 0xFFFFFFFFu;
