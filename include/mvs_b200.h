@@ -170,7 +170,8 @@ typedef struct mvs_sparse_result {
     int32_t* cols;         /* n column indices */
     int64_t* values;       /* n dot products (the wrapped int32 value, widened) */
     double gemm_ms;        /* CUDA-event time of the dot-product kernel(s) */
-    double filter_ms;      /* CUDA-event time of threshold + count + scan + emit */
+    double filter_ms;      /* CUDA-event time of the exact count of the pre-filtered segments + scan + emit
+                              (the pre-filter itself runs in the GEMM epilogue) */
     double prep_ms;        /* host wall time of the operand preparation (min/max + int8 limb planes) */
     double wall_ms;        /* host wall clock of the call, copies included */
     uint64_t h2d_bytes, d2h_bytes;
@@ -214,8 +215,14 @@ int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second);
 
 /* Kernel tuning knobs for experiments (0 = default).  Unknown keys are ignored.
  * "pairwise_path": 0 = tcgen05 limb GEMM (TMA + TMEM, default), 1 = IMAD GEMM, 2 = mma.sync limb GEMM;
- * "pairwise_limbs": 0 = from the data, 1..4 = use at least that many base-256 limbs (all paths are exact; the
- * knobs exist for the parity tests). */
+ * "pairwise_limbs": 0 = from the data, 1..4 = use at least that many base-256 limbs;
+ * "pairwise_pair": tcgen05 path, 0 = CTA pairs (cta_group::2, 256 x 128 tiles) when there are two tile rows (default),
+ *                  1 = always pairs, 2 = single CTAs;  "pairwise_cluster": single-CTA kernel in clusters of 2 (1 x 2) or
+ *                  4 (2 x 2) CTAs with TMA multicast;  "pairwise_stream": 1 = stream limb pairs instead of fused stages;
+ * "pairwise_fuse": tcgen05 path, 0 = threshold pre-filter in the GEMM epilogue (default), 2 = separate count pass
+ * (all paths are exact; these knobs exist for the parity tests and the A/B measurements in profiles/);
+ * "release_workspace": frees the device and pinned buffers the pairwise entry points keep between calls (they are
+ * grow-only and otherwise live until mvs_destroy). */
 int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value);
 
 #ifdef __cplusplus

@@ -33,6 +33,31 @@ def make_db(n, d, seed=0):
     return v, nrm
 
 
+def roofline(a, pairs, gemm_ms, imad_peak, max_abs):
+    """Dominant kernel = the limb GEMM.  tcgen05 / mma.sync paths: tensor bound, int8 MACs = pairs x d x limb products
+    (4 for two limbs per side, 10 for four), against the measured dense peak of this pool's B200 (MEASURED_PEAKS.json
+    holds cuBLAS bf16; kind::i8 has twice the bf16 rate: 8192 vs 4096 MAC/clk/SM).  IMAD path: FMA-heavy pipe issue."""
+    if a.path == 1:
+        return {"bound": "int32 IMAD issue (FMA-heavy pipe)", "unit": "TMAC/s", "achieved": pairs * a.d / (gemm_ms * 1e-3) / 1e12,
+                "peak": imad_peak / 1e12, "frac": pairs * a.d / (gemm_ms * 1e-3) / imad_peak,
+                "peak_how": "live microbenchmark mvs_int_issue_peak(1) (IMAD only)", "traffic": None}
+    limbs = max(a.limbs, 1 if max_abs <= 127 else 2 if max_abs <= 32639 else 3 if max_abs <= 8355711 else 4)
+    products = sum(1 for p in range(limbs) for q in range(limbs) if p + q <= 3)
+    ops = 2.0 * pairs * a.d * products
+    peak_tf, how = 2250.0, "nominal dense bf16 (no MEASURED_PEAKS.json)"
+    try:
+        mp = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "MEASURED_PEAKS.json")))
+        peak_tf, how = float(mp["bf16_tflops"]), "MEASURED_PEAKS.json bf16_tflops (burst, cuBLAS)"
+    except (OSError, KeyError, ValueError):
+        pass
+    return {"bound": "tensor", "unit": "TOP/s (int8)", "achieved": ops / (gemm_ms * 1e-3) / 1e12, "peak": 2.0 * peak_tf,
+            "frac": ops / (gemm_ms * 1e-3) / 1e12 / (2.0 * peak_tf), "peak_how": "2 x " + how + ": kind::i8 runs at twice the bf16 rate",
+            "limb_products": products, "int32_mac_equivalent_TMAC_s": pairs * a.d / (gemm_ms * 1e-3) / 1e12,
+            "imad_issue_peak_TMAC_s": imad_peak / 1e12,
+            "algorithmic": "2 x pairs x d x limb products int8 operations; bytes: operands re-read from L2, C stored only for "
+                           "segments that may keep a pair (fused pre-filter)", "traffic": None}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--n", type=int, default=10000)
@@ -72,14 +97,7 @@ def main():
         "max_abs_entry": int(np.abs(v).max()),
         "e2e": {"value": pairs / (min(x[3] for x in runs) * 1e-3), "unit": "pairs/s", "wall_ms": min(x[3] for x in runs),
                 "h2d_bytes": best[5], "d2h_bytes": best[6], "api": "mvs_pairwise_shard (host vectors in, host triples out)"},
-        "roofline": {"bound": "int32 IMAD issue (FMA-heavy pipe) for the algorithmic int32 MACs; the limb path runs "
-                              "4 (2 limbs) .. 10 (4 limbs) int8 tensor MACs per int32 MAC, so frac > 1 means the tensor "
-                              "cores beat the integer pipe", "unit": "TMAC/s",
-                     "achieved": pairs * a.d / (best[1] * 1e-3) / 1e12, "peak": imad_peak / 1e12,
-                     "frac": pairs * a.d / (best[1] * 1e-3) / imad_peak,
-                     "peak_how": "live microbenchmark mvs_int_issue_peak(1) (IMAD only)",
-                     "algorithmic": "one int32 multiply-add per (pair, dimension); bytes: 4*d per vector read once "
-                                    "per 128-row tile from L2, 4 B of dense C written + read per pair"},
+        "roofline": roofline(a, pairs, best[1], imad_peak, int(np.abs(v).max())),
     }
     # parity spot check + CPU baseline on a bounded prefix
     import oracle_util as ou
