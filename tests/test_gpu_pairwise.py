@@ -144,3 +144,14 @@ def test_more_triples_than_the_initial_output_buffers(sk):
     got = pw.compute_sparse_dot_products(sk, v, v, nrm, nrm)
     want = oracle_pairwise(v, v, d, nrm, nrm)
     assert len(want[0]) == n * n and same(got, want)
+
+
+def test_workspace_can_be_released_between_calls(sk):
+    """The context keeps its device buffers between calls; option release_workspace frees them and the next call
+    simply allocates again."""
+    v, nrm = toy()
+    want = oracle_pairwise(v, v, 2048, nrm, nrm)
+    assert same(pw.pairwise_shard(sk, v, nrm), want)
+    sk.set_option("release_workspace", 1)
+    assert same(pw.pairwise_shard(sk, v, nrm), want)
+    assert same(pw.compute_sparse_dot_products(sk, v[:40], v, nrm[:40], nrm), [w[want[0] < 40] for w in want])
