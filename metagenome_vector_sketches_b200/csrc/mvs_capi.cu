@@ -87,6 +87,9 @@ struct mvs_ctx {
     void* pw_pinned = nullptr;                   // 256 bytes of pinned host memory for small read-backs
     void* pw_stage = nullptr;                    // pinned staging ring for uploads from pageable caller memory
     size_t pw_stage_bytes = 0;
+    cudaEvent_t stage_ev[2] = {nullptr, nullptr};    // "the DMA out of ring slot k has finished"
+    bool stage_busy[2] = {false, false};
+    unsigned stage_turn = 0;
 };
 
 namespace {
@@ -404,11 +407,55 @@ void* mvs_internal_pinned_stage(mvs_ctx* ctx, size_t bytes)
     }
     return ctx->pw_stage;
 }
+// Host -> device copy of a caller buffer.  cudaMemcpyAsync from PAGEABLE memory goes through the driver's
+// single-threaded staging copy (~8 GB/s on this box) and blocks the host; here such a buffer is cut into 8 MB chunks
+// that several host threads copy into a two-slot pinned ring while the previous chunk's DMA runs (PCIe rate).
+// Pinned / registered sources are copied directly.  Asynchronous on `st` like cudaMemcpyAsync.
+int mvs_internal_upload(mvs_ctx* ctx, cudaStream_t st, void* dst, const void* src, size_t bytes)
+{
+    constexpr size_t kChunk = 8u << 20;
+    bool pageable = false;
+    if (bytes >= (2u << 20)) {
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, src) == cudaSuccess) pageable = at.type == cudaMemoryTypeUnregistered;
+        else cudaGetLastError();
+    }
+    char* stage = pageable ? static_cast<char*>(mvs_internal_pinned_stage(ctx, 2 * kChunk)) : nullptr;
+    if (stage)
+        for (auto& e : ctx->stage_ev)
+            if (!e && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) {
+                cudaGetLastError();
+                e = nullptr;
+                stage = nullptr;
+            }
+    if (!stage) {
+        MVS_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st));
+        return MVS_OK;
+    }
+    for (size_t off = 0; off < bytes; off += kChunk) {
+        const size_t n = std::min(kChunk, bytes - off);
+        const unsigned k = ctx->stage_turn++ & 1u;
+        char* slot = stage + k * kChunk;
+        if (ctx->stage_busy[k]) MVS_CUDA(ctx, cudaEventSynchronize(ctx->stage_ev[k]));
+        const char* from = static_cast<const char*>(src) + off;
+        constexpr int kParts = 8;
+#pragma omp parallel for num_threads(kParts) schedule(static)
+        for (int p = 0; p < kParts; ++p) {
+            const size_t a = n * p / kParts, b = n * (p + 1) / kParts;
+            std::memcpy(slot + a, from + a, b - a);
+        }
+        MVS_CUDA(ctx, cudaMemcpyAsync(static_cast<char*>(dst) + off, slot, n, cudaMemcpyHostToDevice, st));
+        MVS_CUDA(ctx, cudaEventRecord(ctx->stage_ev[k], st));
+        ctx->stage_busy[k] = true;
+    }
+    return MVS_OK;
+}
 static void release_workspace(mvs_ctx* ctx)
 {
     if (ctx->pw_stage) cudaFreeHost(ctx->pw_stage);
     ctx->pw_stage = nullptr;
     ctx->pw_stage_bytes = 0;
+    ctx->stage_busy[0] = ctx->stage_busy[1] = false;
     for (auto& b : ctx->pw_ws) {
         if (b.p) cudaFree(b.p);
         b.p = nullptr;
@@ -479,6 +526,8 @@ void mvs_destroy(mvs_ctx* ctx)
             if (e) cudaEventDestroy(e);
     if (ctx->d_sink) cudaFree(ctx->d_sink);
     release_workspace(ctx);
+    for (auto& e : ctx->stage_ev)
+        if (e) cudaEventDestroy(e);
     if (ctx->pw_pinned) cudaFreeHost(ctx->pw_pinned);
     cudaGetLastError();
     delete ctx;
@@ -541,9 +590,7 @@ int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offse
         if (sumsq && (rc = ensure_dev(ctx, sl.sumsq, static_cast<size_t>(rows) * sizeof(uint64_t))) != MVS_OK) break;
         if (out16 && (rc = ensure_dev(ctx, sl.out16, static_cast<size_t>(rows) * row_bytes / 2)) != MVS_OK) break;
         if (nh) {
-            cudaError_t e = cudaMemcpyAsync(sl.hashes.p, hashes + h0, nh * sizeof(uint64_t), cudaMemcpyHostToDevice,
-                                            sl.stream);
-            if (e != cudaSuccess) { ctx->last_cuda = e; cudaGetLastError(); rc = MVS_ERR_CUDA; break; }
+            if ((rc = mvs_internal_upload(ctx, sl.stream, sl.hashes.p, hashes + h0, nh * sizeof(uint64_t))) != MVS_OK) break;
             ctx->timing.h2d_bytes += nh * sizeof(uint64_t);
         }
         rc = run_range(ctx, sl, static_cast<const uint64_t*>(sl.hashes.p), offsets, s0, s1, h0, s0, g, seed,

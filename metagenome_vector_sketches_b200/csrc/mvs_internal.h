@@ -20,3 +20,5 @@ int mvs_internal_pairwise_fuse(const mvs_ctx* ctx);               // option "pai
 int mvs_internal_workspace(mvs_ctx* ctx, int slot, size_t bytes, void** out);
 void* mvs_internal_pinned_scratch(mvs_ctx* ctx);                 // 256 bytes of pinned host memory (nullptr on failure)
 void* mvs_internal_pinned_stage(mvs_ctx* ctx, size_t bytes);      // persistent pinned staging buffer (nullptr on failure)
+// cudaMemcpyAsync(host -> device) that takes pageable sources through a pinned ring filled by several host threads
+int mvs_internal_upload(mvs_ctx* ctx, cudaStream_t st, void* dst, const void* src, size_t bytes);

@@ -56,44 +56,6 @@ struct Triples {
         }                                                                     \
     } while (0)
 
-// Host -> device copy of a caller buffer that is (in general) pageable: cudaMemcpyAsync from pageable memory goes
-// through the driver's single-threaded staging copy (~8 GB/s here).  Instead the buffer is cut into 8 MB chunks that
-// several host threads copy into a two-slot pinned ring while the previous chunk's DMA runs (PCIe rate, ~4x faster).
-int upload(mvs_ctx* ctx, cudaStream_t st, void* dst, const void* src, size_t bytes)
-{
-    constexpr size_t kChunk = 8u << 20;
-    if (bytes < (4u << 20)) {
-        PW_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st));
-        return MVS_OK;
-    }
-    char* stage = static_cast<char*>(mvs_internal_pinned_stage(ctx, 2 * kChunk));
-    if (!stage) {                                // no pinned memory: plain copy
-        PW_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st));
-        return MVS_OK;
-    }
-    cudaEvent_t ev[2];
-    PW_CUDA(ctx, cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
-    PW_CUDA(ctx, cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
-    struct Guard { cudaEvent_t* e; ~Guard() { cudaEventDestroy(e[0]); cudaEventDestroy(e[1]); } } guard{ev};
-    size_t i = 0;
-    for (size_t off = 0; off < bytes; off += kChunk, ++i) {
-        const size_t n = std::min(kChunk, bytes - off);
-        char* slot = stage + (i & 1) * kChunk;
-        if (i >= 2) PW_CUDA(ctx, cudaEventSynchronize(ev[i & 1]));     // the DMA out of this slot has finished
-        const char* from = static_cast<const char*>(src) + off;
-        constexpr int kParts = 8;
-#pragma omp parallel for num_threads(kParts) schedule(static)
-        for (int p = 0; p < kParts; ++p) {
-            const size_t a = n * p / kParts, b = n * (p + 1) / kParts;
-            std::memcpy(slot + a, from + a, b - a);
-        }
-        PW_CUDA(ctx, cudaMemcpyAsync(static_cast<char*>(dst) + off, slot, n, cudaMemcpyHostToDevice, st));
-        PW_CUDA(ctx, cudaEventRecord(ev[i & 1], st));
-    }
-    PW_CUDA(ctx, cudaStreamSynchronize(st));     // the ring may be reused by the next call
-    return MVS_OK;
-}
-
 // An int32 operand matrix resident in HBM, plus (tensor-core path) its int8 limb planes.
 struct Operand {
     const int32_t* v = nullptr;                  // [n x d] int32
@@ -515,8 +477,8 @@ int mvs_pairwise_block(mvs_ctx* ctx, const int32_t* block_i, int64_t mi, const i
         PW_RC(B.alloc(ctx, kWsB, bb));
         PW_RC(ni.alloc(ctx, kWsNi, static_cast<size_t>(mi) * 8));
         PW_RC(nj.alloc(ctx, kWsNj, static_cast<size_t>(mj) * 8));
-        PW_RC(upload(ctx, st, A.p, block_i, ab));
-        PW_RC(upload(ctx, st, B.p, block_j, bb));
+        PW_RC(mvs_internal_upload(ctx, st, A.p, block_i, ab));
+        PW_RC(mvs_internal_upload(ctx, st, B.p, block_j, bb));
         PW_CUDA(ctx, cudaMemcpyAsync(ni.p, norms_i, static_cast<size_t>(mi) * 8, cudaMemcpyHostToDevice, st));
         PW_CUDA(ctx, cudaMemcpyAsync(nj.p, norms_j, static_cast<size_t>(mj) * 8, cudaMemcpyHostToDevice, st));
         h2d = ab + bb + static_cast<uint64_t>(mi + mj) * 8;
@@ -553,7 +515,7 @@ int mvs_pairwise_shard(mvs_ctx* ctx, const int32_t* vectors, int64_t n_total, in
         const size_t vb = static_cast<size_t>(n_total) * d * 4;
         PW_RC(V.alloc(ctx, kWsB, vb));
         PW_RC(nrm.alloc(ctx, kWsNj, static_cast<size_t>(n_total) * 8));
-        PW_RC(upload(ctx, st, V.p, vectors, vb));
+        PW_RC(mvs_internal_upload(ctx, st, V.p, vectors, vb));
         PW_CUDA(ctx, cudaMemcpyAsync(nrm.p, norms_sq, static_cast<size_t>(n_total) * 8, cudaMemcpyHostToDevice, st));
         h2d = vb + static_cast<uint64_t>(n_total) * 8;
         Operand op, unused;
