@@ -155,3 +155,37 @@ def test_workspace_can_be_released_between_calls(sk):
     sk.set_option("release_workspace", 1)
     assert same(pw.pairwise_shard(sk, v, nrm), want)
     assert same(pw.compute_sparse_dot_products(sk, v[:40], v, nrm[:40], nrm), [w[want[0] < 40] for w in want])
+
+
+def test_full_size_shard_properties():
+    """10 000 vectors x d = 2048 (two GEMM row blocks, CTA pairs, fused pre-filter) is too big for the oracle; check what
+    does not depend on size: the kept set is symmetric with equal values, the diagonal is kept with value = sum v^2,
+    rows and columns come out in (row, col) order, every kept value equals an int64 numpy dot product on a sample, the
+    keep-test holds for all kept pairs and fails for a sample of dropped ones, and a 300-row shard equals the oracle."""
+    n, d = 10000, 2048
+    rng = np.random.default_rng(5)
+    fam = np.rint(rng.normal(0.0, 190.0, ((n + 19) // 20, d)))
+    v = (fam[np.arange(n) // 20] + np.rint(rng.normal(0.0, 110.0, (n, d)))).astype(np.int32)
+    nrm = norms_sq_like_reference(v, d)
+    with mvs.Sketcher(0) as s:
+        r = pw.pairwise_shard(s, v, nrm)
+        part = pw.pairwise_shard(s, v, nrm, 4990, 5290)
+    rows, cols, vals = r.rows.astype(np.int64), r.cols.astype(np.int64), r.values
+    key = rows * n + cols
+    assert np.all(np.diff(key) > 0)                                                  # (row, col) order, no duplicates
+    tkey = cols * n + rows
+    order = np.argsort(tkey)
+    assert np.array_equal(tkey[order], key) and np.array_equal(vals[order], vals)    # symmetric
+    diag = rows == cols
+    assert diag.sum() == n and np.array_equal(vals[diag], (v.astype(np.int64) ** 2).sum(axis=1))
+    pick = rng.choice(len(rows), 2000, replace=False)
+    exact = np.einsum("ij,ij->i", v[rows[pick]].astype(np.int64), v[cols[pick]].astype(np.int64))
+    assert np.array_equal(vals[pick], exact)                                         # |dot| < 2^31 here: no wrap
+    q = np.trunc(vals / d)                                                           # the reference's keep-test on every kept pair
+    assert np.all(q > 0.05 * (nrm[rows] + nrm[cols]))
+    ri, ci = rng.integers(0, n, 20000), rng.integers(0, n, 20000)
+    dots = np.einsum("ij,ij->i", v[ri].astype(np.int64), v[ci].astype(np.int64))
+    keep = np.trunc(dots / d) > 0.05 * (nrm[ri] + nrm[ci])
+    assert np.array_equal(keep, np.isin(ri * n + ci, key))                           # dropped pairs really fail it
+    want = oracle_pairwise(v[4990:5290], v, d, nrm[4990:5290], nrm)
+    assert same(part, (want[0] + 4990, want[1], want[2]))
