@@ -385,7 +385,7 @@ int run_blocks(mvs_ctx* ctx, cudaStream_t st, Operand& A, int64_t begin, int64_t
 {
     const int64_t mj = B.n;
     const int64_t ldc = (mj + 3) & ~int64_t{3};
-    const int64_t rb = std::min<int64_t>(std::max<int64_t>(128, std::min<int64_t>(8192, (int64_t{1} << 30) / (4 * std::max<int64_t>(ldc, 1)) / 128 * 128)),
+    const int64_t rb = std::min<int64_t>(std::max<int64_t>(128, std::min<int64_t>(16384, (int64_t{1} << 30) / (4 * std::max<int64_t>(ldc, 1)) / 256 * 256)),
                                          (end - begin + 127) / 128 * 128);
     const int nseg = static_cast<int>((mj + mvs::kPwSeg - 1) / mvs::kPwSeg);
     Dev C, segcount, rowoff, mm;
@@ -397,6 +397,7 @@ int run_blocks(mvs_ctx* ctx, cudaStream_t st, Operand& A, int64_t begin, int64_t
     PW_RC(segcount.alloc(ctx, kWsSeg, static_cast<size_t>(rb) * nseg * 4));
     PW_RC(rowoff.alloc(ctx, kWsRowoff, static_cast<size_t>(rb + 1) * 8));
     if (mvs_internal_pairwise_path(ctx) != 1) {
+        PW_CUDA(ctx, cudaStreamSynchronize(st));                      // the asynchronous upload is not part of prep_ms
         const auto t0 = std::chrono::steady_clock::now();
         PW_RC(mm.alloc(ctx, kWsMinmax, 8));
         PW_CUDA(ctx, cudaFuncSetAttribute(mvs::pairwise_dot_imma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mvs::kImSmemBytes));

@@ -492,7 +492,7 @@ pairwise_rowsum_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, in
     if (lane == 0) rowoff[row] = total;
 }
 
-// In-place exclusive scan of rowoff[0..n), total in rowoff[n].  One CTA of 1024 threads (n <= 8192 rows per call).
+// In-place exclusive scan of rowoff[0..n), total in rowoff[n].  One CTA of 1024 threads (n <= 16384 rows per call: a few sequential chunks).
 __global__ void __launch_bounds__(1024)
 pairwise_scan_kernel(unsigned long long* __restrict__ rowoff, int64_t n)
 {
