@@ -204,24 +204,34 @@ int limbs_for_range(int lo, int hi)
 
 int prepare_operand(mvs_ctx* ctx, cudaStream_t st, Operand& op, int planes_slot, int d, int* d_mm, int* h_pinned)
 {
+    // one extra zero tile of rows: a row block may start at any row (shards), its last tile then reads past n
+    op.n_pad = (op.n + mvs::kImBM - 1) / mvs::kImBM * mvs::kImBM + mvs::kImBM;
+    op.k_pad = (d + mvs::kUmBKB - 1) / mvs::kUmBKB * mvs::kUmBKB;      // 128: a multiple of both paths' k-slices
+    const int forced = mvs_internal_pairwise_limbs(ctx);
+    int sms = 148;
+    PW_CUDA(ctx, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, mvs_internal_device(ctx)));
+    const int64_t quads = op.n_pad * (op.k_pad / 4);
+    const unsigned grid = static_cast<unsigned>(std::min<int64_t>((quads + 255) / 256, static_cast<int64_t>(sms) * 16));
+    auto split = [&](int P, int* mm) {
+        const int rc = op.planes.alloc(ctx, planes_slot, static_cast<size_t>(P) * op.n_pad * op.k_pad);
+        if (rc != MVS_OK) return rc;
+        mvs::pairwise_split_kernel<<<grid, 256, 0, st>>>(op.v, op.n, d, P, op.planes.as<int8_t>(), op.n_pad, op.k_pad, mm);
+        mvs_internal_count_launches(ctx, 1);
+        if (cudaGetLastError() != cudaSuccess) return static_cast<int>(MVS_ERR_CUDA);
+        return static_cast<int>(MVS_OK);
+    };
+    // sketch entries are ~sqrt(#hashes): two limbs is the normal case.  Split for the guess and measure the range in the
+    // same pass; only if the range asks for another limb count is V read a second time.
+    const int guess = std::max(2, forced);
     int* mm = h_pinned;                          // pinned: the two small copies are truly asynchronous
     mm[0] = 2147483647;
     mm[1] = -2147483647 - 1;
     PW_CUDA(ctx, cudaMemcpyAsync(d_mm, mm, 2 * sizeof(int), cudaMemcpyHostToDevice, st));
-    mvs::pairwise_minmax_kernel<<<1184, 256, 0, st>>>(op.v, op.n * d, d_mm);
-    PW_CUDA(ctx, cudaGetLastError());
+    PW_RC(split(guess, d_mm));
     PW_CUDA(ctx, cudaMemcpyAsync(mm, d_mm, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
     PW_CUDA(ctx, cudaStreamSynchronize(st));
-    op.P = std::max(limbs_for_range(mm[0], mm[1]), mvs_internal_pairwise_limbs(ctx));
-    // one extra zero tile of rows: a row block may start at any row (shards), its last tile then reads past n
-    op.n_pad = (op.n + mvs::kImBM - 1) / mvs::kImBM * mvs::kImBM + mvs::kImBM;
-    op.k_pad = (d + mvs::kUmBKB - 1) / mvs::kUmBKB * mvs::kUmBKB;      // 128: a multiple of both paths' k-slices
-    PW_RC(op.planes.alloc(ctx, planes_slot, static_cast<size_t>(op.P) * op.n_pad * op.k_pad));
-    const int64_t threads = op.n_pad * (op.k_pad / 4);
-    mvs::pairwise_split_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, st>>>(
-        op.v, op.n, d, op.P, op.planes.as<int8_t>(), op.n_pad, op.k_pad);
-    PW_CUDA(ctx, cudaGetLastError());
-    mvs_internal_count_launches(ctx, 2);
+    op.P = std::max(limbs_for_range(mm[0], mm[1]), forced);
+    if (op.P != guess) PW_RC(split(op.P, nullptr));
     return MVS_OK;
 }
 

@@ -183,47 +183,49 @@ struct ImmaPlan {                                         // limb pairs in order
     unsigned char p[10], q[10], shift_before[10];         // shift_before: accumulators <<= 8 before this pair
 };
 
-// min / max of an int32 array (order-independent atomics on two words initialised to INT_MAX / INT_MIN)
-__global__ void __launch_bounds__(256) pairwise_minmax_kernel(const int32_t* __restrict__ v, int64_t n, int* __restrict__ mm)
-{
-    int lo = 2147483647, hi = -2147483647 - 1;
-    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int x = v[i];
-        lo = min(lo, x);
-        hi = max(hi, x);
-    }
-#pragma unroll
-    for (int m = 16; m; m >>= 1) {
-        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, m));
-        hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, m));
-    }
-    if ((threadIdx.x & 31) == 0) {
-        atomicMin(mm, lo);
-        atomicMax(mm + 1, hi);
-    }
-}
-
-// V [n x d] int32 -> P planes of int8 [n_pad x k_pad] (row-major, zero padded).  One thread = 4 consecutive k.
+// V [n x d] int32 -> P planes of int8 [n_pad x k_pad] (row-major, zero padded).  One thread = 4 consecutive k per
+// step of a grid-stride loop.  mm != nullptr: also the min / max of V (two words initialised to INT_MAX / INT_MIN),
+// so that the usual case -- the guessed P turns out right -- needs one pass over V instead of two.
 __global__ void __launch_bounds__(256)
-pairwise_split_kernel(const int32_t* __restrict__ V, int64_t n, int d, int P, int8_t* __restrict__ planes, int64_t n_pad, int k_pad)
+pairwise_split_kernel(const int32_t* __restrict__ V, int64_t n, int d, int P, int8_t* __restrict__ planes, int64_t n_pad, int k_pad,
+                      int* __restrict__ mm)
 {
     const int64_t quads = static_cast<int64_t>(k_pad) / 4;
-    const int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (t >= n_pad * quads) return;
-    const int64_t row = t / quads;
-    const int k = static_cast<int>(t - row * quads) * 4;
-    long long v[4] = {0, 0, 0, 0};
-    if (row < n)
-        for (int e = 0; e < 4; ++e)
-            if (k + e < d) v[e] = V[row * d + k + e];
-    for (int p = 0; p < P; ++p) {
-        uint32_t word = 0;
-        for (int e = 0; e < 4; ++e) {
-            const int s = static_cast<int>(static_cast<signed char>(v[e] & 0xFF));
-            word |= static_cast<uint32_t>(s & 0xFF) << (8 * e);
-            v[e] = (v[e] - s) >> 8;                                  // exact: v - s is a multiple of 256
+    int lo = 2147483647, hi = -2147483647 - 1;
+    for (int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < n_pad * quads;
+         t += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int64_t row = t / quads;
+        const int k = static_cast<int>(t - row * quads) * 4;
+        long long v[4] = {0, 0, 0, 0};
+        if (row < n)
+            for (int e = 0; e < 4; ++e)
+                if (k + e < d) {
+                    const int x = V[row * d + k + e];
+                    v[e] = x;
+                    lo = min(lo, x);
+                    hi = max(hi, x);
+                }
+        for (int p = 0; p < P; ++p) {
+            uint32_t word = 0;
+            for (int e = 0; e < 4; ++e) {
+                const int s = static_cast<int>(static_cast<signed char>(v[e] & 0xFF));
+                word |= static_cast<uint32_t>(s & 0xFF) << (8 * e);
+                v[e] = (v[e] - s) >> 8;                              // exact: v - s is a multiple of 256
+            }
+            *reinterpret_cast<uint32_t*>(planes + (static_cast<int64_t>(p) * n_pad + row) * k_pad + k) = word;
         }
-        *reinterpret_cast<uint32_t*>(planes + (static_cast<int64_t>(p) * n_pad + row) * k_pad + k) = word;
+    }
+    if (mm) {
+        __shared__ int s_lo[8], s_hi[8];
+        lo = __reduce_min_sync(0xffffffffu, lo);
+        hi = __reduce_max_sync(0xffffffffu, hi);
+        if ((threadIdx.x & 31) == 0) { s_lo[threadIdx.x >> 5] = lo; s_hi[threadIdx.x >> 5] = hi; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int w = 1; w < 8; ++w) { lo = min(lo, s_lo[w]); hi = max(hi, s_hi[w]); }
+            atomicMin(mm, lo);
+            atomicMax(mm + 1, hi);
+        }
     }
 }
 
