@@ -41,9 +41,26 @@ struct OutBuf {                                  // device triples of one row bl
     }
 };
 
-struct Triples {
-    std::vector<int32_t> rows, cols;
-    std::vector<int64_t> values;
+struct Triples {                                 // the arrays handed to the caller in mvs_sparse_result (malloc / realloc / free)
+    int32_t* rows = nullptr;
+    int32_t* cols = nullptr;
+    int64_t* values = nullptr;
+    size_t n = 0, cap = 0;
+    ~Triples() { std::free(rows); std::free(cols); std::free(values); }
+    bool reserve(size_t more)                    // room for `more` further triples; no zero fill, no second copy later
+    {
+        if (n + more <= cap) return true;
+        const size_t want = std::max(n + more, cap + cap / 2);
+        void* r = std::realloc(rows, want * sizeof(int32_t));
+        if (r) rows = static_cast<int32_t*>(r);
+        void* c = std::realloc(cols, want * sizeof(int32_t));
+        if (c) cols = static_cast<int32_t*>(c);
+        void* v = std::realloc(values, want * sizeof(int64_t));
+        if (v) values = static_cast<int64_t*>(v);
+        if (!r || !c || !v) return false;
+        cap = want;
+        return true;
+    }
 };
 
 #define PW_CUDA(ctx, call)                                                    \
@@ -370,14 +387,13 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
         PW_CUDA(ctx, emit());
     }
     if (total) {
-        const size_t at = out.rows.size();
-        out.rows.resize(at + total);
-        out.cols.resize(at + total);
-        out.values.resize(at + total);
-        PW_CUDA(ctx, cudaMemcpyAsync(out.rows.data() + at, ob.rows.p, total * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-        PW_CUDA(ctx, cudaMemcpyAsync(out.cols.data() + at, ob.cols.p, total * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-        PW_CUDA(ctx, cudaMemcpyAsync(out.values.data() + at, ob.vals.p, total * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        if (!out.reserve(total)) return MVS_ERR_OOM;
+        const size_t at = out.n;
+        PW_CUDA(ctx, cudaMemcpyAsync(out.rows + at, ob.rows.p, total * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        PW_CUDA(ctx, cudaMemcpyAsync(out.cols + at, ob.cols.p, total * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        PW_CUDA(ctx, cudaMemcpyAsync(out.values + at, ob.vals.p, total * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
         PW_CUDA(ctx, cudaStreamSynchronize(st));
+        out.n += total;
         d2h_bytes += total * 16;
     }
     float a = 0.f, b = 0.f;
@@ -429,21 +445,16 @@ int run_blocks(mvs_ctx* ctx, cudaStream_t st, Operand& A, int64_t begin, int64_t
 int finish(Triples& t, double gemm_ms, double filter_ms, double prep_ms, double wall_ms, uint64_t h2d, uint64_t d2h, mvs_sparse_result** out)
 {
     mvs_sparse_result* r = static_cast<mvs_sparse_result*>(std::calloc(1, sizeof(mvs_sparse_result)));
-    if (!r) return MVS_ERR_OOM;
-    const size_t n = t.rows.size();
-    r->n = static_cast<int64_t>(n);
-    r->rows = static_cast<int32_t*>(std::malloc(sizeof(int32_t) * (n ? n : 1)));
-    r->cols = static_cast<int32_t*>(std::malloc(sizeof(int32_t) * (n ? n : 1)));
-    r->values = static_cast<int64_t*>(std::malloc(sizeof(int64_t) * (n ? n : 1)));
-    if (!r->rows || !r->cols || !r->values) {
-        mvs_free_sparse_result(r);
+    if (!r || !t.reserve(t.n ? 0 : 1)) {         // an empty result still carries valid (1-element) arrays
+        std::free(r);
         return MVS_ERR_OOM;
     }
-    if (n) {
-        std::memcpy(r->rows, t.rows.data(), n * sizeof(int32_t));
-        std::memcpy(r->cols, t.cols.data(), n * sizeof(int32_t));
-        std::memcpy(r->values, t.values.data(), n * sizeof(int64_t));
-    }
+    r->n = static_cast<int64_t>(t.n);
+    r->rows = t.rows;                            // ownership moves to the result (mvs_free_sparse_result frees them)
+    r->cols = t.cols;
+    r->values = t.values;
+    t.rows = t.cols = nullptr;
+    t.values = nullptr;
     r->gemm_ms = gemm_ms;
     r->filter_ms = filter_ms;
     r->prep_ms = prep_ms;
