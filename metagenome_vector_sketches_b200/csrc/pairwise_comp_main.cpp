@@ -20,6 +20,9 @@
 
 #include <algorithm>
 #include <chrono>
+#include <thread>
+#include <new>
+#include <memory>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -213,47 +216,71 @@ int main(int argc, char** argv)
         return 1;
     }
     const auto t0 = std::chrono::high_resolution_clock::now();
-    std::vector<int32_t> db(static_cast<size_t>(total) * dimension);
+    auto since = [&](std::chrono::high_resolution_clock::time_point t) {
+        return std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - t).count();
+    };
+    // CUDA context creation (0.5 - 1.3 s) runs on a second thread while vectors.bin is read
+    mvs_ctx* ctx = nullptr;
+    int create_rc = MVS_OK;
+    std::thread creator([&] { create_rc = mvs_create(&ctx, a.gpu); });
+    const size_t db_count = static_cast<size_t>(total) * dimension;
+    std::unique_ptr<int32_t[]> db(new (std::nothrow) int32_t[db_count ? db_count : 1]);   // not zero-filled: read() fills it
+    if (!db) {
+        creator.join();
+        if (ctx) mvs_destroy(ctx);
+        std::cerr << "pairwise_comp_b200: out of memory for " << matrix_file << std::endl;
+        return 1;
+    }
     vf.seekg(0);
-    vf.read(reinterpret_cast<char*>(db.data()), static_cast<std::streamsize>(db.size() * sizeof(int32_t)));
+    vf.read(reinterpret_cast<char*>(db.get()), static_cast<std::streamsize>(db_count * sizeof(int32_t)));
     vf.close();
+    const double read_s = since(t0);
 
     const std::string shard_folder = out + "shard_" + std::to_string(a.shard_idx) + "/";
-    if (!fs::exists(shard_folder)) fs::create_directories(shard_folder);
     const int rows_per_shard = (total + a.num_shards - 1) / a.num_shards;
     const int begin_row = std::min(a.shard_idx * rows_per_shard, total);
     const int end_row = std::min(begin_row + rows_per_shard, total);
     std::cout << "Shard " << a.shard_idx << " processing rows " << begin_row << " to " << end_row << std::endl;
 
-    mvs_ctx* ctx = nullptr;
-    int rc = mvs_create(&ctx, a.gpu);
+    const auto t_wait = std::chrono::high_resolution_clock::now();
+    creator.join();
+    const double wait_ctx_s = since(t_wait);
+    int rc = create_rc;
     if (rc != MVS_OK) {
         std::cerr << "pairwise_comp_b200: cuda:" << a.gpu << ": " << mvs_strerror(rc) << std::endl;
         return 2;
     }
+    if (!fs::exists(shard_folder)) fs::create_directories(shard_folder);   // only once a device exists
+    const auto t_shard = std::chrono::high_resolution_clock::now();
     mvs_sparse_result* r = nullptr;
-    rc = mvs_pairwise_shard(ctx, db.data(), total, dimension, norms_sq.data(), begin_row, end_row, &r);
+    rc = mvs_pairwise_shard(ctx, db.get(), total, dimension, norms_sq.data(), begin_row, end_row, &r);
     if (rc != MVS_OK) {
         std::cerr << "pairwise_comp_b200: " << mvs_strerror(rc) << std::endl;
         mvs_destroy(ctx);
         return 2;
     }
+    const double shard_s = since(t_shard);
+    db.reset();
+    const auto t_write = std::chrono::high_resolution_clock::now();
     // (row, col)-sorted GPU output -> the order in which the reference appends to all_results (:949-983):
     // row chunks outermost, then column chunks, then rows, then columns (a stable sort on the two chunk ids)
     std::vector<Pair> ordered(static_cast<size_t>(r->n));
     for (int64_t k = 0; k < r->n; ++k) ordered[static_cast<size_t>(k)] = {r->rows[k], r->cols[k], r->values[k]};
     const double gemm_ms = r->gemm_ms, filter_ms = r->filter_ms, prep_ms = r->prep_ms;
     mvs_free_sparse_result(r);
-    mvs_destroy(ctx);
+    std::thread destroyer([&] { mvs_destroy(ctx); });                  // context teardown overlaps the writer
     std::stable_sort(ordered.begin(), ordered.end(), [&](const Pair& x, const Pair& y) {
         const int xi = (x.row - begin_row) / chunk, yi = (y.row - begin_row) / chunk;
         if (xi != yi) return xi < yi;
         return x.col / chunk < y.col / chunk;
     });
     write_shard(shard_folder, ordered, norms_sq, dimension);
+    const double write_s = since(t_write);
+    destroyer.join();
     const auto ms = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::high_resolution_clock::now() - t0).count();
     std::cout << "Total computation time: " << ms << " ms" << std::endl;
     if (std::getenv("MVS_TIMING"))
-        std::fprintf(stderr, "mvs_timing pairs_kept=%zu gemm_ms=%.3f filter_ms=%.3f prep_ms=%.3f\n", ordered.size(), gemm_ms, filter_ms, prep_ms);
+        std::fprintf(stderr, "mvs_timing pairs_kept=%zu gemm_ms=%.3f filter_ms=%.3f prep_ms=%.3f read_s=%.3f wait_ctx_s=%.3f shard_s=%.3f write_s=%.3f\n",
+                     ordered.size(), gemm_ms, filter_ms, prep_ms, read_s, wait_ctx_s, shard_s, write_s);
     return 0;
 }
