@@ -7,14 +7,15 @@
 // and the kept triples are returned in row-major (i, then j) order, like the reference's double loop.
 //
 // How:
-//   1a. pairwise_dot_imma_kernel (default): the int32 operands are split into balanced base-256 limbs and the
-//       limb products run on the tensor cores (int8 IMMA, int32 accumulate), combined modulo 2^32 by Horner's
-//       rule in one accumulator set -- exact for any int32 input; see the section header below.
+//   1a. the int32 operands are split into balanced base-256 limbs (pairwise_split_kernel) and the limb products run
+//       on the tensor cores, combined modulo 2^32 by Horner's rule -- exact for any int32 input.  Default: the
+//       tcgen05 kernels of mvs_pairwise_umma.cuh; here: pairwise_dot_imma_kernel, the same GEMM with warp-level
+//       mma.sync (option "pairwise_path" = 2), see the section header below.
 //   1b. pairwise_dot_kernel (cross-check path, option "pairwise_path" = 1): register-tiled int32 GEMM on the
 //       FMA-heavy pipe (IMAD is exact modulo 2^32 by construction).  128 x 128 x 16 CTA tiles, 256 threads,
 //       8 x 8 outputs per thread, operands staged k-major in shared memory (double buffered).
-//   2.  pairwise_count_kernel / pairwise_scan_kernel / pairwise_emit_kernel: threshold + ordered compaction of the
-//       dense C block into (row, col, dot) triples in the reference's loop order, no atomics.
+//   2.  pairwise_count_kernel / pairwise_rowsum_kernel / pairwise_scan_kernel / pairwise_emit_kernel: threshold +
+//       ordered compaction of the C block into (row, col, dot) triples in the reference's loop order, no atomics.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>

@@ -4,15 +4,16 @@
 //
 //   C[i][j] = sum over limb pairs (p, q), p + q <= 3, of 256^(p+q) * sum_k A_p[i][k] * B_q[j][k]      (mod 2^32)
 //
-// Persistent CTAs (one per SM) loop over 128 x 128 tiles of C; 192 threads: warp 0 (one lane) = TMA producer,
-// warp 1 (one lane) = MMA issuer, warps 2..5 = epilogue.  Every weight s = p + q owns its own 128-column int32 accumulator in TMEM (<= 4 weights =
-// the SM's 512 columns), so limb pairs may run in any order and the Horner combine v = (v << 8) + acc_s happens
-// once, in the epilogue, on the way from TMEM to registers.  Because of that freedom a pipeline stage holds ALL limb
-// planes of one 128-byte k-slice (FUSED, when they fit: PA + PB <= 4, i.e. the normal 2-limb case) and every staged
-// byte feeds up to four MMAs; with more limbs the planes are streamed pair by pair (STREAM).  The kernel is bound
-// by L2 -> shared-memory operand traffic, which FUSED halves.
-// The epilogue only combines and stores, and it frees TMEM as soon as its row is in registers: the keep-test stays
-// in the massively parallel pairwise_count_kernel (fusing it here cost 1 ms per 10^8 pairs, the separate pass 0.15 ms).
+// Persistent CTAs (one per SM) loop over 128 x 128 tiles of C (CTA pairs with tcgen05 cta_group::2: over 256 x 128
+// tiles, see pairwise_dot_umma_pair_kernel); 192 threads: warp 0 = TMA producer, warp 1 = MMA issuer (all lanes run
+// the loops with uniform state, one elected lane issues), warps 2..5 = epilogue.  Every weight s = p + q owns its own
+// 128-column int32 accumulator in TMEM (<= 4 weights = the SM's 512 columns), so limb pairs may run in any order and
+// the Horner combine v = (v << 8) + acc_s happens once, in the epilogue, on the way from TMEM to registers.  Because
+// of that freedom a pipeline stage holds ALL limb planes of one 128-byte k-slice (FUSED, when they fit: PA + PB <= 4,
+// i.e. the normal 2-limb case) and every staged byte feeds up to four MMAs; with more limbs the planes are streamed
+// pair by pair (STREAM, twice the operand bytes per MMA: that is L2-ingress bound, FUSED is tensor-pipe bound).
+// The epilogue frees TMEM as soon as its row is in registers, then applies a lower-bound pre-filter of the keep-test
+// (um_store_row) and stores only rows that may keep a pair; the exact test runs later on those segments only.
 #pragma once
 #include <cstdint>
 #include <cuda.h>
