@@ -85,6 +85,46 @@ __device__ __forceinline__ void um_tmem_ld32(uint32_t taddr, uint32_t (&r)[32])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ void um_tmem_ld32_nowait(uint32_t taddr, uint32_t (&r)[32])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]),
+                   "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+                   "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                 : "r"(taddr));
+}
+__device__ __forceinline__ void um_tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// TMEM -> registers for one thread's row of a tile: v[c] = sum_s 256^s * acc_s[c] (mod 2^32).  With three weights (the
+// two-limb case) the three loads of a 32-column chunk are in flight together and share one wait.
+__device__ __forceinline__ void um_drain_row(uint32_t tmem_row, int smax, bool skip, uint32_t (&v)[kUmBN])
+{
+    if (smax == 2 && !skip) {
+#pragma unroll
+        for (int c0 = 0; c0 < kUmBN; c0 += 32) {
+            uint32_t r0[32], r1[32], r2[32];
+            um_tmem_ld32_nowait(tmem_row + static_cast<uint32_t>(0 * kUmBN + c0), r0);
+            um_tmem_ld32_nowait(tmem_row + static_cast<uint32_t>(1 * kUmBN + c0), r1);
+            um_tmem_ld32_nowait(tmem_row + static_cast<uint32_t>(2 * kUmBN + c0), r2);
+            um_tmem_ld_wait();
+#pragma unroll
+            for (int e = 0; e < 32; ++e) v[c0 + e] = (((r2[e] << 8) + r1[e]) << 8) + r0[e];
+        }
+        return;
+    }
+#pragma unroll
+    for (int c0 = 0; c0 < kUmBN; c0 += 32) {
+#pragma unroll
+        for (int e = 0; e < 32; ++e) v[c0 + e] = 0;
+        for (int s = skip ? -1 : smax; s >= 0; --s) {
+            uint32_t r[32];
+            um_tmem_ld32(tmem_row + static_cast<uint32_t>(s * kUmBN + c0), r);
+#pragma unroll
+            for (int e = 0; e < 32; ++e) v[c0 + e] = (v[c0 + e] << 8) + r[e];
+        }
+    }
+}
+
 __device__ __forceinline__ void um_mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
 __device__ __forceinline__ void um_tma_load_3d_mc(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1, int c2, uint16_t mask)
 {
@@ -385,17 +425,7 @@ pairwise_dot_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             UM_PROBE_T(te1);
             uint32_t v[kUmBN];                                         // this thread's row of the tile: 128 registers
-#pragma unroll
-            for (int c0 = 0; c0 < kUmBN; c0 += 32) {
-#pragma unroll
-                for (int e = 0; e < 32; ++e) v[c0 + e] = 0;
-                for (int s = (plan.probe & 2) ? -1 : plan.smax; s >= 0; --s) {
-                    uint32_t r[32];
-                    um_tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(s * kUmBN + c0), r);
-#pragma unroll
-                    for (int e = 0; e < 32; ++e) v[c0 + e] = (v[c0 + e] << 8) + r[e];
-                }
-            }
+            um_drain_row(tmem_base + (static_cast<uint32_t>(q * 32) << 16), plan.smax, (plan.probe & 2) != 0, v);
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) um_mbar_arrive(bar_tmem_empty);             // TMEM may be overwritten; the stores below overlap the next tile
@@ -615,17 +645,7 @@ pairwise_dot_umma_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __g
             um_mbar_wait(bar_tmem_full, tile_phase);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             uint32_t v[kUmBN];
-#pragma unroll
-            for (int c0 = 0; c0 < kUmBN; c0 += 32) {
-#pragma unroll
-                for (int e = 0; e < 32; ++e) v[c0 + e] = 0;
-                for (int s = (plan.probe & 2) ? -1 : plan.smax; s >= 0; --s) {
-                    uint32_t r[32];
-                    um_tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(s * kUmBN + c0), r);
-#pragma unroll
-                    for (int e = 0; e < 32; ++e) v[c0 + e] = (v[c0 + e] << 8) + r[e];
-                }
-            }
+            um_drain_row(tmem_base + (static_cast<uint32_t>(q * 32) << 16), plan.smax, (plan.probe & 2) != 0, v);
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) um_mbar_arrive_remote(leader_tmem_empty);
