@@ -438,7 +438,7 @@ int mvs_internal_upload(mvs_ctx* ctx, cudaStream_t st, void* dst, const void* sr
         char* slot = stage + k * kChunk;
         if (ctx->stage_busy[k]) MVS_CUDA(ctx, cudaEventSynchronize(ctx->stage_ev[k]));
         const char* from = static_cast<const char*>(src) + off;
-        constexpr int kParts = 8;
+        constexpr int kParts = 4;
 #pragma omp parallel for num_threads(kParts) schedule(static)
         for (int p = 0; p < kParts; ++p) {
             const size_t a = n * p / kParts, b = n * (p + 1) / kParts;
