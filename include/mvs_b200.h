@@ -221,6 +221,8 @@ int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second);
  *                  4 (2 x 2) CTAs with TMA multicast;  "pairwise_stream": 1 = stream limb pairs instead of fused stages;
  * "pairwise_fuse": tcgen05 path, 0 = threshold pre-filter in the GEMM epilogue (default), 2 = separate count pass
  * (all paths are exact; these knobs exist for the parity tests and the A/B measurements in profiles/);
+ * "stage_uploads": 0 = uploads from pageable caller memory go through a pinned ring filled by host threads (default),
+ *                  2 = plain cudaMemcpyAsync (the driver's own staging), for A/B measurements;
  * "release_workspace": frees the device and pinned buffers the pairwise entry points keep between calls (they are
  * grow-only and otherwise live until mvs_destroy). */
 int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value);

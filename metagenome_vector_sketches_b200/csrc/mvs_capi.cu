@@ -90,6 +90,7 @@ struct mvs_ctx {
     cudaEvent_t stage_ev[2] = {nullptr, nullptr};    // "the DMA out of ring slot k has finished"
     bool stage_busy[2] = {false, false};
     unsigned stage_turn = 0;
+    int stage_uploads = 0;                       // 0 = pageable sources go through the pinned ring (default), 2 = plain cudaMemcpyAsync
 };
 
 namespace {
@@ -415,7 +416,7 @@ int mvs_internal_upload(mvs_ctx* ctx, cudaStream_t st, void* dst, const void* sr
 {
     constexpr size_t kChunk = 8u << 20;
     bool pageable = false;
-    if (bytes >= (2u << 20)) {
+    if (bytes >= (2u << 20) && ctx->stage_uploads != 2) {
         cudaPointerAttributes at{};
         if (cudaPointerGetAttributes(&at, src) == cudaSuccess) pageable = at.type == cudaMemoryTypeUnregistered;
         else cudaGetLastError();
@@ -808,6 +809,7 @@ int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value)
     else if (!std::strcmp(key, "task_cap") && value >= 0) ctx->task_cap = static_cast<uint64_t>(value);
     else if (!std::strcmp(key, "pairwise_path") && value >= 0 && value <= 2) ctx->pairwise_path = static_cast<int>(value);
     else if (!std::strcmp(key, "release_workspace")) { cudaSetDevice(ctx->device); cudaDeviceSynchronize(); release_workspace(ctx); }
+    else if (!std::strcmp(key, "stage_uploads") && (value == 0 || value == 2)) ctx->stage_uploads = static_cast<int>(value);
     else if (!std::strcmp(key, "pairwise_fuse") && (value == 0 || value == 2)) ctx->pairwise_fuse = static_cast<int>(value);
     else if (!std::strcmp(key, "pairwise_pair") && value >= 0 && value <= 2) ctx->pairwise_pair = static_cast<int>(value);
     else if (!std::strcmp(key, "pairwise_cluster") && (value == 0 || value == 1 || value == 2 || value == 4)) ctx->pairwise_cluster = static_cast<int>(value);

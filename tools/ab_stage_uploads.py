@@ -1,0 +1,17 @@
+"""A/B of the pinned staging ring for pageable caller buffers (option stage_uploads): run on the GPU box."""
+import time, numpy as np, sys
+sys.path.insert(0, '/root/repo')
+import metagenome_vector_sketches_b200 as mvs
+n, per, d = 2000, 50000, 2048
+rng = np.random.default_rng(1)
+h = rng.integers(0, 2**54, n*per, dtype=np.uint64)
+off = np.arange(n+1, dtype=np.uint64)*per
+out = np.empty((n, d), dtype=np.int32)
+sk = mvs.Sketcher(0)
+for mode in (0, 2, 0, 2):
+    sk.set_option("stage_uploads", mode)
+    sk.project_csr(h, off, d, out=out)
+    t = time.perf_counter()
+    for _ in range(3): sk.project_csr(h, off, d, out=out)
+    dt = (time.perf_counter()-t)/3
+    print("stage_uploads=%d: %.1f ms per 0.8 GB batch = %.1f GB/s, %.2f G hashes/s" % (mode, dt*1e3, n*per*8/dt/1e9, n*per/dt/1e9))
