@@ -189,3 +189,23 @@ def test_full_size_shard_properties():
     assert np.array_equal(keep, np.isin(ri * n + ci, key))                           # dropped pairs really fail it
     want = oracle_pairwise(v[4990:5290], v, d, nrm[4990:5290], nrm)
     assert same(part, (want[0] + 4990, want[1], want[2]))
+
+
+def test_seeded_fuzz_of_shards(sk):
+    """25 random dbs: any n, d, value scale (1 .. 4 limbs, wrapped products), shard range and a few impossible norms
+    (zero, negative, NaN), through mvs_pairwise_shard against the oracle on the same rows."""
+    rng = np.random.default_rng(20261104)
+    for case in range(25):
+        n, d = int(rng.integers(1, 700)), int(rng.integers(1, 600))
+        scale = float(rng.choice([3.0, 60.0, 900.0, 2.0e4, 3.0e6, 7.0e8]))
+        v = np.clip(np.rint(rng.normal(0.0, scale, (n, d))), -2 ** 31, 2 ** 31 - 1).astype(np.int32)
+        if n > 4:
+            v[rng.integers(0, n, n // 3)] = v[int(rng.integers(0, n))]                 # duplicates: pairs that are kept
+        nrm = norms_sq_like_reference(v, d) * float(rng.choice([1.0, 1.0, 0.3, 3.0]))
+        for k in rng.integers(0, n, 3):
+            nrm[k] = float(rng.choice([0.0, -1.0, -1e9, np.nan, 1e300]))
+        b = int(rng.integers(0, n))
+        e = int(rng.integers(b, n + 1))
+        got = pw.pairwise_shard(sk, v, nrm, b, e)
+        want = oracle_pairwise(v[b:e], v, d, nrm[b:e], nrm)
+        assert same(got, (want[0] + b, want[1], want[2])), (case, n, d, scale, b, e)
