@@ -129,6 +129,24 @@ def test_reference_driver_linked_against_our_shim(tmp_path, toy_hash_file):
     assert (db / "vector_norms.txt").read_text() == ref["norms_txt"] or ref_dir() != REFV3
 
 
+@pytest.mark.parametrize("threads,serial", [(1, False), (8, False), (24, False), (8, True)])
+def test_shim_called_concurrently_from_openmp_threads(threads, serial):
+    """The a4 sample loop (project_everything.cpp:287-298) over in-memory sets: our replacement of
+    transform_set_into_vector, one context per calling thread, against the reference's function."""
+    ours, theirs = os.path.join(REFV3, "a4_loop_b200shim"), os.path.join(REFV3, "a4_loop_ref")
+    if not (os.path.exists(ours) and os.path.exists(theirs)):
+        pytest.skip("a4 loop harness not prebuilt")
+    for n, h, d in ((70, 3000, 2048), (33, 1, 100), (9, 40000, 4096)):
+        env = dict(os.environ, OMP_NUM_THREADS=str(threads))
+        if serial:
+            env["MVS_SHIM_SERIAL"] = "1"
+        a = run([ours, str(n), str(h), str(d), "2"], env=env)
+        b = run([theirs, str(n), str(h), str(d), "1"], env=dict(os.environ, OMP_NUM_THREADS="8"))
+        assert a.returncode == 0 and b.returncode == 0, a.stderr + b.stderr
+        ja, jb = json.loads(a.stdout.strip().splitlines()[-1]), json.loads(b.stdout.strip().splitlines()[-1])
+        assert ja["checksum"] == jb["checksum"] and ja["hashes"] == jb["hashes"] == n * h
+
+
 PWB = os.path.join(BIN, "pairwise_comp_b200")
 SHARD_FILES = ("matrix.bin", "row_index.bin", "neighbor_start.bin")
 
