@@ -182,6 +182,12 @@ def run_gpu(args):
                          "(use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # host locality: this rank's pinned buffers should live on the NUMA node its GPU hangs off (matters at N > 1,
+    # where the ranks' uploads otherwise meet on one socket's memory controllers / the socket interconnect)
+    binding = {"numa_node": None, "applied": 0}
+    if not args.no_bind:
+        node, applied = mvs.bind_host_to_device(local)
+        binding = {"numa_node": node, "applied": applied}
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -248,7 +254,15 @@ def run_gpu(args):
     t1 = time.perf_counter()
     barrier()
     clk = clocks.stop()
+    my_e2e_ms = (t1 - t0) * 1e3 / args.steps
     e2e_ms = max_over_ranks((t1 - t0) * 1e3) / args.steps
+    per_rank = [[my_e2e_ms, binding["numa_node"], binding["applied"]]]
+    if world > 1:
+        t = torch.tensor([my_e2e_ms, -1.0 if binding["numa_node"] is None else float(binding["numa_node"]),
+                          float(binding["applied"])], dtype=torch.float64, device=dev)
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        per_rank = [[float(x[0]), int(x[1]), int(x[2])] for x in allt]
     tb = sk.timing()
     e2e_value = world * total / (e2e_ms * 1e-3)
     checksum_host = int(out_np.sum(dtype=np.int64))
@@ -315,6 +329,7 @@ def main():
     ap.add_argument("--hashes-per-sample", type=int, default=50000)
     ap.add_argument("--d", type=int, default=2048)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-bind", action="store_true", help="skip mvs_bind_host_to_device (A/B of the host locality)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
@@ -389,6 +404,9 @@ def main():
             "e2e": {"value": g["e2e_value"], "unit": UNIT, "ms_per_step": g["e2e_ms"],
                     "h2d_bytes_per_step": int(tb["h2d_bytes"]), "d2h_bytes_per_step": int(tb["d2h_bytes"]),
                     "api": "mvs_project_batch (pinned host CSR in, pinned host int32 rows out)",
+                    "host_binding": {"how": "mvs_bind_host_to_device per rank before the pinned buffers are allocated "
+                                            "(applied: 1 = CPU affinity, 2 = preferred memory node)",
+                                     "per_rank_ms_node_applied": g["per_rank"]},
                     "pageable_host_buffers": None if g["pageable_ms"] is None else {
                         "value": g["total"] / (g["pageable_ms"] * 1e-3), "unit": UNIT, "ms_per_step": g["pageable_ms"],
                         "how": "same call, numpy (pageable) arrays in and out: the library stages them through a pinned "

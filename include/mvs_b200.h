@@ -157,6 +157,16 @@ void mvs_host_free(void* p);
 int mvs_host_register(void* p, size_t bytes);       /* pin caller-owned memory */
 int mvs_host_unregister(void* p);
 
+/* Host locality (no counterpart in the reference, which has no device): binds the CALLING host thread to the
+ * NUMA node the device hangs off -- CPU affinity = the device's local CPUs that the thread may already run on
+ * (/sys/bus/pci/devices/<bus id>/local_cpulist; skipped when fewer than 4 remain), memory policy = prefer that node (/sys/.../numa_node) -- so that
+ * pinned buffers the thread allocates afterwards (mvs_host_alloc, the library's own staging) are read by the
+ * device's DMA engine without crossing the socket interconnect.  On a multi-GPU box every rank / per-GPU thread
+ * calls it once before it allocates.  *numa_node (may be NULL) receives the node or -1 when the platform reports
+ * none; *applied (may be NULL) receives a bit mask: 1 = CPU affinity set, 2 = memory policy set.  A platform
+ * without the sysfs entries, or a container that forbids the node, is not an error (MVS_OK, *applied = 0). */
+int mvs_bind_host_to_device(int device, int* numa_node, int* applied);
+
 /* ---- all-pairs comparison of projected vectors --------------------
  * Replaces compute_sparse_dot_products_optimized (reference src/pairwise_comp_optimized.cpp:57-160)
  * and the block loops of its main (:949-983).  dot(i, j) = sum_k a[i][k] * b[j][k] in int32

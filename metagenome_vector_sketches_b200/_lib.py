@@ -71,6 +71,7 @@ SIGNATURES = {
     "mvs_host_free": (None, [C.c_void_p]),
     "mvs_host_register": (C.c_int, [C.c_void_p, C.c_size_t]),
     "mvs_host_unregister": (C.c_int, [C.c_void_p]),
+    "mvs_bind_host_to_device": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "mvs_get_timing": (C.c_int, [C.c_void_p, C.POINTER(Timing)]),
     "mvs_int_issue_peak": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),
     "mvs_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),

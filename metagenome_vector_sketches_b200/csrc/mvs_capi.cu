@@ -19,6 +19,10 @@
 #include <new>
 #include <vector>
 
+#include <sched.h>
+#include <sys/syscall.h>
+#include <unistd.h>
+
 namespace {
 
 using mvs::ReduceItem;
@@ -713,6 +717,81 @@ void mvs_host_free(void* p)
 {
     if (p) cudaFreeHost(p);
 }
+// ---- host locality ---------------------------------------------------------------------------------------
+namespace {
+
+bool read_small_file(const char* path, char* buf, size_t cap)
+{
+    FILE* f = std::fopen(path, "r");
+    if (!f) return false;
+    const size_t n = std::fread(buf, 1, cap - 1, f);
+    std::fclose(f);
+    buf[n] = 0;
+    return n > 0;
+}
+
+// "0-15,64-79" -> cpu_set_t
+bool parse_cpulist(const char* s, cpu_set_t* set)
+{
+    CPU_ZERO(set);
+    bool any = false;
+    while (*s) {
+        char* end = nullptr;
+        const long a = std::strtol(s, &end, 10);
+        if (end == s) break;
+        long b = a;
+        s = end;
+        if (*s == '-') {
+            b = std::strtol(s + 1, &end, 10);
+            s = end;
+        }
+        for (long c = a; c <= b && c < CPU_SETSIZE; ++c) {
+            if (c >= 0) {
+                CPU_SET(static_cast<int>(c), set);
+                any = true;
+            }
+        }
+        while (*s == ',' || *s == ' ' || *s == '\n') ++s;
+    }
+    return any;
+}
+
+}  // namespace
+
+int mvs_bind_host_to_device(int device, int* numa_node, int* applied)
+{
+    if (numa_node) *numa_node = -1;
+    if (applied) *applied = 0;
+    char bus[32] = {0};
+    if (cudaDeviceGetPCIBusId(bus, sizeof bus, device) != cudaSuccess) {
+        cudaGetLastError();
+        return MVS_ERR_NO_DEVICE;
+    }
+    for (char* c = bus; *c; ++c)
+        if (*c >= 'A' && *c <= 'F') *c = static_cast<char>(*c - 'A' + 'a');       // sysfs spells the bus id in lower case
+    char path[128], buf[4096];
+    int node = -1, did = 0;
+    std::snprintf(path, sizeof path, "/sys/bus/pci/devices/%s/numa_node", bus);
+    if (read_small_file(path, buf, sizeof buf)) node = std::atoi(buf);
+    std::snprintf(path, sizeof path, "/sys/bus/pci/devices/%s/local_cpulist", bus);
+    cpu_set_t local, allowed, both;
+    if (read_small_file(path, buf, sizeof buf) && parse_cpulist(buf, &local) &&
+        sched_getaffinity(0, sizeof allowed, &allowed) == 0) {
+        CPU_AND(&both, &local, &allowed);
+        // fewer than 4 local CPUs would starve the library's own copy threads: leave the affinity alone then
+        if (CPU_COUNT(&both) >= 4 && sched_setaffinity(0, sizeof both, &both) == 0) did |= 1;
+    }
+    if (node >= 0 && node < 1024) {
+        unsigned long mask[16] = {0};                                             // 1024 nodes
+        mask[node / (8 * sizeof(unsigned long))] |= 1ul << (node % (8 * sizeof(unsigned long)));
+        constexpr int kMpolPreferred = 1;                                         // <linux/mempolicy.h>; no libnuma here
+        if (syscall(SYS_set_mempolicy, kMpolPreferred, mask, 1025ul) == 0) did |= 2;
+    }
+    if (numa_node) *numa_node = node;
+    if (applied) *applied = did;
+    return MVS_OK;
+}
+
 int mvs_host_register(void* p, size_t bytes)
 {
     if (!p) return MVS_ERR_INVALID_ARG;

@@ -137,6 +137,14 @@ def transform_set_into_vector(hashes, d, seed=0, device=0):
     return sk.transform_set(hashes, d, seed)
 
 
+def bind_host_to_device(device):
+    """mvs_bind_host_to_device: pin the calling host thread (CPU affinity + preferred memory node) to the NUMA
+    node of `device`; call it once per rank before allocating pinned buffers.  Returns (numa_node, applied)."""
+    node, applied = C.c_int(-1), C.c_int(0)
+    check(load_library().mvs_bind_host_to_device(int(device), C.byref(node), C.byref(applied)), "mvs_bind_host_to_device")
+    return node.value, applied.value
+
+
 def norm_from_sumsq(sumsq, d):
     """norm written to vector_norms.txt: ||v / sqrt(d)|| (reference project_everything.cpp:327-329)."""
     return math.sqrt(float(int(sumsq)) / float(d))
