@@ -239,7 +239,12 @@ def run_gpu(args):
     checksum_dev = int(dout.sum(dtype=torch.int64).item())
 
     # ---- e2e: pinned host buffers through mvs_project_batch -------------------------------
-    hh = torch.empty(total, dtype=torch.int64, pin_memory=True)
+    if args.wc_input:                             # experiment: write-combined input buffer (no CPU cache snoops)
+        from metagenome_vector_sketches_b200.projection import pinned_empty
+        wc = pinned_empty(total, np.int64, write_combined=True)
+        hh = torch.from_numpy(wc.a)
+    else:
+        hh = torch.empty(total, dtype=torch.int64, pin_memory=True)
     hh.copy_(dh)
     hout = torch.empty((n, d), dtype=torch.int32, pin_memory=True)
     h_np = hh.numpy().view(np.uint64)
@@ -272,7 +277,7 @@ def run_gpu(args):
     # ---- the same call with PAGEABLE host buffers (what a caller with a std::vector has); extra information ----
     pageable_ms = None                           # single-GPU runs only: N ranks would hold N more 4 GB host copies
     if world == 1:
-        pg_in = np.array(h_np, copy=True)
+        pg_in = dh.cpu().numpy().view(np.uint64) if args.wc_input else np.array(h_np, copy=True)
         pg_out = np.empty((n, d), dtype=np.int32)
         sk.project_csr(pg_in, off, d, out=pg_out)
         torch.cuda.synchronize()
@@ -329,6 +334,7 @@ def main():
     ap.add_argument("--hashes-per-sample", type=int, default=50000)
     ap.add_argument("--d", type=int, default=2048)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--wc-input", action="store_true", help="experiment: write-combined pinned input buffer")
     ap.add_argument("--no-bind", action="store_true", help="skip mvs_bind_host_to_device (A/B of the host locality)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
@@ -403,7 +409,8 @@ def main():
             "samples_per_s": g["value"] / per,
             "e2e": {"value": g["e2e_value"], "unit": UNIT, "ms_per_step": g["e2e_ms"],
                     "h2d_bytes_per_step": int(tb["h2d_bytes"]), "d2h_bytes_per_step": int(tb["d2h_bytes"]),
-                    "api": "mvs_project_batch (pinned host CSR in, pinned host int32 rows out)",
+                    "api": "mvs_project_batch (%s host CSR in, pinned host int32 rows out)"
+                           % ("write-combined pinned" if args.wc_input else "pinned"),
                     "host_binding": {"how": "mvs_bind_host_to_device per rank before the pinned buffers are allocated "
                                             "(applied: 1 = CPU affinity, 2 = preferred memory node)",
                                      "per_rank_ms_node_applied": g["per_rank"]},

@@ -153,6 +153,10 @@ int mvs_convert_signatures(const char* signature_folder, const char* hash_file, 
 int64_t mvs_sort_unique(uint64_t* hashes, int64_t n);
 
 void* mvs_host_alloc(size_t bytes);                 /* pinned host memory, NULL on failure */
+/* The same, write-combined (cudaHostAllocWriteCombined): not snooped by the CPU caches, so the device's DMA reads need
+ * no cache probes on the host side.  For INPUT buffers the host only ever writes (sequentially); host reads of
+ * write-combined memory are very slow.  Freed with mvs_host_free. */
+void* mvs_host_alloc_write_combined(size_t bytes);
 void mvs_host_free(void* p);
 int mvs_host_register(void* p, size_t bytes);       /* pin caller-owned memory */
 int mvs_host_unregister(void* p);

@@ -68,6 +68,7 @@ SIGNATURES = {
     "mvs_convert_signatures": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int, C.c_int]),
     "mvs_sort_unique": (C.c_int64, [C.c_void_p, C.c_int64]),
     "mvs_host_alloc": (C.c_void_p, [C.c_size_t]),
+    "mvs_host_alloc_write_combined": (C.c_void_p, [C.c_size_t]),
     "mvs_host_free": (None, [C.c_void_p]),
     "mvs_host_register": (C.c_int, [C.c_void_p, C.c_size_t]),
     "mvs_host_unregister": (C.c_int, [C.c_void_p]),

@@ -713,6 +713,15 @@ void* mvs_host_alloc(size_t bytes)
     }
     return p;
 }
+void* mvs_host_alloc_write_combined(size_t bytes)
+{
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocWriteCombined) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
 void mvs_host_free(void* p)
 {
     if (p) cudaFreeHost(p);

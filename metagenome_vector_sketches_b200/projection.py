@@ -155,12 +155,13 @@ def format_norm(x):
     return "%g" % x
 
 
-def pinned_empty(n, dtype):
-    """numpy array over pinned host memory from mvs_host_alloc (kept alive by the array's base)."""
+def pinned_empty(n, dtype, write_combined=False):
+    """numpy array over pinned host memory from mvs_host_alloc (kept alive by the array's base);
+    write_combined: mvs_host_alloc_write_combined (input buffers the host only writes)."""
     lib = load_library()
     dt = np.dtype(dtype)
     nbytes = max(1, int(n) * dt.itemsize)
-    p = lib.mvs_host_alloc(nbytes)
+    p = (lib.mvs_host_alloc_write_combined if write_combined else lib.mvs_host_alloc)(nbytes)
     if not p:
         raise MemoryError("mvs_host_alloc(%d)" % nbytes)
     buf = (C.c_char * nbytes).from_address(p)
