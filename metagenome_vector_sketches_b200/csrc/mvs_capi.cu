@@ -94,6 +94,8 @@ struct mvs_ctx {
     cudaEvent_t stage_ev[2] = {nullptr, nullptr};    // "the DMA out of ring slot k has finished"
     bool stage_busy[2] = {false, false};
     unsigned stage_turn = 0;
+    int stage_copy = 0;                          // 0 = memcpy into the ring, 1 = streaming stores (mvs_internal_copy_streaming)
+    int stage_threads = 4;                       // host threads filling one ring slot
     int stage_uploads = 0;                       // 0 = pageable sources go through the pinned ring (default), 2 = plain cudaMemcpyAsync
 };
 
@@ -443,11 +445,13 @@ int mvs_internal_upload(mvs_ctx* ctx, cudaStream_t st, void* dst, const void* sr
         char* slot = stage + k * kChunk;
         if (ctx->stage_busy[k]) MVS_CUDA(ctx, cudaEventSynchronize(ctx->stage_ev[k]));
         const char* from = static_cast<const char*>(src) + off;
-        constexpr int kParts = 4;
+        const int kParts = ctx->stage_threads;
+        const bool streaming = ctx->stage_copy == 1;
 #pragma omp parallel for num_threads(kParts) schedule(static)
         for (int p = 0; p < kParts; ++p) {
-            const size_t a = n * p / kParts, b = n * (p + 1) / kParts;
-            std::memcpy(slot + a, from + a, b - a);
+            const size_t a = (n * p / kParts) & ~size_t(63), b = p + 1 == kParts ? n : (n * (p + 1) / kParts) & ~size_t(63);
+            if (streaming) mvs_internal_copy_streaming(slot + a, from + a, b - a);
+            else std::memcpy(slot + a, from + a, b - a);
         }
         MVS_CUDA(ctx, cudaMemcpyAsync(static_cast<char*>(dst) + off, slot, n, cudaMemcpyHostToDevice, st));
         MVS_CUDA(ctx, cudaEventRecord(ctx->stage_ev[k], st));
@@ -897,6 +901,8 @@ int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value)
     else if (!std::strcmp(key, "task_cap") && value >= 0) ctx->task_cap = static_cast<uint64_t>(value);
     else if (!std::strcmp(key, "pairwise_path") && value >= 0 && value <= 2) ctx->pairwise_path = static_cast<int>(value);
     else if (!std::strcmp(key, "release_workspace")) { cudaSetDevice(ctx->device); cudaDeviceSynchronize(); release_workspace(ctx); }
+    else if (!std::strcmp(key, "stage_copy") && (value == 0 || value == 1)) ctx->stage_copy = static_cast<int>(value);
+    else if (!std::strcmp(key, "stage_threads") && value >= 1 && value <= 64) ctx->stage_threads = static_cast<int>(value);
     else if (!std::strcmp(key, "stage_uploads") && (value == 0 || value == 2)) ctx->stage_uploads = static_cast<int>(value);
     else if (!std::strcmp(key, "pairwise_fuse") && (value == 0 || value == 2)) ctx->pairwise_fuse = static_cast<int>(value);
     else if (!std::strcmp(key, "pairwise_pair") && value >= 0 && value <= 2) ctx->pairwise_pair = static_cast<int>(value);

@@ -624,3 +624,33 @@ int mvs_standalone_file(mvs_ctx* ctx, const char* hashes_file, int d, uint64_t s
 }
 
 }  // extern "C"
+
+// ---- streaming copy for the pinned staging ring (mvs_internal.h) -------------------------------------------
+#include <immintrin.h>
+
+__attribute__((target("avx2"))) static void copy_streaming_avx2(char* dst, const char* src, size_t n)
+{
+    size_t head = (32 - (reinterpret_cast<uintptr_t>(dst) & 31)) & 31;
+    if (head > n) head = n;
+    std::memcpy(dst, src, head);
+    size_t i = head;
+    for (; i + 128 <= n; i += 128) {
+        const __m256i a = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(src + i));
+        const __m256i b = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(src + i + 32));
+        const __m256i c = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(src + i + 64));
+        const __m256i d = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(src + i + 96));
+        _mm256_stream_si256(reinterpret_cast<__m256i*>(dst + i), a);
+        _mm256_stream_si256(reinterpret_cast<__m256i*>(dst + i + 32), b);
+        _mm256_stream_si256(reinterpret_cast<__m256i*>(dst + i + 64), c);
+        _mm256_stream_si256(reinterpret_cast<__m256i*>(dst + i + 96), d);
+    }
+    std::memcpy(dst + i, src + i, n - i);
+    _mm_sfence();
+}
+
+void mvs_internal_copy_streaming(void* dst, const void* src, size_t bytes)
+{
+    static const bool avx2 = __builtin_cpu_supports("avx2");
+    if (avx2) copy_streaming_avx2(static_cast<char*>(dst), static_cast<const char*>(src), bytes);
+    else std::memcpy(dst, src, bytes);
+}

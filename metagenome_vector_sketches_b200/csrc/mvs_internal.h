@@ -22,3 +22,6 @@ void* mvs_internal_pinned_scratch(mvs_ctx* ctx);                 // 256 bytes of
 void* mvs_internal_pinned_stage(mvs_ctx* ctx, size_t bytes);      // persistent pinned staging buffer (nullptr on failure)
 // cudaMemcpyAsync(host -> device) that takes pageable sources through a pinned ring filled by several host threads
 int mvs_internal_upload(mvs_ctx* ctx, cudaStream_t st, void* dst, const void* src, size_t bytes);
+// memcpy whose stores bypass the caches (AVX2 streaming stores; plain memcpy on hosts without AVX2): for filling the
+// pinned staging ring, whose lines the host never reads again.  mvs_driver.cpp.
+void mvs_internal_copy_streaming(void* dst, const void* src, size_t bytes);

@@ -15,3 +15,15 @@ for mode in (0, 2, 0, 2):
     for _ in range(3): sk.project_csr(h, off, d, out=out)
     dt = (time.perf_counter()-t)/3
     print("stage_uploads=%d: %.1f ms per 0.8 GB batch = %.1f GB/s, %.2f G hashes/s" % (mode, dt*1e3, n*per*8/dt/1e9, n*per/dt/1e9))
+
+# how the ring is filled: memcpy / streaming stores x host threads
+sk.set_option("stage_uploads", 0)
+for copy in (0, 1):
+    for threads in (2, 4, 8, 12, 16):
+        sk.set_option("stage_copy", copy)
+        sk.set_option("stage_threads", threads)
+        sk.project_csr(h, off, d, out=out)
+        t = time.perf_counter()
+        for _ in range(3): sk.project_csr(h, off, d, out=out)
+        dt = (time.perf_counter()-t)/3
+        print("stage_copy=%d stage_threads=%2d: %.1f ms per 0.8 GB batch = %.1f GB/s" % (copy, threads, dt*1e3, n*per*8/dt/1e9))
