@@ -417,7 +417,7 @@ def main():
                     "pageable_host_buffers": None if g["pageable_ms"] is None else {
                         "value": g["total"] / (g["pageable_ms"] * 1e-3), "unit": UNIT, "ms_per_step": g["pageable_ms"],
                         "how": "same call, numpy (pageable) arrays in and out: the library stages them through a pinned "
-                               "ring with 4 copy threads (measured at N = 1 only)"}},
+                               "ring with 8 copy threads using streaming stores (measured at N = 1 only)"}},
             "gpu_launches": int(g["launches"]),
             "clocks": g["clk"],
             "roofline": roofline,

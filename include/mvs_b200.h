@@ -237,8 +237,8 @@ int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second);
  * (all paths are exact; these knobs exist for the parity tests and the A/B measurements in profiles/);
  * "stage_uploads": 0 = uploads from pageable caller memory go through a pinned ring filled by host threads (default),
  *                  2 = plain cudaMemcpyAsync (the driver's own staging), for A/B measurements;
- * "stage_copy": how the ring is filled, 0 = memcpy (default), 1 = streaming stores;  "stage_threads": 1..64 host threads
- *                  per ring slot (default 4);
+ * "stage_copy": how the ring is filled, 0 = memcpy, 1 = streaming stores (default);  "stage_threads": 1..64 host
+ *                  threads per ring slot (default 8; profiles/r01g_stage_copy_ab.txt);
  * "release_workspace": frees the device and pinned buffers the pairwise entry points keep between calls (they are
  * grow-only and otherwise live until mvs_destroy). */
 int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value);

@@ -94,8 +94,8 @@ struct mvs_ctx {
     cudaEvent_t stage_ev[2] = {nullptr, nullptr};    // "the DMA out of ring slot k has finished"
     bool stage_busy[2] = {false, false};
     unsigned stage_turn = 0;
-    int stage_copy = 0;                          // 0 = memcpy into the ring, 1 = streaming stores (mvs_internal_copy_streaming)
-    int stage_threads = 4;                       // host threads filling one ring slot
+    int stage_copy = 1;                          // 0 = memcpy into the ring, 1 = streaming stores (mvs_internal_copy_streaming)
+    int stage_threads = 8;                       // host threads filling one ring slot
     int stage_uploads = 0;                       // 0 = pageable sources go through the pinned ring (default), 2 = plain cudaMemcpyAsync
 };
 
