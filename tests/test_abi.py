@@ -70,3 +70,19 @@ def test_synthetic_generator_is_injective_and_in_range():
     hr, offr = mvs.synthetic.ragged_batch([3, 0, 5], seed=0, first_sample=10)
     assert offr.tolist() == [0, 3, 3, 8] and len(np.unique(hr)) == 8
     assert np.array_equal(hr[:3], mvs.synthetic.synth_hashes([10, 10, 10], [0, 1, 2], 0))
+
+
+def test_streaming_copy_handles_every_alignment_and_tail():
+    """The copy that fills the pinned staging ring (streaming stores after an aligned head) is a memcpy."""
+    lib = mvs.load_library()
+    fn = getattr(lib, "_Z27mvs_internal_copy_streamingPvPKvm")          # internal C++ symbol, not part of the C ABI
+    fn.restype, fn.argtypes = None, [C.c_void_p, C.c_void_p, C.c_size_t]
+    rng = np.random.default_rng(3)
+    src = rng.integers(0, 256, 4096 + 700, dtype=np.uint8)
+    for doff in (0, 1, 31, 32, 33, 63):
+        for soff in (0, 5, 64):
+            for n in (0, 1, 31, 127, 128, 129, 1000, 4096):
+                dst = np.full(4096 + 800, 0xAB, dtype=np.uint8)
+                fn(dst.ctypes.data + doff, src.ctypes.data + soff, n)
+                assert np.array_equal(dst[doff:doff + n], src[soff:soff + n])
+                assert (dst[:doff] == 0xAB).all() and (dst[doff + n:] == 0xAB).all()

@@ -199,3 +199,27 @@ def test_error_paths(sk):
     assert lib.mvs_project_batch(sk._h, h.ctypes.data, bad_off.ctypes.data, 1, 0, 0, out.ctypes.data) == -1
     assert lib.mvs_project_batch(sk._h, None, None, 1, 64, 0, out.ctypes.data) == -1
     assert lib.mvs_project_batch(sk._h, h.ctypes.data, bad_off.ctypes.data, 0, 64, 0, None) == 0
+
+
+def test_host_side_helpers_binding_write_combined_and_staging_modes(sk):
+    """mvs_bind_host_to_device never fails on a box without NUMA information; a write-combined input buffer and
+    every way of filling the staging ring (pageable source >= 2 MB, odd offsets) give the oracle's vectors."""
+    from metagenome_vector_sketches_b200.projection import pinned_empty
+    node, applied = mvs.bind_host_to_device(0)
+    assert node >= -1 and 0 <= applied <= 3
+    sizes = [300001, 7, 0, 123457]
+    h, off = mvs.synthetic.ragged_batch(sizes, seed=21)
+    want = oracle_csr(h, off, 192)
+    wc = pinned_empty(len(h), np.uint64, write_combined=True)
+    wc.a[:] = h
+    assert np.array_equal(sk.project_csr(wc.a, off, 192), want)
+    big = np.empty(len(h) + 3, dtype=np.uint64)[3:]                       # pageable, 24 bytes off the allocation
+    big[:] = h
+    try:
+        for copy, threads in ((0, 4), (1, 1), (1, 3), (1, 8), (0, 64)):
+            sk.set_option("stage_copy", copy)
+            sk.set_option("stage_threads", threads)
+            assert np.array_equal(sk.project_csr(big, off, 192), want)
+    finally:
+        sk.set_option("stage_copy", 1)
+        sk.set_option("stage_threads", 8)
