@@ -63,7 +63,6 @@ constexpr uint64_t kGolden = 0x9e3779b97f4a7c15ULL;
 constexpr uint32_t kFold = 0x80000001u;          // passed as a kernel argument so that the multiply stays an IMAD
 constexpr uint32_t kCarryRisk = 0xFFFFF800u;     // (lo32(hb) | 0xC0000000) >= this: + 64*block may reach bit 30
 constexpr uint32_t kK1lo = 0x1ce4e5b9u, kK1hi = 0xbf58476du;   // 0xbf58476d1ce4e5b9
-constexpr uint32_t kK2lo = 0x133111ebu, kK2hi = 0x94d049bbu;   // 0x94d049bb133111eb
 
 struct __align__(16) WarpTask {                  // 32 bytes
     uint64_t begin;                              // first hash (index into the batch array)
@@ -91,24 +90,18 @@ __device__ __forceinline__ void mix64(uint64_t x, uint32_t& lo, uint32_t& hi)
     hi = static_cast<uint32_t>(x >> 32);
 }
 
-// c = cooked record of one hash: c.x = hb = hash + base, c.y = {F, M} (see header), raw = the hash itself (read only when EXACT);
-// off = 64*block of this lane (< 2048).  EXACT = false: the tile pass has proved that lo32(hb) + off stays below
-// bit 30.  Outputs: lo = final low word; hi = high word BEFORE the last xor-shift (columns 33..63 are final, slot 0
-// holds the raw bit 0); eacc += popc(hi * fold), fold = 0x80000001 (see header).
-// Pipe placement (the ALU pipe is the binding unit): the second 64-bit multiply is one IMAD.WIDE whose high word is
-// then accumulated by two IMADs, and the running popcount sum is an IMAD by `one` (a kernel-argument 1 that ptxas cannot
-// fold into an IADD3), so no integer add of the mixer is left on the ALU pipe.  (Handing {0, M} to the first
-// IMAD.WIDE as its 64-bit addend was tried: ptxas splits it into IMAD.WIDE + IADD3 + IMAD.X.)
+// c = cooked record of one hash: c.x = hb = hash + base, c.y = {F, M} (see header); off = 64*block of
+// this lane (< 2048).  EXACT = false: the tile pass has proved that lo32(hb) + off stays below bit 30.
+// Outputs: lo = final low word; hi = high word BEFORE the last xor-shift (columns 33..63 are
+// final, slot 0 holds the raw bit 0); eacc += popc(hi * fold), fold = 0x80000001 (see header).
 template <bool EXACT>
-__device__ __forceinline__ void mix_staged(ulonglong2 c, uint64_t raw, uint64_t base, uint32_t off, uint32_t fold, uint32_t one,
-                                           uint32_t& lo, uint32_t& hi, uint32_t& eacc)
+__device__ __forceinline__ void mix_staged(ulonglong2 c, uint32_t off, uint32_t fold, uint32_t& lo, uint32_t& hi,
+                                           uint32_t& eacc)
 {
-    uint32_t zl, zh;                             // (x ^ (x >> 30)) * K1
+    uint64_t x;
     if constexpr (EXACT) {
-        uint64_t x = raw + base + off;
+        x = c.x + off;
         x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ULL;
-        zl = static_cast<uint32_t>(x);
-        zh = static_cast<uint32_t>(x >> 32);
     } else {
         const uint32_t xl = static_cast<uint32_t>(c.x) + off;
         const uint32_t l1 = xl ^ static_cast<uint32_t>(c.y);
@@ -116,23 +109,16 @@ __device__ __forceinline__ void mix_staged(ulonglong2 c, uint64_t raw, uint64_t 
         asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(t) : "r"(l1), "r"(kK1hi));
         uint64_t w;
         asm("mul.wide.u32 %0, %1, %2;" : "=l"(w) : "r"(l1), "r"(kK1lo));
-        zl = static_cast<uint32_t>(w);
-        zh = static_cast<uint32_t>(w >> 32) + t;
+        x = (static_cast<uint64_t>(static_cast<uint32_t>(w >> 32) + t) << 32) | static_cast<uint32_t>(w);
     }
-    const uint32_t yl = zl ^ __funnelshift_r(zl, zh, 27);                        // x ^ (x >> 27)
-    const uint32_t yh = zh ^ (zh >> 27);
-    uint64_t w2;                                                                   // * K2 = 0x94d049bb133111eb
-    asm("mul.wide.u32 %0, %1, %2;" : "=l"(w2) : "r"(yl), "r"(kK2lo));
-    const uint32_t xl = static_cast<uint32_t>(w2);
-    uint32_t xh = static_cast<uint32_t>(w2 >> 32);
-    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(xh) : "r"(yl), "r"(kK2hi));
-    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(xh) : "r"(yh), "r"(kK2lo));
+    x = (x ^ (x >> 27)) * 0x94d049bb133111ebULL;
+    const uint32_t xl = static_cast<uint32_t>(x);
+    const uint32_t xh = static_cast<uint32_t>(x >> 32);
     lo = xl ^ __funnelshift_r(xl, xh, 31);
     hi = xh;
     uint32_t t;
     asm("mul.lo.u32 %0, %1, %2;" : "=r"(t) : "r"(xh), "r"(fold));
-    const uint32_t pc = static_cast<uint32_t>(__popc(t));
-    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(eacc) : "r"(pc), "r"(one));
+    eacc += static_cast<uint32_t>(__popc(t));
 }
 
 // tile pass: raw hash -> cooked record
@@ -183,15 +169,13 @@ __device__ __forceinline__ uint32_t hs4(uint32_t (&P)[kPlanes], uint32_t a, uint
 // carry per word.  sp points at the lane's first cooked record of the group in shared
 // memory; consecutive hashes of the lane are S records apart.
 template <int S, bool EXACT>
-__device__ __forceinline__ void group16(const ulonglong2* __restrict__ sp, const uint64_t* __restrict__ rp, uint64_t base,
-                                        uint32_t off, uint32_t fold, uint32_t one,
+__device__ __forceinline__ void group16(const ulonglong2* __restrict__ sp, uint32_t off, uint32_t fold,
                                         uint32_t (&Plo)[kPlanes], uint32_t (&Phi)[kPlanes],
                                         uint32_t& c16lo, uint32_t& c16hi, uint32_t& eacc)
 {
     uint32_t lo[16], hi[16];
 #pragma unroll
-    for (int i = 0; i < 16; ++i)                 // LDS.128 (broadcast if S == 1); the raw hash only on the EXACT path
-        mix_staged<EXACT>(sp[i * S], EXACT ? rp[i * S] : 0ull, base, off, fold, one, lo[i], hi[i], eacc);
+    for (int i = 0; i < 16; ++i) mix_staged<EXACT>(sp[i * S], off, fold, lo[i], hi[i], eacc);   // LDS.128 (broadcast if S == 1)
     uint32_t fl[4], fh[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
@@ -255,7 +239,6 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
     uint32_t pend16lo = 0, pend16hi = 0, pend32lo = 0, pend32hi = 0;
     uint32_t g = 0;                              // groups done (warp-uniform)
     uint32_t eacc = 0;                           // sum of popc(hi * fold) over this lane's hashes
-    const uint32_t one = fold >> 31;             // 1, opaque to ptxas (see mix_staged)
 
     const uint32_t ntiles = (count + kTileHashes - 1) / kTileHashes;
 
@@ -289,9 +272,8 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
         const uint32_t ngroups = (rounds + 15) >> 4;           // <= kGroupsPerTile
         for (uint32_t gi = 0; gi < ngroups; ++gi, ++g) {
             uint32_t c16lo, c16hi;
-            const uint32_t at = gi * (16 * S) + slot;
-            if (exact) group16<S, true>(cooked + at, st + at, base, off, fold, one, Plo, Phi, c16lo, c16hi, eacc);
-            else group16<S, false>(cooked + at, st + at, base, off, fold, one, Plo, Phi, c16lo, c16hi, eacc);
+            if (exact) group16<S, true>(cooked + gi * (16 * S) + slot, off, fold, Plo, Phi, c16lo, c16hi, eacc);
+            else group16<S, false>(cooked + gi * (16 * S) + slot, off, fold, Plo, Phi, c16lo, c16hi, eacc);
             if ((g & 1u) == 0u) {
                 pend16lo = c16lo; pend16hi = c16hi;
             } else {
