@@ -37,10 +37,10 @@ UNIT = "hashes/s"
 WORKLOAD = "configs[1]: synthetic 10k samples x 50k hashes, d=2048, seed 0"
 
 
-# dram__bytes_read.sum (4.003425 GB) + dram__bytes_write.sum (317.2 MB) of one project_kernel launch of the default
-# workload, profiles/r01c_project_kernel_ncu_full.txt; algorithmic bytes are 4.08 GB, the rest are the partial rows
+# dram__bytes_read.sum (4.005037 GB) + dram__bytes_write.sum (317.1 MB) of one project_kernel launch of the default
+# workload, profiles/r01j_project_kernel_ncu_full.txt; algorithmic bytes are 4.08 GB, the rest are the partial rows
 # of samples split over 4 warp tasks (written once, read once by reduce_partials_kernel)
-NCU_TRAFFIC_BYTES = 4003425000 + 317199616
+NCU_TRAFFIC_BYTES = 4005037000 + 317129984
 
 
 def work_per_hash(d):
@@ -356,7 +356,7 @@ def main():
     alg_bytes = total * 8 + n * d * 4
     # Issued-instruction view, the one that cannot exceed 1: per (hash, 32 blocks) round a warp issues
     # ALU_EQUIV instructions that need an ALU-pipe slot: 12.9 on the ALU pipe itself (8.6 LOP3, 3.2 SHF, 1.1 other:
-    # per-opcode counts of profiles/r01c_project_kernel_ncu_full.txt) + 2 IMAD.WIDE, which displace one ALU slot
+    # per-opcode counts of profiles/r01j_project_kernel_ncu_full.txt) + 2 IMAD.WIDE, which displace one ALU slot
     # each (profiles/r01b_kexp_issue_mix_and_variants.txt); the 16-lane ALU pipe takes one warp instruction every
     # 2 clocks (= the live LOP3 peak below).
     nb = (d + 63) // 64
@@ -368,10 +368,10 @@ def main():
                 "peak": peaks["lop3"] / 1e12, "frac": alu_lane_ops / peaks["lop3"],
                 "alu_equiv_warp_instr_per_round": ALU_EQUIV,
                 "how": "ALU-slot instructions of the inner loop (static SASS count) x rounds / kernel time, against the "
-                       "live LOP3-only issue peak; ncu (profiles/r01c_project_kernel_ncu_full.txt): pipe_alu 74.0 % + "
-                       "IMAD.WIDE slots, fmaheavy 68.0 %, xu 23.3 %, issue 73.8 %"}
+                       "live LOP3-only issue peak; ncu (profiles/r01j_project_kernel_ncu_full.txt): pipe_alu 74.4 % + "
+                       "IMAD.WIDE slots, fmaheavy 70.9 %, xu 23.7 %, issue 74.5 %"}
     # DRAM bytes of one project_kernel launch from the committed ncu --set full capture of THIS workload
-    # (profiles/r01c_project_kernel_ncu_full.txt: dram__bytes_read.sum + dram__bytes_write.sum); other shapes: null
+    # (profiles/r01j_project_kernel_ncu_full.txt: dram__bytes_read.sum + dram__bytes_write.sum); other shapes: null
     traffic = NCU_TRAFFIC_BYTES if (n, per, d) == (10000, 50000, 2048) else None
     roofline = {
         "bound": "int32-issue (ALU+FMA pipes); not hbm, not tensor -- see DESIGN.md",
