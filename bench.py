@@ -130,9 +130,19 @@ def _load_cpu_arm():
 def cpu_arm(per_sample, d, steps, warmup, target_s):
     """Time the CPU arm on a bounded prefix of the workload.  Returns dict(value, cores, kind, sample, ms_per_step)."""
     import metagenome_vector_sketches_b200.synthetic as syn
-    cores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))      # before libgomp is loaded
+    try:
+        cores = len(os.sched_getaffinity(0)) or 1
+    except AttributeError:  # pragma: no cover
+        cores = os.cpu_count() or 1
+    # The CPU arm uses every host thread it may run on.  torchrun exports OMP_NUM_THREADS=1 to its workers, so the
+    # variable is overwritten (before libgomp is loaded) and the thread count is also set through libgomp itself.
+    os.environ["OMP_NUM_THREADS"] = str(cores)
     kind, fn = _load_cpu_arm()
+    try:
+        import ctypes as C
+        C.CDLL("libgomp.so.1").omp_set_num_threads(int(cores))
+    except OSError:  # pragma: no cover
+        pass
     # calibrate on one sample per core, then size a step to ~target_s seconds
     h, off = syn.uniform_batch(cores, per_sample, seed=0)
     t_cal = max(fn(h, off, d), 1e-4)
