@@ -74,13 +74,25 @@ int mvs_project_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offs
                       int64_t n_samples, int d, uint64_t seed, int32_t* out);
 
 /* mvs_project_batch fused with the epilogue of sketch() (reference
- * src/project_everything.cpp:327-347): any of the three HOST outputs may be NULL.
- *   out    n_samples*d int32   (vectors.bin, int32 mode)
- *   out16  n_samples*d int16   (vectors.bin, --int16 mode: saturated to [-32768, 32767])
- *   sumsq  n_samples uint64    (exact sum of squares; norm = sqrt(sumsq / d)) */
+ * src/project_everything.cpp:327-347): any of the four HOST outputs may be NULL.
+ *   out        n_samples*d int32   (vectors.bin, int32 mode)
+ *   out16      n_samples*d int16   (vectors.bin, --int16 mode: saturated to [-32768, 32767])
+ *   sumsq      n_samples uint64    (exact sum of squares; sqrt(sumsq / d) is the mathematically exact norm)
+ *   ref_norms  n_samples float     (the norm AS THE REFERENCE COMPUTES IT, :328-329: float32, Eigen 3.2 SSE
+ *                                   reduction order, FMA, 1/sqrt(d) from the host CPU's rsqrtss -- widened to
+ *                                   double and printed with %g it is the reference's vector_norms.txt column
+ *                                   on the same host; computed from the int32 values before saturation) */
 int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offsets,
                      int64_t n_samples, int d, uint64_t seed, int32_t* out, int16_t* out16,
-                     uint64_t* sumsq);
+                     uint64_t* sumsq, float* ref_norms);
+
+/* The same over several GPUs in ONE call (SURVEY 8b "one call may use all GPUs"; the reference's analogue is
+ * the dynamic OpenMP schedule of src/project_everything.cpp:289): the batch is cut into n_ctx contiguous
+ * size-balanced shards (mvs_partition_samples), each context projects its shard on its own host thread and
+ * writes its own row range of the caller's buffers.  No inter-GPU exchange.  Contexts may share a device. */
+int mvs_sketch_batch_multi(mvs_ctx* const* ctxs, int n_ctx, const uint64_t* hashes, const uint64_t* offsets,
+                           int64_t n_samples, int d, uint64_t seed, int32_t* out, int16_t* out16,
+                           uint64_t* sumsq, float* ref_norms);
 
 /* Same computation with the hash array and the output already resident in HBM.
  * d_hashes / d_out are DEVICE pointers on the context's GPU, h_offsets is a HOST array
@@ -90,15 +102,22 @@ int mvs_project_device(mvs_ctx* ctx, const uint64_t* d_hashes, const uint64_t* h
                        int64_t n_samples, int d, uint64_t seed, int32_t* d_out, void* stream);
 
 /* Epilogue of sketch() on device-resident vectors (reference
- * src/project_everything.cpp:327-347): per row the exact integer sum of squares
- * (norm = sqrt(sumsq / d)) and, if d_out16 != NULL, the int16-saturated copy.
- * d_vec, d_sumsq (n_samples uint64) and d_out16 (n_samples*d int16) are DEVICE pointers. */
+ * src/project_everything.cpp:327-347): per row the exact integer sum of squares, the reference's
+ * float32 norm (see mvs_sketch_batch) and the int16-saturated copy; each output may be NULL.
+ * d_vec, d_sumsq (n_samples uint64), d_out16 (n_samples*d int16) and d_ref_norms (n_samples float)
+ * are DEVICE pointers. */
 int mvs_finalize_device(mvs_ctx* ctx, const int32_t* d_vec, int64_t n_samples, int d,
-                        uint64_t* d_sumsq, int16_t* d_out16, void* stream);
+                        uint64_t* d_sumsq, int16_t* d_out16, float* d_ref_norms, void* stream);
 
 /* Host-pointer convenience wrapper of the above (copies in and out). */
 int mvs_finalize(mvs_ctx* ctx, const int32_t* vec, int64_t n_samples, int d,
-                 uint64_t* sumsq, int16_t* out16);
+                 uint64_t* sumsq, int16_t* out16, float* ref_norms);
+
+/* The reference's norm on the HOST (needs no GPU): the same float32 sequence as the device epilogue, for
+ * callers that hold int32 rows only.  mvs_reference_inv_sqrt_d is the 1/sqrt(d) factor the reference binary
+ * uses (rsqrtss + one Newton-Raphson step; the approximation instruction is the executing CPU's). */
+int mvs_reference_norms(const int32_t* vec, int64_t n_samples, int d, float* norms);
+float mvs_reference_inv_sqrt_d(int d);
 
 /* ---- drivers: the reference's two CLIs as library calls ------------------------------ */
 typedef struct mvs_hash_batch {
@@ -118,10 +137,16 @@ int mvs_parse_hash_file(const char* path, int named, mvs_hash_batch** out);
 void mvs_free_hash_batch(mvs_hash_batch* b);
 
 /* db/ writer of sketch() (reference src/project_everything.cpp:306-361): vectors.bin (int32
- * rows, or int16 if vec16 != NULL), vector_norms.txt ("<name> <sqrt(sumsq/d)>", %g),
- * dimension.txt, dtype.txt.  Needs no GPU. */
+ * rows, or int16 if vec16 != NULL), vector_norms.txt ("<name> <norm>", %g), dimension.txt, dtype.txt.
+ * The norm column is ref_norms (the reference's float32 value, file identical to the reference's) when
+ * given, else sqrt(sumsq/d) when sumsq is given, else mvs_reference_norms(vec32).  Needs no GPU. */
 int mvs_write_db(const char* index_folder, int64_t n_samples, int d, const char* const* names,
-                 const uint64_t* sumsq, const int32_t* vec32, const int16_t* vec16);
+                 const float* ref_norms, const uint64_t* sumsq, const int32_t* vec32, const int16_t* vec16);
+
+/* Which norm mvs_sketch_file / the CLI print (process-wide): 0 = the reference's float32 norm (default;
+ * vector_norms.txt byte-identical to the reference's on the same host), 1 = sqrt(exact sum of squares / d). */
+int mvs_set_norms_mode(int mode);
+int mvs_get_norms_mode(void);
 
 /* Contiguous size-balanced static partition of a CSR batch over n_parts GPUs; writes
  * n_parts + 1 sample bounds.  No collective is needed afterwards: samples are independent. */

@@ -45,15 +45,22 @@ SIGNATURES = {
     "mvs_transform_set": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64, C.c_void_p]),
     "mvs_project_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64, C.c_void_p]),
     "mvs_sketch_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64, C.c_void_p,
-                                   C.c_void_p, C.c_void_p]),
+                                   C.c_void_p, C.c_void_p, C.c_void_p]),
+    "mvs_sketch_batch_multi": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int,
+                                         C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "mvs_project_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64,
                                      C.c_void_p, C.c_void_p]),
-    "mvs_finalize_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
-    "mvs_finalize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]),
+    "mvs_finalize_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_void_p]),
+    "mvs_finalize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "mvs_reference_norms": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_void_p]),
+    "mvs_reference_inv_sqrt_d": (C.c_float, [C.c_int]),
+    "mvs_set_norms_mode": (C.c_int, [C.c_int]),
+    "mvs_get_norms_mode": (C.c_int, []),
     "mvs_parse_hash_file": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.POINTER(HashBatch))]),
     "mvs_free_hash_batch": (None, [C.POINTER(HashBatch)]),
     "mvs_write_db": (C.c_int, [C.c_char_p, C.c_int64, C.c_int, C.POINTER(C.c_char_p), C.c_void_p, C.c_void_p,
-                               C.c_void_p]),
+                               C.c_void_p, C.c_void_p]),
     "mvs_partition_samples": (None, [C.c_void_p, C.c_int64, C.c_int, C.c_void_p]),
     "mvs_sketch_file": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_char_p, C.c_char_p, C.c_int, C.c_int,
                                   C.c_uint64, C.c_int]),

@@ -29,7 +29,7 @@ using mvs::ReduceItem;
 using mvs::WarpTask;
 
 constexpr int kSlots = 3;                        // slices in flight in mvs_project_batch
-constexpr int kAbiVersion = 1;
+constexpr int kAbiVersion = 2;                   // 2: reference-order float32 norms (ref_norms) in the epilogue entry points
 constexpr int kTimingRing = 64;
 
 constexpr int kPairwiseSlots = 16;
@@ -48,7 +48,7 @@ struct Slot {
     cudaEvent_t uploaded = nullptr;              // the pinned plan buffers have been read by the copy engine
     bool busy = false;
     bool upload_busy = false;
-    DevBuf hashes, out, partials, tasks, reduce, sumsq, out16;
+    DevBuf hashes, out, partials, tasks, reduce, sumsq, out16, refnorm;
     PinBuf h_tasks, h_reduce;
 };
 
@@ -277,7 +277,7 @@ int run_range(mvs_ctx* ctx, Slot& sl, const uint64_t* d_hashes, const uint64_t* 
               cudaStream_t st, bool record_timing)
 {
     // Small batches: shrink the per-task hash cap so that the grid still fills the GPU for several
-    // waves (a warp task is the unit of parallelism); large batches keep the full 4080-round cap.
+    // waves (a warp task is the unit of parallelism); large batches keep the full kMaxRounds cap.
     Geometry g = g_in;
     {
         const uint64_t total = offsets[s1] - offsets[s0];
@@ -522,7 +522,7 @@ void mvs_destroy(mvs_ctx* ctx)
     cudaSetDevice(ctx->device);
     for (auto& sl : ctx->slots) {
         if (sl.stream) cudaStreamSynchronize(sl.stream);
-        for (DevBuf* b : {&sl.hashes, &sl.out, &sl.partials, &sl.tasks, &sl.reduce, &sl.sumsq, &sl.out16})
+        for (DevBuf* b : {&sl.hashes, &sl.out, &sl.partials, &sl.tasks, &sl.reduce, &sl.sumsq, &sl.out16, &sl.refnorm})
             if (b->p) cudaFree(b->p);
         for (PinBuf* b : {&sl.h_tasks, &sl.h_reduce})
             if (b->p) cudaFreeHost(b->p);
@@ -566,9 +566,9 @@ int mvs_project_device(mvs_ctx* ctx, const uint64_t* d_hashes, const uint64_t* h
 }
 
 int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offsets, int64_t n_samples, int d,
-                     uint64_t seed, int32_t* out, int16_t* out16, uint64_t* sumsq)
+                     uint64_t seed, int32_t* out, int16_t* out16, uint64_t* sumsq, float* ref_norms)
 {
-    if (!ctx || !offsets || n_samples < 0 || d <= 0 || (!out && !out16 && !sumsq && n_samples > 0))
+    if (!ctx || !offsets || n_samples < 0 || d <= 0 || (!out && !out16 && !sumsq && !ref_norms && n_samples > 0))
         return MVS_ERR_INVALID_ARG;
     if (n_samples == 0) return MVS_OK;
     if (n_samples >= 0xFFFFFFF0ll) return MVS_ERR_TOO_LARGE;
@@ -598,6 +598,7 @@ int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offse
         if ((rc = ensure_dev(ctx, sl.out, static_cast<size_t>(rows) * row_bytes)) != MVS_OK) break;
         if (sumsq && (rc = ensure_dev(ctx, sl.sumsq, static_cast<size_t>(rows) * sizeof(uint64_t))) != MVS_OK) break;
         if (out16 && (rc = ensure_dev(ctx, sl.out16, static_cast<size_t>(rows) * row_bytes / 2)) != MVS_OK) break;
+        if (ref_norms && (rc = ensure_dev(ctx, sl.refnorm, static_cast<size_t>(rows) * sizeof(float))) != MVS_OK) break;
         if (nh) {
             if ((rc = mvs_internal_upload(ctx, sl.stream, sl.hashes.p, hashes + h0, nh * sizeof(uint64_t))) != MVS_OK) break;
             ctx->timing.h2d_bytes += nh * sizeof(uint64_t);
@@ -607,10 +608,11 @@ int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offse
         if (rc != MVS_OK) break;
         ctx->timing.h2d_bytes += ctx->timing.warp_tasks * sizeof(WarpTask);
         cudaError_t e = cudaSuccess;
-        if (out16 || sumsq) {                    // fused epilogue of sketch(): sum of squares + int16 saturation
+        if (out16 || sumsq || ref_norms) {       // fused epilogue of sketch(): norms + int16 saturation
             rc = mvs_finalize_device(ctx, static_cast<const int32_t*>(sl.out.p), rows, d,
                                      sumsq ? static_cast<uint64_t*>(sl.sumsq.p) : nullptr,
-                                     out16 ? static_cast<int16_t*>(sl.out16.p) : nullptr, sl.stream);
+                                     out16 ? static_cast<int16_t*>(sl.out16.p) : nullptr,
+                                     ref_norms ? static_cast<float*>(sl.refnorm.p) : nullptr, sl.stream);
             if (rc != MVS_OK) break;
         }
         if (out) {
@@ -628,6 +630,11 @@ int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offse
                                 cudaMemcpyDeviceToHost, sl.stream);
             ctx->timing.d2h_bytes += static_cast<uint64_t>(rows) * sizeof(uint64_t);
         }
+        if (ref_norms && e == cudaSuccess) {
+            e = cudaMemcpyAsync(ref_norms + s0, sl.refnorm.p, static_cast<size_t>(rows) * sizeof(float),
+                                cudaMemcpyDeviceToHost, sl.stream);
+            ctx->timing.d2h_bytes += static_cast<uint64_t>(rows) * sizeof(float);
+        }
         if (e == cudaSuccess) e = cudaEventRecord(sl.done, sl.stream);
         if (e != cudaSuccess) { ctx->last_cuda = e; cudaGetLastError(); rc = MVS_ERR_CUDA; break; }
         sl.busy = true;
@@ -644,7 +651,7 @@ int mvs_project_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offs
                       uint64_t seed, int32_t* out)
 {
     if (!out && n_samples > 0) return MVS_ERR_INVALID_ARG;
-    return mvs_sketch_batch(ctx, hashes, offsets, n_samples, d, seed, out, nullptr, nullptr);
+    return mvs_sketch_batch(ctx, hashes, offsets, n_samples, d, seed, out, nullptr, nullptr, nullptr);
 }
 
 int mvs_transform_set(mvs_ctx* ctx, const uint64_t* hashes, int64_t n_hashes, int d, uint64_t seed, int32_t* out)
@@ -655,7 +662,7 @@ int mvs_transform_set(mvs_ctx* ctx, const uint64_t* hashes, int64_t n_hashes, in
 }
 
 int mvs_finalize_device(mvs_ctx* ctx, const int32_t* d_vec, int64_t n_samples, int d, uint64_t* d_sumsq,
-                        int16_t* d_out16, void* stream)
+                        int16_t* d_out16, float* d_ref_norms, void* stream)
 {
     if (!ctx || n_samples < 0 || d <= 0 || (!d_vec && n_samples > 0)) return MVS_ERR_INVALID_ARG;
     if (n_samples == 0) return MVS_OK;
@@ -665,14 +672,16 @@ int mvs_finalize_device(mvs_ctx* ctx, const int32_t* d_vec, int64_t n_samples, i
     const int64_t grid = (n_samples + rows_per_cta - 1) / rows_per_cta;
     if (grid > 0x7FFFFFFFll) return MVS_ERR_TOO_LARGE;
     mvs::finalize_kernel<<<static_cast<unsigned>(grid), 256, 0, st>>>(
-        d_vec, n_samples, d, reinterpret_cast<unsigned long long*>(d_sumsq), d_out16);
+        d_vec, n_samples, d, reinterpret_cast<unsigned long long*>(d_sumsq), d_out16,
+        d_ref_norms ? mvs_reference_inv_sqrt_d(d) : 0.f, d_ref_norms);
     MVS_CUDA(ctx, cudaGetLastError());
     ctx->launches += 1;
     if (!stream) MVS_CUDA(ctx, cudaStreamSynchronize(st));
     return MVS_OK;
 }
 
-int mvs_finalize(mvs_ctx* ctx, const int32_t* vec, int64_t n_samples, int d, uint64_t* sumsq, int16_t* out16)
+int mvs_finalize(mvs_ctx* ctx, const int32_t* vec, int64_t n_samples, int d, uint64_t* sumsq, int16_t* out16,
+                 float* ref_norms)
 {
     if (!ctx || n_samples < 0 || d <= 0 || (!vec && n_samples > 0)) return MVS_ERR_INVALID_ARG;
     if (n_samples == 0) return MVS_OK;
@@ -681,17 +690,22 @@ int mvs_finalize(mvs_ctx* ctx, const int32_t* vec, int64_t n_samples, int d, uin
     int rc = wait_slot(ctx, sl);
     if (rc != MVS_OK) return rc;
     const size_t n = static_cast<size_t>(n_samples) * static_cast<size_t>(d);
-    // layout in sl.out: [vec int32 n][sumsq u64 n_samples][out16 int16 n]
+    // layout in sl.out: [vec int32 n][sumsq u64 n_samples][ref norms f32 n_samples][out16 int16 n]
     const size_t off_ss = (n * sizeof(int32_t) + 255) / 256 * 256;
-    const size_t off_16 = off_ss + (static_cast<size_t>(n_samples) * sizeof(uint64_t) + 255) / 256 * 256;
+    const size_t off_rn = off_ss + (static_cast<size_t>(n_samples) * sizeof(uint64_t) + 255) / 256 * 256;
+    const size_t off_16 = off_rn + (static_cast<size_t>(n_samples) * sizeof(float) + 255) / 256 * 256;
     const size_t total = off_16 + n * sizeof(int16_t);
     if ((rc = ensure_dev(ctx, sl.out, total)) != MVS_OK) return rc;
     char* base = static_cast<char*>(sl.out.p);
     MVS_CUDA(ctx, cudaMemcpyAsync(base, vec, n * sizeof(int32_t), cudaMemcpyHostToDevice, sl.stream));
     rc = mvs_finalize_device(ctx, reinterpret_cast<int32_t*>(base), n_samples, d,
                              reinterpret_cast<uint64_t*>(base + off_ss),
-                             out16 ? reinterpret_cast<int16_t*>(base + off_16) : nullptr, sl.stream);
+                             out16 ? reinterpret_cast<int16_t*>(base + off_16) : nullptr,
+                             ref_norms ? reinterpret_cast<float*>(base + off_rn) : nullptr, sl.stream);
     if (rc != MVS_OK) return rc;
+    if (ref_norms)
+        MVS_CUDA(ctx, cudaMemcpyAsync(ref_norms, base + off_rn, static_cast<size_t>(n_samples) * sizeof(float),
+                                      cudaMemcpyDeviceToHost, sl.stream));
     if (sumsq)
         MVS_CUDA(ctx, cudaMemcpyAsync(sumsq, base + off_ss, static_cast<size_t>(n_samples) * sizeof(uint64_t),
                                       cudaMemcpyDeviceToHost, sl.stream));

@@ -31,6 +31,9 @@
 
 namespace fs = std::filesystem;
 
+#include <atomic>
+static std::atomic<int> g_norms_mode{0};         // mvs_set_norms_mode: 0 = reference float32 (default), 1 = exact
+
 namespace {
 
 inline bool is_space(unsigned char c)            // isspace() in the "C" locale, as used by operator>>
@@ -388,11 +391,18 @@ static int parse_hash_file_impl(const char* path, int named, bool want_pinned, m
 extern "C" {
 
 int mvs_write_db(const char* index_folder, int64_t n_samples, int d, const char* const* names,
-                 const uint64_t* sumsq, const int32_t* vec32, const int16_t* vec16)
+                 const float* ref_norms, const uint64_t* sumsq, const int32_t* vec32, const int16_t* vec16)
 {
     if (!index_folder || n_samples < 0 || d <= 0 || (!vec32 && !vec16 && n_samples > 0) ||
-        (n_samples > 0 && (!names || !sumsq)))
+        (n_samples > 0 && (!names || (!ref_norms && !sumsq && !vec32))))
         return MVS_ERR_INVALID_ARG;
+    std::vector<float> host_norms;
+    if (!ref_norms && !sumsq && n_samples > 0) {                        // int32 rows only: the reference's expression on the host
+        host_norms.resize(static_cast<size_t>(n_samples));
+        const int nrc = mvs_reference_norms(vec32, n_samples, d, host_norms.data());
+        if (nrc != MVS_OK) return nrc;
+        ref_norms = host_norms.data();
+    }
     std::string dir(index_folder);
     if (dir.empty() || dir.back() != '/') dir += '/';
     FILE* fn = std::fopen((dir + "vector_norms.txt").c_str(), "w");
@@ -408,8 +418,10 @@ int mvs_write_db(const char* index_folder, int64_t n_samples, int d, const char*
         std::string text;
         text.reserve(static_cast<size_t>(n_samples) * 24);
         for (int64_t i = 0; i < n_samples; ++i) {
-            // norm = || v / sqrt(d) ||  (:327-329), from the exact integer sum of squares
-            const double norm = std::sqrt(static_cast<double>(sumsq[i]) / static_cast<double>(d));
+            // norm = || v / sqrt(d) ||  (:327-329): the reference's own float32 evaluation widened to double
+            // (mvs_norms.cpp), or -- the caller's choice -- from the exact integer sum of squares
+            const double norm = ref_norms ? static_cast<double>(ref_norms[i])
+                                          : std::sqrt(static_cast<double>(sumsq[i]) / static_cast<double>(d));
             text += names[i];
             text += ' ';
             text += format_g(norm);                                     // default ostream precision (:330)
@@ -448,8 +460,53 @@ void mvs_partition_samples(const uint64_t* offsets, int64_t n_samples, int n_par
     bounds[n_parts] = n_samples;
 }
 
-// sketch() after the parse: project hb on the given contexts (one host thread each), print the
-// reference's lines, write db/.  t0 = start of the reference's timer (:255, includes the parse).
+int mvs_set_norms_mode(int mode)
+{
+    if (mode != 0 && mode != 1) return MVS_ERR_INVALID_ARG;
+    g_norms_mode.store(mode);
+    return MVS_OK;
+}
+int mvs_get_norms_mode(void) { return g_norms_mode.load(); }
+
+// The sample loop of sketch() (:289-298) over several GPUs: contiguous size-balanced shards
+// (mvs_partition_samples), one host thread per context, every shard written straight into its own
+// row range of the caller's buffers.  No exchange between the GPUs: samples are independent.
+int mvs_sketch_batch_multi(mvs_ctx* const* ctxs, int n_ctx, const uint64_t* hashes, const uint64_t* offsets,
+                           int64_t n_samples, int d, uint64_t seed, int32_t* out, int16_t* out16, uint64_t* sumsq,
+                           float* ref_norms)
+{
+    if (!ctxs || n_ctx <= 0 || !offsets || n_samples < 0 || d <= 0) return MVS_ERR_INVALID_ARG;
+    for (int k = 0; k < n_ctx; ++k)
+        if (!ctxs[k]) return MVS_ERR_INVALID_ARG;
+    if (n_samples == 0) return MVS_OK;
+    if (!out && !out16 && !sumsq && !ref_norms) return MVS_ERR_INVALID_ARG;
+    for (int64_t s = 0; s < n_samples; ++s)
+        if (offsets[s + 1] < offsets[s]) return MVS_ERR_INVALID_ARG;
+    const int parts = static_cast<int>(std::min<int64_t>(n_ctx, n_samples));
+    std::vector<int64_t> bounds(static_cast<size_t>(parts) + 1);
+    mvs_partition_samples(offsets, n_samples, parts, bounds.data());
+    std::vector<int> rcs(static_cast<size_t>(parts), MVS_OK);
+    auto work = [&](int k) {
+        const int64_t a = bounds[static_cast<size_t>(k)], b = bounds[static_cast<size_t>(k) + 1];
+        if (b <= a) return;
+        const size_t row0 = static_cast<size_t>(a) * static_cast<size_t>(d);
+        rcs[static_cast<size_t>(k)] =
+            mvs_sketch_batch(ctxs[k], hashes, offsets + a, b - a, d, seed, out ? out + row0 : nullptr,
+                             out16 ? out16 + row0 : nullptr, sumsq ? sumsq + a : nullptr,
+                             ref_norms ? ref_norms + a : nullptr);
+    };
+    std::vector<std::thread> th;
+    for (int k = 1; k < parts; ++k) th.emplace_back(work, k);          // one host thread per GPU
+    work(0);
+    for (auto& t : th) t.join();
+    for (int r : rcs)
+        if (r != MVS_OK) return r;
+    return MVS_OK;
+}
+
+// sketch() after the parse: project hb on the given contexts, print the reference's lines, write db/.
+// t0 = start of the reference's timer (:255, includes the parse).  norms_mode 0 = the reference's float32
+// norm (vector_norms.txt identical to the reference's on this host), 1 = sqrt(exact sum of squares / d).
 static int sketch_parsed(mvs_ctx* const* ctxs, int n_ctx, mvs_hash_batch* hb, const std::string& dir, int d,
                          int use_int16, uint64_t seed, int verbose, std::chrono::steady_clock::time_point t0,
                          double parse_s, double wait_ctx_s)
@@ -461,29 +518,14 @@ static int sketch_parsed(mvs_ctx* const* ctxs, int n_ctx, mvs_hash_batch* hb, co
     int pin32 = 0, pin16 = 0;
     int32_t* v32 = use_int16 ? nullptr : static_cast<int32_t*>(host_alloc_any(count * sizeof(int32_t), &pin32));
     int16_t* v16 = use_int16 ? static_cast<int16_t*>(host_alloc_any(count * sizeof(int16_t), &pin16)) : nullptr;
-    std::vector<uint64_t> sumsq(static_cast<size_t>(n ? n : 1));
+    const bool exact_norms = g_norms_mode.load() == 1;
+    std::vector<uint64_t> sumsq(exact_norms ? static_cast<size_t>(n ? n : 1) : 0);
+    std::vector<float> ref_norms(exact_norms ? 0 : static_cast<size_t>(n ? n : 1));
     if ((!use_int16 && !v32) || (use_int16 && !v16)) rc = MVS_ERR_OOM;
 
-    if (rc == MVS_OK && n > 0) {
-        const int parts = static_cast<int>(std::min<int64_t>(n_ctx, n));
-        std::vector<int64_t> bounds(static_cast<size_t>(parts) + 1);
-        mvs_partition_samples(hb->offsets, n, parts, bounds.data());
-        std::vector<int> rcs(static_cast<size_t>(parts), MVS_OK);
-        auto work = [&](int k) {
-            const int64_t a = bounds[static_cast<size_t>(k)], b = bounds[static_cast<size_t>(k) + 1];
-            if (b <= a) return;
-            rcs[static_cast<size_t>(k)] = mvs_sketch_batch(
-                ctxs[k], hb->hashes, hb->offsets + a, b - a, d, seed,
-                v32 ? v32 + static_cast<size_t>(a) * d : nullptr, v16 ? v16 + static_cast<size_t>(a) * d : nullptr,
-                sumsq.data() + a);
-        };
-        std::vector<std::thread> th;
-        for (int k = 1; k < parts; ++k) th.emplace_back(work, k);      // one host thread per GPU
-        work(0);
-        for (auto& t : th) t.join();
-        for (int r : rcs)
-            if (r != MVS_OK && rc == MVS_OK) rc = r;
-    }
+    if (rc == MVS_OK && n > 0)
+        rc = mvs_sketch_batch_multi(ctxs, n_ctx, hb->hashes, hb->offsets, n, d, seed, v32, v16,
+                                    exact_norms ? sumsq.data() : nullptr, exact_norms ? nullptr : ref_norms.data());
     if (rc == MVS_OK) {
         if (verbose)
             for (int64_t i = 0; i < n; ++i)                             // :294-297 (order is arbitrary there)
@@ -492,7 +534,9 @@ static int sketch_parsed(mvs_ctx* const* ctxs, int n_ctx, mvs_hash_batch* hb, co
         const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         std::printf("Time to compute all projected vectors: %g seconds\n", sec);   // :300-303
         const auto t_projected = std::chrono::steady_clock::now();
-        rc = mvs_write_db(dir.c_str(), n, d, hb->names, sumsq.data(), v32, v16);
+        rc = mvs_write_db(dir.c_str(), n, d, hb->names, exact_norms ? nullptr : ref_norms.data(),
+                          exact_norms ? sumsq.data() : nullptr, v32, v16);
+        if (rc != MVS_OK) std::fprintf(stderr, "mvs: writing %s failed: %s\n", dir.c_str(), mvs_strerror(rc));
         if (std::getenv("MVS_TIMING")) {                                // stage split for tests/perf_cli.py
             const auto t_written = std::chrono::steady_clock::now();
             std::fprintf(stderr,

@@ -7,9 +7,9 @@
 // How: a *bit-sliced positional popcount*.  A lane owns one 64-column block b of one
 // hash stream.  For every hash it evaluates the 64-bit mixer once (two 32-bit words =
 // 64 columns) and feeds the two words into a Harley-Seal carry-save-adder tree whose
-// bit planes (weights 1,2,4,...,2^11) live in registers; one CSA is two LOP3.  No
+// bit planes (weights 1,2,4,...,2^13: kPlanes = 14) live in registers; one CSA is two LOP3.  No
 // per-column add is ever issued in the loop; the planes are expanded into int32
-// columns once per warp task (<= 4080 hashes per lane).  No matrix is materialised,
+// columns once per warp task (<= kMaxRounds = 16368 hashes per lane).  No matrix is materialised,
 // no atomics are used, integer adds make every partition order bit-exact.
 //
 // Work decomposition: a *warp task* = (sample, contiguous hash range, 32-block column
@@ -377,25 +377,87 @@ reduce_partials_kernel(const ReduceItem* __restrict__ items, uint32_t nitems, in
 
 // ------------------------------------------------------------------------------------
 // Epilogue of sketch() (reference src/project_everything.cpp:327-347): per row the exact
-// sum of squares and the int16-saturated copy.  One warp per row.
+// sum of squares, the int16-saturated copy and the norm the reference prints.  One warp per row.
+//
+// The reference norm (:328-329) is  (vec.cast<float>() / std::sqrt(float(d))).norm()  under
+// -O3 -ffast-math with the vendored Eigen 3.2.10, i.e. (read off the compiled reference, both its
+// -march=native and x86-64-v3 builds):
+//     inv  = rsqrtss(float(d)) refined by one Newton-Raphson step   (host: the instruction is the CPU's)
+//     x_j  = float(v_j) * inv                                       (one rounding each)
+//     SSE packets of 4, two packet accumulators: acc0 = x[0:4]^2, acc1 = x[4:8]^2 (plain products),
+//     then acc_k = fma(x, x, acc_k) over the following packet pairs, acc0 += acc1, one more fma for an
+//     odd last packet, horizontal add (a0 + a1) + (a2 + a3), scalar fma for the <= 3 tail columns,
+//     sqrtss.  Fewer than 4 columns: x_0^2 then scalar fma.
+// Every step is a correctly rounded IEEE binary32 operation, so the same sequence of __fmul_rn /
+// __fmaf_rn / __fadd_rn / __fsqrt_rn gives the same bits; lanes 0..7 of the warp own the 8 chains.
 // ------------------------------------------------------------------------------------
+__device__ __forceinline__ float reference_norm_row(const int32_t* __restrict__ v, int d, float inv, int lane)
+{
+    const int a2 = (d / 8) * 8, a1 = (d / 4) * 4;
+    float acc = 0.f;
+    if (lane < 8 && lane < a1) {                 // chain `lane`: columns lane, lane + 8, ... below a2 (or the only packet)
+        const float x0 = __fmul_rn(__int2float_rn(v[lane]), inv);
+        acc = __fmul_rn(x0, x0);
+        if (a1 > 4)
+            for (int j = lane + 8; j < a2; j += 8) {
+                const float x = __fmul_rn(__int2float_rn(v[j]), inv);
+                acc = __fmaf_rn(x, x, acc);
+            }
+    }
+    float res = 0.f;
+    if (a1 >= 4) {
+        if (a1 > 4) {
+            const float other = __shfl_down_sync(0xffffffffu, acc, 4);
+            acc = __fadd_rn(acc, other);         // lanes 0..3: acc0 + acc1
+            if (a1 > a2 && lane < 4) {           // odd last packet
+                const float x = __fmul_rn(__int2float_rn(v[a2 + lane]), inv);
+                acc = __fmaf_rn(x, x, acc);
+            }
+        }
+        const float nb = __shfl_xor_sync(0xffffffffu, acc, 1);
+        const float pair = __fadd_rn(acc, nb);   // lane 0: a0 + a1, lane 2: a2 + a3
+        const float hi = __shfl_down_sync(0xffffffffu, pair, 2);
+        res = __fadd_rn(pair, hi);               // lane 0: (a0 + a1) + (a2 + a3)
+        if (lane == 0)
+            for (int j = a1; j < d; ++j) {
+                const float x = __fmul_rn(__int2float_rn(v[j]), inv);
+                res = __fmaf_rn(x, x, res);
+            }
+    } else if (lane == 0) {
+        const float x0 = __fmul_rn(__int2float_rn(v[0]), inv);
+        res = __fmul_rn(x0, x0);
+        for (int j = 1; j < d; ++j) {
+            const float x = __fmul_rn(__int2float_rn(v[j]), inv);
+            res = __fmaf_rn(x, x, res);
+        }
+    }
+    return __fsqrt_rn(res);                      // valid in lane 0
+}
+
 __global__ void __launch_bounds__(256)
 finalize_kernel(const int32_t* __restrict__ vec, int64_t n_rows, int d,
-                unsigned long long* __restrict__ sumsq, int16_t* __restrict__ out16)
+                unsigned long long* __restrict__ sumsq, int16_t* __restrict__ out16,
+                float inv_sqrt_d, float* __restrict__ ref_norms)
 {
     const int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= n_rows) return;
     const int lane = threadIdx.x & 31;
     const int32_t* v = vec + row * d;
-    unsigned long long ss = 0;
-    for (int j = lane; j < d; j += 32) {
-        const int32_t x = v[j];
-        ss += static_cast<unsigned long long>(static_cast<long long>(x) * static_cast<long long>(x));
-        if (out16) out16[row * d + j] = static_cast<int16_t>(max(-32768, min(32767, x)));
-    }
+    if (sumsq || out16) {
+        unsigned long long ss = 0;
+        for (int j = lane; j < d; j += 32) {
+            const int32_t x = v[j];
+            ss += static_cast<unsigned long long>(static_cast<long long>(x) * static_cast<long long>(x));
+            if (out16) out16[row * d + j] = static_cast<int16_t>(max(-32768, min(32767, x)));
+        }
 #pragma unroll
-    for (int m = 16; m; m >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, m);
-    if (lane == 0 && sumsq) sumsq[row] = ss;
+        for (int m = 16; m; m >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, m);
+        if (lane == 0 && sumsq) sumsq[row] = ss;
+    }
+    if (ref_norms) {
+        const float nrm = reference_norm_row(v, d, inv_sqrt_d, lane);
+        if (lane == 0) ref_norms[row] = nrm;
+    }
 }
 
 // ------------------------------------------------------------------------------------

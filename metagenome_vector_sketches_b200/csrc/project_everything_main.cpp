@@ -2,7 +2,7 @@
 //
 //   project_everything sketch  <hash_file> <index_folder> [-t N] [-d D] [--int16]     (reference grammar)
 //   project_everything convert <signature_folder> <hash_file> [-t N]
-// additive, all optional:      [-s|--seed S] [--gpus G] [--quiet]
+// additive, all optional:      [-s|--seed S] [--gpus G | --devices a,b,..] [--norms reference|exact] [--quiet]
 // README / BASELINE spelling:  project_everything <input> <db>/ [-t N] [-d D] [-s S]
 //   (<input> a hash file -> sketch; a folder of *.sig.zip -> convert to <db>/hashes.txt.tmp, then sketch)
 //
@@ -39,6 +39,9 @@ void usage(const char* argv0)
                  "      --int16          : Use int16 instead of int32 for vector storage\n"
                  "      -s, --seed       : additive generator seed (default 0 = reference)\n"
                  "      --gpus           : number of GPUs to shard samples over (default 1)\n"
+                 "      --devices        : explicit CUDA device list, e.g. 0,1,2,3 (one shard per entry)\n"
+                 "      --norms          : reference (default: vector_norms.txt as the reference binary prints it\n"
+                 "                         on this host) | exact (sqrt of the exact integer sum of squares / d)\n"
                  "      --quiet          : no per-sample progress lines\n",
                  argv0, argv0);
 }
@@ -66,6 +69,8 @@ int main(int argc, char** argv)
     long long t = 1, d = 2048, gpus = 1;
     unsigned long long seed = 0;
     bool int16 = false, quiet = false, bad = false;
+    std::vector<int> devices;
+    int norms_mode = 0;
 
     int i = 1;
     if (argc > 1 && !std::strcmp(argv[1], "convert")) { mode = CONVERT; i = 2; }
@@ -88,6 +93,26 @@ int main(int argc, char** argv)
                 if (!end || *end) bad = true;
             }
         } else if (a == "--gpus" && mode != CONVERT) need(gpus);
+        else if (a == "--devices" && mode != CONVERT) {
+            if (i + 1 >= argc) bad = true;
+            else {
+                const char* p = argv[++i];
+                while (*p && !bad) {
+                    char* end = nullptr;
+                    const long v = std::strtol(p, &end, 10);
+                    if (end == p || v < 0 || v > 1023) bad = true;
+                    else devices.push_back(static_cast<int>(v));
+                    p = (*end == ',') ? end + 1 : end;
+                    if (*end && *end != ',') bad = true;
+                }
+                if (devices.empty()) bad = true;
+            }
+        } else if (a == "--norms" && mode != CONVERT) {
+            if (i + 1 >= argc) bad = true;
+            else if (!std::strcmp(argv[i + 1], "reference")) { norms_mode = 0; ++i; }
+            else if (!std::strcmp(argv[i + 1], "exact")) { norms_mode = 1; ++i; }
+            else bad = true;
+        }
         else if (a == "--quiet") quiet = true;
         else if (!a.empty() && a[0] == '-' && a.size() > 1) bad = true;      // unknown option
         else pos.push_back(a);
@@ -115,8 +140,9 @@ int main(int argc, char** argv)
         input = tmp_hash_file;
     }
 
-    std::vector<int> devices;
-    for (long long g = 0; g < gpus; ++g) devices.push_back(static_cast<int>(g));
+    if (devices.empty())
+        for (long long g = 0; g < gpus; ++g) devices.push_back(static_cast<int>(g));
+    mvs_set_norms_mode(norms_mode);
     // contexts are created while the hash file is parsed (CUDA start-up overlaps the parse)
     const int rc = mvs_sketch_file_on_devices(devices.data(), static_cast<int>(devices.size()), input.c_str(),
                                               output.c_str(), static_cast<int>(d), int16 ? 1 : 0, seed, quiet ? 0 : 1);

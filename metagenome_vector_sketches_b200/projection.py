@@ -94,22 +94,28 @@ class Sketcher:
                                            C.c_void_p(stream) if stream else None),
               "mvs_project_device", self._h)
 
-    def finalize_device(self, d_vec_ptr, n, d, d_sumsq_ptr, d_out16_ptr=None, stream=None):
+    def finalize_device(self, d_vec_ptr, n, d, d_sumsq_ptr, d_out16_ptr=None, stream=None, d_ref_norms_ptr=None):
         check(self._lib.mvs_finalize_device(self._h, C.c_void_p(d_vec_ptr), int(n), int(d),
-                                            C.c_void_p(d_sumsq_ptr),
+                                            C.c_void_p(d_sumsq_ptr) if d_sumsq_ptr else None,
                                             C.c_void_p(d_out16_ptr) if d_out16_ptr else None,
+                                            C.c_void_p(d_ref_norms_ptr) if d_ref_norms_ptr else None,
                                             C.c_void_p(stream) if stream else None),
               "mvs_finalize_device", self._h)
 
-    def finalize(self, vec, want_int16=False):
-        """(n, d) int32 host array -> (sumsq uint64[n], int16 copy or None)."""
+    def finalize(self, vec, want_int16=False, want_ref_norms=False):
+        """(n, d) int32 host array -> (sumsq uint64[n], int16 copy or None[, reference float32 norms])."""
         vec = np.ascontiguousarray(vec, dtype=np.int32)
         n, d = vec.shape
         sumsq = np.empty(n, dtype=np.uint64)
         out16 = np.empty((n, d), dtype=np.int16) if want_int16 else None
-        check(self._lib.mvs_finalize(self._h, _ptr(vec), n, d, _ptr(sumsq), _ptr(out16)),
+        ref = np.empty(n, dtype=np.float32) if want_ref_norms else None
+        check(self._lib.mvs_finalize(self._h, _ptr(vec), n, d, _ptr(sumsq), _ptr(out16), _ptr(ref)),
               "mvs_finalize", self._h)
-        return sumsq, out16
+        return (sumsq, out16, ref) if want_ref_norms else (sumsq, out16)
+
+    def sketch_csr(self, hashes, offsets, d, seed=0, int16=False):
+        """mvs_sketch_batch: projection + epilogue.  Returns dict(vec | vec16, sumsq, ref_norms)."""
+        return sketch_csr_multi([self], hashes, offsets, d, seed, int16)
 
     # ---- measurement ----------------------------------------------------------------
     def timing(self):
@@ -124,6 +130,35 @@ class Sketcher:
 
     def set_option(self, key, value):
         check(self._lib.mvs_set_option(self._h, key.encode(), int(value)), "mvs_set_option", self._h)
+
+
+def sketch_csr_multi(sketchers, hashes, offsets, d, seed=0, int16=False):
+    """mvs_sketch_batch_multi: ONE call over several contexts (one per GPU; they may also share a device).
+    Returns dict(vec | vec16, sumsq, ref_norms); rows are in input order."""
+    lib = load_library()
+    hashes = np.ascontiguousarray(hashes, dtype=np.uint64)
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+    n = len(offsets) - 1
+    vec = None if int16 else np.empty((n, d), dtype=np.int32)
+    vec16 = np.empty((n, d), dtype=np.int16) if int16 else None
+    sumsq = np.empty(n, dtype=np.uint64)
+    ref = np.empty(n, dtype=np.float32)
+    handles = (C.c_void_p * len(sketchers))(*[s._h for s in sketchers])
+    check(lib.mvs_sketch_batch_multi(handles, len(sketchers), _ptr(hashes), _ptr(offsets), n, int(d), C.c_uint64(seed),
+                                     _ptr(vec), _ptr(vec16), _ptr(sumsq), _ptr(ref)), "mvs_sketch_batch_multi",
+          sketchers[0]._h)
+    out = {"sumsq": sumsq, "ref_norms": ref}
+    out["vec16" if int16 else "vec"] = vec16 if int16 else vec
+    return out
+
+
+def reference_norms(vec):
+    """mvs_reference_norms: the reference's float32 norm of (n, d) int32 rows on the HOST (no GPU needed)."""
+    vec = np.ascontiguousarray(vec, dtype=np.int32)
+    n, d = vec.shape
+    out = np.empty(n, dtype=np.float32)
+    check(load_library().mvs_reference_norms(_ptr(vec), n, d, _ptr(out)), "mvs_reference_norms")
+    return out
 
 
 _default = {}

@@ -90,6 +90,58 @@ double oracle_norm_exact(const int32_t *v, int d)
     return sqrt((double)ss / (double)d);
 }
 
+/* The value the reference actually prints (project_everything.cpp:328-330), restated operation by
+ * operation from its compiled code (g++ 13, -O3 -ffast-math, vendored Eigen 3.2.10 = SSE packets of 4;
+ * the -march=native and x86-64-v3 builds agree):
+ *   inv = 1/sqrt(float(d)) as  r = rsqrtss(d);  inv = ((d*r)*r - 3 [one fma]) * (r * -0.5)
+ *   x_j = float(v_j) * inv
+ *   Eigen redux with two packet accumulators: acc0 = x[0..3]^2, acc1 = x[4..7]^2 (products), then
+ *   fma per following packet pair, acc0 += acc1, fma for an odd last packet, hadd (a0+a1)+(a2+a3),
+ *   scalar fma tail, sqrtss; d < 4: x0^2 then scalar fma.
+ * `inv` is an argument: rsqrtss is an approximation defined by the executing CPU, so the caller asks
+ * the CPU for it (oracle_inv_sqrt_d below). Compile with -ffp-contract=off: every rounding is explicit. */
+float oracle_norm_reference(const int32_t *v, int d, float inv)
+{
+    const int ps = 4;
+    const int aligned2 = (d / (2 * ps)) * (2 * ps), aligned = (d / ps) * ps;
+    float res;
+    if (aligned == 0) {
+        float x = (float)v[0] * inv;
+        res = x * x;
+        for (int j = 1; j < d; ++j) { x = (float)v[j] * inv; res = fmaf(x, x, res); }
+        return sqrtf(res);
+    }
+    float p0[4], p1[4];
+    for (int l = 0; l < ps; ++l) { float x = (float)v[l] * inv; p0[l] = x * x; }
+    if (aligned > ps) {
+        for (int l = 0; l < ps; ++l) { float x = (float)v[ps + l] * inv; p1[l] = x * x; }
+        for (int idx = 2 * ps; idx < aligned2; idx += 2 * ps)
+            for (int l = 0; l < ps; ++l) {
+                float x = (float)v[idx + l] * inv, y = (float)v[idx + ps + l] * inv;
+                p0[l] = fmaf(x, x, p0[l]);
+                p1[l] = fmaf(y, y, p1[l]);
+            }
+        for (int l = 0; l < ps; ++l) p0[l] = p0[l] + p1[l];
+        if (aligned > aligned2)
+            for (int l = 0; l < ps; ++l) { float x = (float)v[aligned2 + l] * inv; p0[l] = fmaf(x, x, p0[l]); }
+    }
+    res = (p0[0] + p0[1]) + (p0[2] + p0[3]);
+    for (int j = aligned; j < d; ++j) { float x = (float)v[j] * inv; res = fmaf(x, x, res); }
+    return sqrtf(res);
+}
+
+#if defined(__x86_64__)
+#include <xmmintrin.h>
+float oracle_inv_sqrt_d(int d)
+{
+    const float x = (float)d;
+    const float r = _mm_cvtss_f32(_mm_rsqrt_ss(_mm_set_ss(x)));
+    return fmaf(x * r, r, -3.0f) * (r * -0.5f);
+}
+#else
+float oracle_inv_sqrt_d(int d) { return 1.0f / sqrtf((float)d); }
+#endif
+
 uint64_t oracle_sumsq(const int32_t *v, int d)
 {
     uint64_t ss = 0;

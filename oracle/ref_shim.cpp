@@ -56,3 +56,18 @@ extern "C" void ref_project_csr(const uint64_t* hashes, const uint64_t* offsets,
     auto t1 = std::chrono::steady_clock::now();
     if (seconds_kernel) *seconds_kernel = std::chrono::duration<double>(t1 - t0).count();
 }
+
+// The norm column of vector_norms.txt: the two statements of
+// /root/reference/src/project_everything.cpp:328-329 on an arbitrary int32 row, compiled with the
+// reference's Eigen and flags.  (They live inside sketch(), which only the binary can execute; the
+// binary's own files are the primary pin, this is the per-row live check for any d and any values.)
+#include <cmath>
+extern "C" void ref_norms(const int32_t* vec, int64_t n, int d, double* out)
+{
+    for (int64_t s = 0; s < n; ++s) {
+        VectorXi v = Eigen::Map<const VectorXi>(vec + static_cast<size_t>(s) * static_cast<size_t>(d), d);
+        Eigen::VectorXf vec_f = v.cast<float>() / std::sqrt(static_cast<float>(d));
+        double norm = vec_f.norm();
+        out[s] = norm;
+    }
+}

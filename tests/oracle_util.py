@@ -31,6 +31,10 @@ def oracle():
         lib.oracle_sumsq.restype = C.c_uint64
         lib.oracle_splitmix64.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64]
         lib.oracle_splitmix64.restype = C.c_uint64
+        lib.oracle_norm_reference.argtypes = [C.c_void_p, C.c_int, C.c_float]
+        lib.oracle_norm_reference.restype = C.c_float
+        lib.oracle_inv_sqrt_d.argtypes = [C.c_int]
+        lib.oracle_inv_sqrt_d.restype = C.c_float
         _oracle = lib
     return _oracle
 
@@ -61,6 +65,7 @@ def ref_lib():
         lib.ref_transform_set.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_void_p]
         lib.ref_project_csr.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p,
                                         C.POINTER(C.c_double)]
+        lib.ref_norms.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_void_p]
         _ref = lib
     return _ref
 
@@ -197,3 +202,72 @@ def norms_sq_like_reference(vectors, d):
     v = np.asarray(vectors, dtype=np.float64)
     norm = np.sqrt((v * v).sum(axis=1) / float(d))
     return np.array([float("%g" % x) ** 2 for x in norm], dtype=np.float64)
+
+
+# ---- the norm column of vector_norms.txt (reference src/project_everything.cpp:328-330) ----
+def oracle_reference_norms(vectors, inv=None):
+    """float32 norms of (n, d) int32 rows by oracle_norm_reference; inv defaults to this host's rsqrtss value."""
+    v = np.ascontiguousarray(vectors, dtype=np.int32)
+    n, d = v.shape
+    lib = oracle()
+    if inv is None:
+        inv = lib.oracle_inv_sqrt_d(d)
+    return np.array([lib.oracle_norm_reference(v[i].ctypes.data, d, C.c_float(inv)) for i in range(n)], dtype=np.float32)
+
+
+def ref_norms_live(vectors):
+    """The reference's two statements compiled with its own Eigen and flags (oracle/ref_shim.cpp), float32 widened."""
+    v = np.ascontiguousarray(vectors, dtype=np.int32)
+    n, d = v.shape
+    out = np.empty(n, dtype=np.float64)
+    ref_lib().ref_norms(v.ctypes.data, n, d, out.ctypes.data)
+    return out
+
+
+def load_norms_golden():
+    z = np.load(os.path.join(GOLDEN, "norms_ref.npz"))
+    return {k: z[k] for k in z.files}
+
+
+def golden_host_has_same_rsqrt(d, golden=None):
+    """rsqrtss is an approximation whose table is the CPU's: the committed norm TEXT fixtures were printed on the
+    build container's CPU and only bind hosts whose 1/sqrt(d) factor has the same bits."""
+    g = golden or load_norms_golden()
+    key = "inv_%d" % d
+    if key not in g:
+        return False
+    mine = np.array([oracle().oracle_inv_sqrt_d(d)], np.float32).view(np.uint32)[0]
+    return int(mine) == int(g[key][0])
+
+
+def norms_text(names, norms_f32):
+    """vector_norms.txt as sketch() prints it: default ostream formatting of the float norm widened to double."""
+    return "".join("%s %s\n" % (nm, "%g" % float(np.float64(x))) for nm, x in zip(names, norms_f32))
+
+
+def write_family_hash_file(path, n, seed=1, mean_size=200, family=10):
+    """A hash file whose samples come in families sharing most of their hashes (so that the all-pairs
+    comparison keeps several neighbours per row), sizes ragged, one empty and one tiny sample included.
+    Returns (names, offsets, hashes) with hashes sorted + unique per sample."""
+    rng = np.random.default_rng(seed)
+    names, sets = [], []
+    base = None
+    for i in range(n):
+        if i % family == 0:
+            size = max(8, int(rng.lognormal(np.log(mean_size), 0.6)))
+            base = rng.integers(0, 2 ** 54, size=size, dtype=np.uint64)
+        keep = base[rng.random(len(base)) < rng.uniform(0.55, 0.95)]
+        extra = rng.integers(0, 2 ** 54, size=int(len(base) * rng.uniform(0.02, 0.3)), dtype=np.uint64)
+        s = np.unique(np.concatenate([keep, extra]))
+        if i == 7:
+            s = s[:0]
+        if i == 8:
+            s = s[:3]
+        names.append("fam%05d" % i)
+        sets.append(s)
+    with open(path, "w") as f:
+        for nm, s in zip(names, sets):
+            f.write(nm + ":" + "".join(" %d" % int(h) for h in s) + "\n")
+    offsets = np.zeros(n + 1, dtype=np.uint64)
+    offsets[1:] = np.cumsum([len(s) for s in sets])
+    return names, offsets, (np.concatenate(sets) if sets else np.zeros(0, np.uint64))

@@ -10,7 +10,8 @@ import pytest
 
 import metagenome_vector_sketches_b200 as mvs
 from metagenome_vector_sketches_b200 import _lib
-from oracle_util import load_kat, load_toy, load_toy_ref, parse_line_like_reference, oracle_set
+from oracle_util import (load_kat, load_toy, load_toy_ref, parse_line_like_reference, oracle_set, ref_dir,
+                         golden_host_has_same_rsqrt, oracle_reference_norms, write_family_hash_file)
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "metagenome_vector_sketches_b200", "bin")
@@ -121,38 +122,78 @@ def test_parser_toy_roundtrip(tmp_path):
 
 
 @pytest.mark.parametrize("tag,i16", [("d2048", False), ("d2048_i16", True), ("d100", False)])
-def test_write_db_matches_reference_files(tmp_path, tag, i16):
+@pytest.mark.parametrize("norms_from", ["ref_norms", "vec32"])
+def test_write_db_matches_reference_files(tmp_path, tag, i16, norms_from):
+    """All four db files byte-identical to the reference binary's (golden: toy, 61 samples)."""
     lib = mvs.load_library()
     names, _, _ = load_toy()
     ref = load_toy_ref(tag)
     vec = ref["vectors"]
     n, d = vec.shape
-    v32 = vec.astype(np.int32)
-    sumsq = (v32.astype(np.int64) ** 2).sum(axis=1).astype(np.uint64)
+    if not golden_host_has_same_rsqrt(d):
+        pytest.skip("this CPU's rsqrtss differs from the host that printed the golden norms")
+    v32 = load_toy_ref("d2048")["vectors"].astype(np.int32) if i16 else vec.astype(np.int32)   # norms come from the int32 rows (:328)
     arr = (C.c_char_p * n)(*[s.encode() for s in names])
     v16 = np.ascontiguousarray(vec.astype(np.int16)) if i16 else None
     out = tmp_path / "db"
     out.mkdir()
-    rc = lib.mvs_write_db(str(out).encode(), n, d, arr, sumsq.ctypes.data,
+    if norms_from == "vec32" and i16:
+        pytest.skip("the writer derives norms itself only from int32 rows")
+    rn = mvs.reference_norms(v32) if norms_from == "ref_norms" else None
+    rc = lib.mvs_write_db(str(out).encode(), n, d, arr, rn.ctypes.data if rn is not None else None, None,
                           None if i16 else v32.ctypes.data, v16.ctypes.data if i16 else None)
     assert rc == 0
     raw = (out / "vectors.bin").read_bytes()
     assert hashlib.sha256(raw).hexdigest() == ref["vectors_sha256"]          # byte-identical vectors.bin
     assert (out / "dimension.txt").read_text() == ref["dimension_txt"]
     assert (out / "dtype.txt").read_text() == ref["dtype_txt"]
-    mine = (out / "vector_norms.txt").read_text().split("\n")[:-1]
-    theirs = ref["norms_txt"].split("\n")[:-1]
-    assert len(mine) == len(theirs) == n
-    same = 0
-    for a, b in zip(mine, theirs):
-        na, va = a.rsplit(" ", 1)
-        nb, vb = b.rsplit(" ", 1)
-        assert na == nb
+    assert (out / "vector_norms.txt").read_text() == ref["norms_txt"]        # 61/61 lines, byte for byte
+
+
+def test_write_db_exact_norms_mode_within_print_precision(tmp_path):
+    """The caller's other choice: sqrt(exact sum of squares / d).  Tolerance parity only (half a unit of the
+    6th digit + 2e-6 relative for the reference's float32 evaluation)."""
+    lib = mvs.load_library()
+    names, _, _ = load_toy()
+    ref = load_toy_ref("d2048")
+    v32 = ref["vectors"].astype(np.int32)
+    n, d = v32.shape
+    sumsq = (v32.astype(np.int64) ** 2).sum(axis=1).astype(np.uint64)
+    arr = (C.c_char_p * n)(*[s.encode() for s in names])
+    out = tmp_path / "db"
+    out.mkdir()
+    assert lib.mvs_write_db(str(out).encode(), n, d, arr, None, sumsq.ctypes.data, v32.ctypes.data, None) == 0
+    for a, b in zip((out / "vector_norms.txt").read_text().split("\n")[:-1], ref["norms_txt"].split("\n")[:-1]):
+        (na, va), (nb, vb) = a.rsplit(" ", 1), b.rsplit(" ", 1)
         exact = float(va)
         ulp6 = 10.0 ** (np.floor(np.log10(exact)) - 5) if exact > 0 else 0.0
-        assert abs(float(vb) - exact) <= 1.0 * ulp6 + 2e-6 * exact             # stated tolerance
-        same += a == b
-    assert same >= 0.8 * n                                                       # most lines are textually identical
+        assert na == nb and abs(float(vb) - exact) <= 1.0 * ulp6 + 2e-6 * exact
+
+
+def test_norms_file_identical_to_live_reference_binary_10k(tmp_path):
+    """>= 10 000 samples: the reference binary sketches a family hash file on THIS host; our writer, fed with the
+    binary's own vectors.bin, must print the same vector_norms.txt byte for byte (project_everything.cpp:328-330)."""
+    rd = ref_dir()
+    if rd is None:
+        pytest.skip("oracle/_ref not built on this host")
+    lib = mvs.load_library()
+    hf = tmp_path / "fam.txt"
+    names, offsets, hashes = write_family_hash_file(str(hf), 10000, seed=3, mean_size=120)
+    db = tmp_path / "db_ref"
+    r = subprocess.run([os.path.join(rd, "project_everything"), "sketch", str(hf), str(db), "-d", "1000"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    d = 1000
+    v32 = np.fromfile(db / "vectors.bin", dtype=np.int32).reshape(-1, d)
+    assert len(v32) == 10000
+    out = tmp_path / "db_ours"
+    out.mkdir()
+    arr = (C.c_char_p * len(names))(*[s.encode() for s in names])
+    assert lib.mvs_write_db(str(out).encode(), len(names), d, arr, None, None, v32.ctypes.data, None) == 0
+    for f in ("vector_norms.txt", "vectors.bin", "dimension.txt", "dtype.txt"):
+        assert (out / f).read_bytes() == (db / f).read_bytes(), f
+    # the oracle's restatement agrees on every row as well
+    assert np.array_equal(oracle_reference_norms(v32[:500]).view(np.uint32), mvs.reference_norms(v32[:500]).view(np.uint32))
 
 
 def test_convert_reads_toy_signatures(tmp_path):

@@ -8,7 +8,8 @@ import pytest
 
 import metagenome_vector_sketches_b200 as mvs
 from oracle_util import (oracle, oracle_set, oracle_csr, ref_lib, ref_set, load_toy, load_toy_ref, load_kat,
-                         parse_line_like_reference)
+                         parse_line_like_reference, oracle_reference_norms, ref_norms_live, load_norms_golden,
+                         golden_host_has_same_rsqrt, norms_text)
 
 pytestmark = pytest.mark.gpu
 
@@ -40,24 +41,106 @@ def test_toy_golden_bit_exact(sk, tag, d):
 
 
 def test_toy_epilogue_int16_and_norms(sk):
+    """Fused epilogue (finalize_kernel): int16 copy and exact sum of squares against the oracle, and the
+    reference-order float32 norm against the oracle bit for bit and against the reference binary's own
+    vector_norms.txt byte for byte (61/61 lines)."""
     names, offsets, hashes = load_toy()
     ref16 = load_toy_ref("d2048_i16")
     got = sk.project_csr(hashes, offsets, 2048)
-    sumsq, out16 = sk.finalize(got, want_int16=True)
+    sumsq, out16, rn = sk.finalize(got, want_int16=True, want_ref_norms=True)
     assert np.array_equal(out16, ref16["vectors"])
     assert hashlib.sha256(out16.tobytes()).hexdigest() == ref16["vectors_sha256"]
-    for row, ss, line in zip(got, sumsq, ref16["norms_txt"].split("\n")[:-1]):
+    for row, ss in zip(got, sumsq):
         assert int(ss) == int(oracle().oracle_sumsq(row.ctypes.data, 2048))
+    assert np.array_equal(rn.view(np.uint32), oracle_reference_norms(got).view(np.uint32))
+    if golden_host_has_same_rsqrt(2048):
+        assert norms_text(names, rn) == ref16["norms_txt"]
+    # the caller's other choice, sqrt(exact sum / d): tolerance parity only (print precision + float32 evaluation)
+    for ss, line in zip(sumsq, ref16["norms_txt"].split("\n")[:-1]):
         printed = float(line.rsplit(" ", 1)[1])
         exact = mvs.norm_from_sumsq(ss, 2048)
         ulp6 = 10.0 ** (np.floor(np.log10(exact)) - 5) if exact > 0 else 0.0
-        assert abs(printed - exact) <= 0.5 * ulp6 + 2e-6 * exact     # stated tolerance: print precision + f32
+        assert abs(printed - exact) <= 0.5 * ulp6 + 2e-6 * exact
+
+
+def test_reference_norms_on_device_all_packet_cases(sk):
+    """finalize_kernel's float32 norm against the committed rows the reference's own expression was run on
+    (every Eigen packet-count case, magnitudes to 2^30), the oracle and -- when built -- the live reference."""
+    g = load_norms_golden()
+    for d in sorted(int(k[5:]) for k in g if k.startswith("rows_")):
+        rows = g["rows_%d" % d]
+        _, _, rn = sk.finalize(rows, want_ref_norms=True)
+        assert np.array_equal(rn.view(np.uint32), oracle_reference_norms(rows).view(np.uint32)), d
+        assert np.array_equal(rn.view(np.uint32), mvs.reference_norms(rows).view(np.uint32)), d      # host twin
+        if golden_host_has_same_rsqrt(d, g):
+            assert np.array_equal(rn.view(np.uint32), g["norms_%d" % d].view(np.uint32)), d
+        if ref_lib() is not None:
+            assert np.array_equal(rn.astype(np.float64), ref_norms_live(rows)), d
+
+
+def test_sketch_batch_epilogue_outputs_and_saturated_norms(sk):
+    """mvs_sketch_batch: vectors, int16 copy, exact sum and reference norm in one call.  In --int16 mode the norm
+    still comes from the int32 values (reference :328 runs before the saturation :332-347): a sample whose
+    columns exceed 32767 shows it."""
+    # hashes whose column-0 entry is +1 (bit 0 of the mixer output clear): v[0] = |H| = ~40 000 > 32767
+    rng = np.random.default_rng(5)
+    cand = np.unique(rng.integers(0, 2 ** 63, 80_000, dtype=np.uint64))
+    big = cand[[(oracle().oracle_splitmix64(int(h), 0, 0) & 1) == 0 for h in cand]]
+    assert len(big) > 36000
+    small = np.unique(rng.integers(0, 2 ** 63, 700, dtype=np.uint64))
+    offsets = np.array([0, len(big), len(big), len(big) + len(small)], dtype=np.uint64)
+    hashes = np.concatenate([big, small])
+    for d in (64, 100):
+        want = oracle_csr(hashes, offsets, d)
+        r32 = sk.sketch_csr(hashes, offsets, d)
+        r16 = sk.sketch_csr(hashes, offsets, d, int16=True)
+        assert np.array_equal(r32["vec"], want) and want[0, 0] == len(big)
+        assert np.array_equal(r16["vec16"], np.clip(want, -32768, 32767).astype(np.int16)) and r16["vec16"][0, 0] == 32767
+        for r in (r32, r16):
+            assert np.array_equal(r["sumsq"], (want.astype(np.int64) ** 2).sum(axis=1).astype(np.uint64))
+            assert np.array_equal(r["ref_norms"].view(np.uint32), oracle_reference_norms(want).view(np.uint32))
+        assert r32["ref_norms"][1] == 0.0                                 # empty sample: zero vector, norm 0
+
+
+def test_sketch_batch_multi_two_contexts_on_one_device(sk):
+    """The multi-GPU call of the C ABI (mvs_sketch_batch_multi) where the 1-GPU test box can see it: two and three
+    contexts on device 0 -- heavy-tailed sizes, empty samples, a sample larger than a whole shard, more contexts
+    than samples -- bit-exact against the oracle and identical to the single-context call."""
+    extra = [mvs.Sketcher(0), mvs.Sketcher(0)]
+    try:
+        sizes = [int(x) for x in mvs.synthetic.lognormal_sizes(160, seed=11, median=2000, lo=1, hi=20000)]
+        sizes[3] = 0
+        sizes[4] = 0
+        sizes[50] = 400_000                                               # larger than a whole mean shard of the 3-context split
+        sizes[159] = 0
+        h, off = mvs.synthetic.ragged_batch(sizes, seed=4)
+        for d in (2048, 300):
+            want = oracle_csr(h, off, d)
+            one = sk.sketch_csr(h, off, d)
+            assert np.array_equal(one["vec"], want)
+            for ctxs in ([sk, extra[0]], [sk, extra[0], extra[1]]):
+                got = mvs.sketch_csr_multi(ctxs, h, off, d)
+                assert np.array_equal(got["vec"], want)
+                assert np.array_equal(got["sumsq"], one["sumsq"])
+                assert np.array_equal(got["ref_norms"].view(np.uint32), one["ref_norms"].view(np.uint32))
+            got16 = mvs.sketch_csr_multi([sk, extra[0]], h, off, d, int16=True)
+            assert np.array_equal(got16["vec16"], np.clip(want, -32768, 32767).astype(np.int16))
+        # more contexts than samples; an all-empty batch
+        h2, off2 = mvs.synthetic.ragged_batch([5, 0], seed=2)
+        got = mvs.sketch_csr_multi([sk] + extra, h2, off2, 128)
+        assert np.array_equal(got["vec"], oracle_csr(h2, off2, 128))
+        z = mvs.sketch_csr_multi([sk, extra[0]], np.zeros(0, np.uint64), np.zeros(4, np.uint64), 64)
+        assert not z["vec"].any() and z["vec"].shape == (3, 64)
+    finally:
+        for e in extra:
+            e.close()
 
 
 def test_int16_saturation_edges(sk):
     v = np.array([[40000, -40000, 32767, -32768, 32768, -32769, 0, 1]], dtype=np.int32)
-    sumsq, o16 = sk.finalize(v, want_int16=True)
+    sumsq, o16, rn = sk.finalize(v, want_int16=True, want_ref_norms=True)
     assert o16.tolist() == [[32767, -32768, 32767, -32768, 32767, -32768, 0, 1]]
+    assert np.array_equal(rn.view(np.uint32), oracle_reference_norms(v).view(np.uint32))   # from the unsaturated values
     assert int(sumsq[0]) == int((v.astype(np.int64) ** 2).sum())
 
 

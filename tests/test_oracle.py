@@ -8,7 +8,8 @@ import numpy as np
 import pytest
 
 from oracle_util import (oracle, oracle_set, oracle_csr, ref_lib, ref_set, load_toy, load_toy_ref, load_kat,
-                         parse_line_like_reference)
+                         parse_line_like_reference, oracle_reference_norms, ref_norms_live, load_norms_golden,
+                         golden_host_has_same_rsqrt, norms_text)
 
 
 def test_splitmix_kat1():
@@ -67,6 +68,47 @@ def test_toy_norms_within_print_precision():
         # half a unit of the 6th significant digit + 2e-6 relative for the float32 evaluation
         ulp6 = 10.0 ** (np.floor(np.log10(exact)) - 5) if exact > 0 else 0.0
         assert abs(printed - exact) <= 0.5 * ulp6 + 2e-6 * exact
+
+
+def test_reference_norm_restatement_matches_golden_rows():
+    """oracle_norm_reference against norms the reference's own expression produced (tests/golden/
+    make_golden_norms.py), bit for bit, with the generating host's 1/sqrt(d) factor: every packet-count
+    case of the Eigen reduction (d < 4, one packet, odd / even packet counts, scalar tails) and magnitudes
+    up to 2^30."""
+    g = load_norms_golden()
+    dims = sorted(int(k[5:]) for k in g if k.startswith("rows_"))
+    assert dims[0] == 1 and 2048 in dims and len(dims) >= 15
+    for d in dims:
+        inv = g["inv_%d" % d].view(np.float32)[0]
+        got = oracle_reference_norms(g["rows_%d" % d], inv)
+        assert np.array_equal(got.view(np.uint32), g["norms_%d" % d].view(np.uint32)), d
+
+
+def test_reference_norm_restatement_prints_the_reference_binary_file():
+    """vectors.bin + vector_norms.txt written by the reference BINARY (sketch(), 300-sample family file):
+    the oracle's norm, printed like an ostream prints a double, reproduces the file byte for byte."""
+    g = load_norms_golden()
+    vec = g["family_vectors"].astype(np.int32)
+    inv = g["inv_2048"].view(np.float32)[0]
+    names = ["fam%05d" % i for i in range(len(vec))]
+    assert norms_text(names, oracle_reference_norms(vec, inv)) == str(g["family_norms_txt"])
+    # and the toy db of SURVEY KAT-3 (61/61 lines), the file the round-1 verdict found one digit off
+    names, _, _ = load_toy()
+    for tag, d in (("d2048", 2048), ("d100", 100)):
+        ref = load_toy_ref(tag)
+        inv = g["inv_%d" % d].view(np.float32)[0]
+        assert norms_text(names, oracle_reference_norms(ref["vectors"].astype(np.int32), inv)) == ref["norms_txt"]
+
+
+def test_reference_norm_restatement_matches_live_reference():
+    if ref_lib() is None:
+        pytest.skip("oracle/_ref not built on this host")
+    rng = np.random.default_rng(77)
+    for d in (1, 3, 4, 6, 8, 10, 12, 15, 16, 17, 100, 257, 2048, 2051):
+        for scale in (1, 50, 5000, 2 ** 24):
+            v = rng.integers(-scale, scale + 1, size=(25, d)).astype(np.int32)
+            live = ref_norms_live(v)
+            assert np.array_equal(oracle_reference_norms(v).astype(np.float64), live), (d, scale)
 
 
 def test_int16_golden_matches_saturation():
