@@ -10,9 +10,16 @@ no data-path collective).
          launching stream, barrier + synchronize on both sides, max over ranks.
   e2e    the same batch through mvs_project_batch with PINNED HOST buffers: H2D of the
          hashes, kernels and D2H of the vectors all inside the timed region.
-  roofline     integer-issue roofline of the projection kernel: algorithmic
-         W(d) = d + 20*ceil(d/64) int32 ops per hash against the live-measured issue peak;
+  roofline     issue-slot roofline of the projection kernel: warp instructions the
+         kernel issues per launch (from the committed ncu capture of the SAME cubin, profiles/
+         project_kernel_profile.json, keyed by tools/cubin_key.py) / live kernel time, against the SM sub-partitions'
+         issue slots (1 warp instruction per clock each) -- a fraction that cannot exceed 1.  The algorithmic view
+         (W(d) = d + 20*ceil(d/64) int32 ops per hash against the live LOP3+IMAD issue peak) is `frac_algorithmic`,
          the HBM view (8 B/hash in, 4d B/sample out) is reported beside it.
+  config3      BASELINE configs[2]: dimension sweep d in {256..4096} on 1024 x 100 000 hashes (N = 1 only).
+  config4      BASELINE configs[3]: heavy-tailed batch (100 000 samples, log-normal 1e3..1e7, d = 2048) STRONG-scaled
+         over the N ranks with the library's own mvs_partition_samples; per-rank ms, imbalance, reduce time, a parity
+         property on every row and an in-process cross-check through mvs_sketch_batch_multi.
   cpu_baseline the reference's own transform_set_into_vector (oracle/_ref, compiled from
          /root/reference) under OpenMP on the host cores, on a bounded prefix of the batch.
 
@@ -37,10 +44,26 @@ UNIT = "hashes/s"
 WORKLOAD = "configs[1]: synthetic 10k samples x 50k hashes, d=2048, seed 0"
 
 
-# dram__bytes_read.sum (4.005037 GB) + dram__bytes_write.sum (317.1 MB) of one project_kernel launch of the default
-# workload, profiles/r01j_project_kernel_ncu_full.txt; algorithmic bytes are 4.08 GB, the rest are the partial rows
-# of samples split over 4 warp tasks (written once, read once by reduce_partials_kernel)
-NCU_TRAFFIC_BYTES = 4005037000 + 317129984
+PROFILE_JSON = os.path.join(ROOT, "profiles", "project_kernel_profile.json")
+
+
+def load_kernel_profile(n, per, d):
+    """The committed ncu capture of the dominant kernel (tools/ncu_summary.py --json) if -- and only if -- it was
+    taken on the cubin that is loaded now and on this workload.  Returns (profile or None, why)."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    try:
+        from cubin_key import projection_cubin_key
+        prof = json.load(open(PROFILE_JSON))
+    except Exception as e:
+        return None, "no profile (%s)" % repr(e)[:80]
+    key = projection_cubin_key()
+    if key is None:
+        return None, "cubin key unavailable (cuobjdump missing)"
+    if key != prof.get("cubin_sha256"):
+        return None, "stale: profile is of cubin %s..., library is %s..." % (str(prof.get("cubin_sha256"))[:12], key[:12])
+    if prof.get("workload") != "%dx%dx%d" % (n, per, d):
+        return None, "profile is of workload %s" % prof.get("workload")
+    return prof, "cubin %s..., %s" % (key[:12], prof.get("source"))
 
 
 def work_per_hash(d):
@@ -299,7 +322,108 @@ def run_gpu(args):
         if int(pg_out.sum(dtype=np.int64)) != checksum_dev:
             raise SystemExit("bench: pageable host path disagrees with the device-resident path")
         del pg_in, pg_out
+
+    # ---- BASELINE configs[2]: dimension sweep (N = 1 only; device-resident, same timing rules as `value`) ----
+    config3 = None
+    if world == 1 and not args.no_config3:
+        config3 = run_config3(sk, torch, syn, dev)
+    # ---- BASELINE configs[3]: heavy-tailed batch, strong-scaled over the ranks ----
+    config4 = None
+    if args.c4_samples > 0:
+        del hh, hout, h_np, out_np
+        config4 = run_config4(sk, mvs, torch, dist if world > 1 else None, syn, dev, rank, world, local, args.c4_samples,
+                              barrier)
     return locals()
+
+
+def run_config3(sk, torch, syn, dev, ns=1024, per=100000):
+    dh, off = syn.uniform_batch_torch(ns, per, dev, seed=0)
+    stream = torch.cuda.current_stream().cuda_stream
+    rows = []
+    for d in (256, 512, 1024, 2048, 4096):
+        dout = torch.empty((ns, d), dtype=torch.int32, device=dev)
+        for _ in range(3):
+            sk.project_device(dh.data_ptr(), off, d, dout.data_ptr(), stream=stream)
+        torch.cuda.synchronize()
+        sk.timing()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            sk.project_device(dh.data_ptr(), off, d, dout.data_ptr(), stream=stream)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 5
+        t = sk.timing()
+        hps = ns * per / (ms * 1e-3)
+        # size-independent property: every column of a row has the parity of |H_s|
+        ok = bool(((dout & 1) == (per & 1)).all().item())
+        rows.append({"d": d, "ms_per_step": ms, "kernel_ms": t["kernel_ms"], "hashes_per_s": hps, "entries_per_s": hps * d,
+                     "warp_tasks": int(t["warp_tasks"]), "parity_property_ok": ok})
+        del dout
+    del dh
+    torch.cuda.empty_cache()
+    return {"workload": "configs[2]: d in {256,512,1024,2048,4096}, %d samples x %d hashes, 1 B200, device-resident "
+                        "(0.82 GB of hashes per step > L2)" % (ns, per), "steps": 5, "warmup": 3, "rows": rows}
+
+
+def run_config4(sk, mvs, torch, dist, syn, dev, rank, world, local, samples, barrier, d=2048, steps=3):
+    from metagenome_vector_sketches_b200 import sharding
+    sizes = syn.lognormal_sizes(samples, seed=0)                    # every rank computes the same sizes
+    offsets = np.zeros(samples + 1, dtype=np.uint64)
+    offsets[1:] = np.cumsum(sizes).astype(np.uint64)
+    bounds = sharding.partition_bounds(offsets, world)              # the library's own mvs_partition_samples
+    a, e = int(bounds[rank]), int(bounds[rank + 1])
+    dh, off = syn.ragged_batch_torch(sizes[a:e], dev, seed=0, first_sample=a)
+    mine = int(off[-1])
+    dout = torch.empty((e - a, d), dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    sk.project_device(dh.data_ptr(), off, d, dout.data_ptr(), stream=stream)
+    torch.cuda.synchronize()
+    sk.timing()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        sk.project_device(dh.data_ptr(), off, d, dout.data_ptr(), stream=stream)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1) / steps
+    tm = sk.timing()
+    # size-independent property on every row of the shard: each column has the parity of |H_s|
+    ok = bool(((dout[:, :8] & 1).to(torch.int64).cpu().numpy() == (sizes[a:e, None] & 1)).all())
+    # in-process cross-check of the torchrun sharding against the library's one-call multi-context path: a prefix of
+    # this rank's shard (<= 2e7 hashes) through mvs_sketch_batch_multi on two contexts of this rank's device
+    k = int(np.searchsorted(off, np.uint64(20_000_000), side="right")) - 1
+    xok = None
+    if k >= 1:
+        h_host = dh[: int(off[k])].cpu().numpy().view(np.uint64)
+        sk2 = mvs.Sketcher(local)
+        try:
+            got = mvs.sketch_csr_multi([sk, sk2], h_host, off[: k + 1], d)
+        finally:
+            sk2.close()
+        xok = bool(np.array_equal(got["vec"], dout[:k].cpu().numpy()))
+    t = torch.tensor([ms, float(mine), float(e - a), 1.0 if ok else 0.0, -1.0 if xok is None else float(xok),
+                      float(tm["reduce_ms"]), float(tm["kernel_ms"]), float(tm["partial_rows"])], dtype=torch.float64, device=dev)
+    allt = [t.clone() for _ in range(world)]
+    if dist is not None:
+        dist.all_gather(allt, t)
+    per = [[float(x[0]), int(x[1]), int(x[2])] for x in allt]
+    step = max(p[0] for p in per)
+    total = int(offsets[-1])
+    del dh, dout
+    torch.cuda.empty_cache()
+    return {"workload": "configs[3]: heavy-tailed synthetic, %d samples, log-normal sizes 1e3..1e7 hashes, d=%d, seed 0, "
+                        "device-resident, sharded by mvs_partition_samples" % (samples, d),
+            "scaling": "strong", "n_gpus": world, "steps": steps, "warmup": 1, "total_hashes": total,
+            "ms_per_step": step, "hashes_per_s": total / (step * 1e-3), "samples_per_s": samples / (step * 1e-3),
+            "per_rank_ms_hashes_samples": per,
+            "hash_imbalance_max_over_mean": max(p[1] for p in per) / (total / world),
+            "reduce_ms_max": max(float(x[5]) for x in allt), "kernel_ms_max": max(float(x[6]) for x in allt),
+            "partial_rows": int(sum(float(x[7]) for x in allt)),
+            "parity_property_ok": all(bool(x[3]) for x in allt),
+            "multi_context_crosscheck_ok": (None if any(float(x[4]) < 0 for x in allt) else all(bool(x[4]) for x in allt)),
+            "collective": "none on the data path (NCCL only for the timing barrier / gathering these numbers)"}
 
 
 def measured_peaks():
@@ -346,6 +470,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--wc-input", action="store_true", help="experiment: write-combined pinned input buffer")
     ap.add_argument("--no-bind", action="store_true", help="skip mvs_bind_host_to_device (A/B of the host locality)")
+    ap.add_argument("--no-config3", action="store_true", help="skip the BASELINE configs[2] dimension sweep (N = 1 leg)")
+    ap.add_argument("--c4-samples", type=int, default=100000,
+                    help="samples of the BASELINE configs[3] heavy-tailed leg (0 = skip; 100000 = the full config)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
@@ -364,39 +491,52 @@ def main():
     achieved_ops = total * w / k_s
     hbm_peak, hbm_how = measured_peaks()
     alg_bytes = total * 8 + n * d * 4
-    # Issued-instruction view, the one that cannot exceed 1: per (hash, 32 blocks) round a warp issues
-    # ALU_EQUIV instructions that need an ALU-pipe slot: 12.9 on the ALU pipe itself (8.6 LOP3, 3.2 SHF, 1.1 other:
-    # per-opcode counts of profiles/r01j_project_kernel_ncu_full.txt) + 2 IMAD.WIDE, which displace one ALU slot
-    # each (profiles/r01b_kexp_issue_mix_and_variants.txt); the 16-lane ALU pipe takes one warp instruction every
-    # 2 clocks (= the live LOP3 peak below).
-    nb = (d + 63) // 64
-    lph = 32 if nb >= 32 else 1 << max(0, (nb - 1).bit_length())
-    rounds = total * ((nb + 31) // 32) / (32 // lph)             # warp rounds of one launch
-    ALU_EQUIV = 14.9
-    alu_lane_ops = rounds * ALU_EQUIV * 32.0 / k_s
-    alu_view = {"bound": "alu-pipe issue", "unit": "Tlane-op/s", "achieved": alu_lane_ops / 1e12,
-                "peak": peaks["lop3"] / 1e12, "frac": alu_lane_ops / peaks["lop3"],
-                "alu_equiv_warp_instr_per_round": ALU_EQUIV,
-                "how": "ALU-slot instructions of the inner loop (static SASS count) x rounds / kernel time, against the "
-                       "live LOP3-only issue peak; ncu (profiles/r01j_project_kernel_ncu_full.txt): pipe_alu 74.4 % + "
-                       "IMAD.WIDE slots, fmaheavy 70.9 %, xu 23.7 %, issue 74.5 %"}
-    # DRAM bytes of one project_kernel launch from the committed ncu --set full capture of THIS workload
-    # (profiles/r01j_project_kernel_ncu_full.txt: dram__bytes_read.sum + dram__bytes_write.sum); other shapes: null
-    traffic = NCU_TRAFFIC_BYTES if (n, per, d) == (10000, 50000, 2048) else None
+    # Issue-slot view, the one that cannot exceed 1.  A B200 SM has 4 sub-partitions that each issue at most one warp
+    # instruction per clock: peak = 4 x SMs x clock.  The warp instructions of one launch come from the committed ncu
+    # capture of THIS cubin on THIS workload (smsp__inst_executed.sum, a property of code + input, not of timing);
+    # a capture of another cubin is refused (frac = null) rather than silently reused.
+    prof, prof_why = load_kernel_profile(n, per, d)
+    clk_mhz = g["clk"].get("sm_mhz") or 1965.0
+    sm_count = g["torch"].cuda.get_device_properties(g["local"]).multi_processor_count
+    slots_per_s = 4.0 * sm_count * clk_mhz * 1e6
+    if prof is not None:
+        inst_per_s = prof["inst_executed"] / k_s
+        scale = (prof["duration_ms_under_ncu"] * prof["sm_clock_ghz"] * 1e3) / (g["kernel_ms"] * clk_mhz)   # cycles under ncu / cycles now
+        issue = {"achieved": inst_per_s / 1e9, "frac": inst_per_s / slots_per_s,
+                 "warp_instructions_per_launch": prof["inst_executed"],
+                 "warp_instructions_per_hash": prof["inst_executed"] / total,
+                 "pipes_pct_live": {"alu": prof["pipe_alu_pct"] * scale, "fmaheavy": prof["pipe_fmaheavy_pct"] * scale,
+                                    "xu": prof["pipe_xu_pct"] * scale, "lsu": prof["pipe_lsu_pct"] * scale,
+                                    "how": "ncu pipe utilisation of the capture x (cycles under ncu / cycles of the live launch)"},
+                 "ncu": {"issue_active_pct": prof["issue_active_pct"], "pipe_alu_pct": prof["pipe_alu_pct"],
+                         "pipe_fmaheavy_pct": prof["pipe_fmaheavy_pct"], "pipe_xu_pct": prof["pipe_xu_pct"],
+                         "kernel_ms_under_ncu": prof["duration_ms_under_ncu"],
+                         "shared_bank_conflicts": prof["shared_bank_conflicts"], "registers": prof["registers_per_thread"]},
+                 "traffic": prof["dram_bytes_read"] + prof["dram_bytes_write"]}
+    else:
+        issue = {"achieved": None, "frac": None, "traffic": None}
     roofline = {
-        "bound": "int32-issue (ALU+FMA pipes); not hbm, not tensor -- see DESIGN.md",
-        "achieved": achieved_ops / 1e12, "peak": p_int / 1e12, "unit": "Tint32op/s", "frac": achieved_ops / p_int,
-        "traffic": traffic,
-        "work_per_hash_ops": w, "kernel_ms": g["kernel_ms"], "kernel_hashes_per_s": total / k_s,
-        "peak_how": "live microbenchmark mvs_int_issue_peak(2): LOP3 (ALU pipe) and IMAD (FMA pipe) interleaved 1:1",
-        "issue_peaks_Top_s": {k: v / 1e12 for k, v in peaks.items()},
-        "note": "algorithmic ops W(d)=d+20*ceil(d/64) per hash (SURVEY 8d); the bit-sliced kernel issues "
-                "fewer instructions than W, so frac may exceed 1; issued-instruction utilisation is in profiles/",
-        "alu_pipe": alu_view,
+        "bound": "issue slots of the SM sub-partitions (integer ALU + FMA-heavy pipes); not hbm, not tensor -- DESIGN.md section 4",
+        "achieved": issue["achieved"], "peak": slots_per_s / 1e9, "unit": "Gwarp-instr/s", "frac": issue["frac"],
+        "traffic": issue["traffic"],
+        "how": "warp instructions of one launch (smsp__inst_executed.sum of the committed ncu capture, " + prof_why + ") / live "
+               "kernel time, over 4 x %d SMs x %.0f MHz (median SM clock sampled during the timed region)" % (sm_count, clk_mhz),
+        "profile": {k: issue[k] for k in issue if k not in ("achieved", "frac", "traffic")},
+        "kernel_ms": g["kernel_ms"], "kernel_hashes_per_s": total / k_s,
+        "frac_algorithmic": achieved_ops / p_int,
+        "algorithmic": {"achieved": achieved_ops / 1e12, "peak": p_int / 1e12, "unit": "Tint32op/s", "work_per_hash_ops": w,
+                        "peak_how": "live microbenchmark mvs_int_issue_peak(2): LOP3 (ALU pipe) and IMAD (FMA pipe) interleaved 1:1",
+                        "issue_peaks_Top_s": {k: v / 1e12 for k, v in peaks.items()},
+                        "note": "W(d)=d+20*ceil(d/64) int32 ops per hash (SURVEY 8d) charges one op per sign-accumulate; the "
+                                "bit-sliced kernel does 32 columns per LOP3, so this ratio exceeds 1 by construction and is "
+                                "not a roofline fraction"},
         "hbm": {"bound": "hbm", "achieved": alg_bytes / k_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
                 "frac": alg_bytes / k_s / 1e9 / hbm_peak, "peak_how": hbm_how,
                 "algorithmic_bytes_per_launch": alg_bytes},
     }
+    if g["config3"] is not None:
+        for row in g["config3"]["rows"]:
+            row["frac_algorithmic"] = row["hashes_per_s"] * work_per_hash(row["d"]) / p_int
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -432,6 +572,8 @@ def main():
             "clocks": g["clk"],
             "roofline": roofline,
             "cpu_baseline": cpu,
+            "config3": g["config3"],
+            "config4": g["config4"],
             "checksum": g["checksum_dev"],
         }
         _emit(line)

@@ -252,21 +252,20 @@ int mvs_get_timing(mvs_ctx* ctx, mvs_timing* t);    /* synchronises the context'
  *        IMAD.WIDE + one LOP3 per counted op). */
 int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second);
 
-/* Kernel tuning knobs for experiments (0 = default).  Unknown keys are ignored.
- * "pairwise_path": 0 = tcgen05 limb GEMM (TMA + TMEM, default), 1 = IMAD GEMM, 2 = mma.sync limb GEMM;
- * "pairwise_limbs": 0 = from the data, 1..4 = use at least that many base-256 limbs;
- * "pairwise_pair": tcgen05 path, 0 = CTA pairs (cta_group::2, 256 x 128 tiles) when there are two tile rows (default),
- *                  1 = always pairs, 2 = single CTAs;  "pairwise_cluster": single-CTA kernel in clusters of 2 (1 x 2) or
- *                  4 (2 x 2) CTAs with TMA multicast;  "pairwise_stream": 1 = stream limb pairs instead of fused stages;
- * "pairwise_fuse": tcgen05 path, 0 = threshold pre-filter in the GEMM epilogue (default), 2 = separate count pass
- * (all paths are exact; these knobs exist for the parity tests and the A/B measurements in profiles/);
- * "stage_uploads": 0 = uploads from pageable caller memory go through a pinned ring filled by host threads (default),
- *                  2 = plain cudaMemcpyAsync (the driver's own staging), for A/B measurements;
- * "stage_copy": how the ring is filled, 0 = memcpy, 1 = streaming stores (default);  "stage_threads": 1..64 host
- *                  threads per ring slot (default 8; profiles/r01g_stage_copy_ab.txt);
- * "release_workspace": frees the device and pinned buffers the pairwise entry points keep between calls (they are
- * grow-only and otherwise live until mvs_destroy). */
+/* Tuning knobs.  Returns MVS_ERR_INVALID_ARG for an unknown key or a value outside the key's range (nothing is
+ * ever ignored silently).  The shipped library knows:
+ *   "slice_hashes" (> 0): hashes per streamed slice of mvs_project_batch / mvs_sketch_batch (default 16 Mi = 128 MB);
+ *   "slice_rows_bytes" (> 0): output bytes per streamed slice (default 256 MB);
+ *   "stage_threads" (1..64): host threads that copy a pageable caller buffer into the pinned staging ring (default 8);
+ *   "release_workspace" (any value): frees the device and pinned buffers the pairwise entry points keep between calls
+ *       (they are grow-only and otherwise live until mvs_destroy).
+ * The A/B knobs of round 1 ("task_cap", "pairwise_path", "pairwise_limbs", "pairwise_pair", "pairwise_cluster",
+ * "pairwise_stream", "pairwise_fuse", "stage_copy", "stage_uploads") select code that only exists in the experiment
+ * build (make -C csrc experiments -> libmvs_b200_exp.so, compiled with -DMVS_EXPERIMENTS; used by tools/ and
+ * tests/test_gpu_experiments.py); the shipped library has one GEMM per shape class (tcgen05 CTA pair / single CTA),
+ * one upload path, and rejects those keys.  mvs_has_experiments() tells which build is loaded. */
 int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value);
+int mvs_has_experiments(void);
 
 #ifdef __cplusplus
 }

@@ -10,7 +10,9 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIBNAME = "libmvs_b200.so"
+_EXPLIBNAME = "libmvs_b200_exp.so"      # -DMVS_EXPERIMENTS build (round-1 A/B kernels and knobs); tools/ and one test module only
 _lib = None
+_explib = None
 
 
 class MvsError(RuntimeError):
@@ -83,11 +85,21 @@ SIGNATURES = {
     "mvs_get_timing": (C.c_int, [C.c_void_p, C.POINTER(Timing)]),
     "mvs_int_issue_peak": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),
     "mvs_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
+    "mvs_has_experiments": (C.c_int, []),
 }
 
 
 def library_path():
     return os.path.join(_HERE, _LIBNAME)
+
+
+def _bind(path):
+    lib = C.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if the .so lacks a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    return lib
 
 
 def load_library():
@@ -100,13 +112,20 @@ def load_library():
         raise ImportError(
             "%s is not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
             "(or `make -C metagenome_vector_sketches_b200/csrc`).  There is no CPU fallback." % path)
-    lib = C.CDLL(path)
-    for name, (res, args) in SIGNATURES.items():
-        fn = getattr(lib, name)          # AttributeError if the .so lacks a declared symbol
-        fn.restype = res
-        fn.argtypes = args
-    _lib = lib
-    return lib
+    _lib = _bind(path)
+    return _lib
+
+
+def load_experiments_library():
+    """The experiment build (make -C csrc experiments), for tools/ and tests/test_gpu_experiments.py only."""
+    global _explib
+    if _explib is None:
+        path = os.path.join(_HERE, _EXPLIBNAME)
+        if not os.path.exists(path):
+            raise ImportError("%s is not built: make -C metagenome_vector_sketches_b200/csrc experiments" % path)
+        _explib = _bind(path)
+        assert _explib.mvs_has_experiments() == 1
+    return _explib
 
 
 def _strerror(status):

@@ -13,6 +13,7 @@
 #include "mvs_internal.h"
 
 #include <algorithm>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -422,7 +423,12 @@ int mvs_internal_upload(mvs_ctx* ctx, cudaStream_t st, void* dst, const void* sr
 {
     constexpr size_t kChunk = 8u << 20;
     bool pageable = false;
-    if (bytes >= (2u << 20) && ctx->stage_uploads != 2) {
+#ifdef MVS_EXPERIMENTS                           // A/B of round 1: the driver's own staging copy, memcpy instead of streaming stores
+    const bool ring_allowed = ctx->stage_uploads != 2, streaming = ctx->stage_copy == 1;
+#else
+    constexpr bool ring_allowed = true, streaming = true;
+#endif
+    if (bytes >= (2u << 20) && ring_allowed) {
         cudaPointerAttributes at{};
         if (cudaPointerGetAttributes(&at, src) == cudaSuccess) pageable = at.type == cudaMemoryTypeUnregistered;
         else cudaGetLastError();
@@ -446,7 +452,6 @@ int mvs_internal_upload(mvs_ctx* ctx, cudaStream_t st, void* dst, const void* sr
         if (ctx->stage_busy[k]) MVS_CUDA(ctx, cudaEventSynchronize(ctx->stage_ev[k]));
         const char* from = static_cast<const char*>(src) + off;
         const int kParts = ctx->stage_threads;
-        const bool streaming = ctx->stage_copy == 1;
 #pragma omp parallel for num_threads(kParts) schedule(static)
         for (int p = 0; p < kParts; ++p) {
             const size_t a = (n * p / kParts) & ~size_t(63), b = p + 1 == kParts ? n : (n * (p + 1) / kParts) & ~size_t(63);
@@ -910,20 +915,51 @@ int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second)
 int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value)
 {
     if (!ctx || !key) return MVS_ERR_INVALID_ARG;
-    if (!std::strcmp(key, "slice_hashes") && value > 0) ctx->slice_hashes = static_cast<uint64_t>(value);
-    else if (!std::strcmp(key, "slice_rows_bytes") && value > 0) ctx->slice_rows_bytes = static_cast<uint64_t>(value);
-    else if (!std::strcmp(key, "task_cap") && value >= 0) ctx->task_cap = static_cast<uint64_t>(value);
-    else if (!std::strcmp(key, "pairwise_path") && value >= 0 && value <= 2) ctx->pairwise_path = static_cast<int>(value);
-    else if (!std::strcmp(key, "release_workspace")) { cudaSetDevice(ctx->device); cudaDeviceSynchronize(); release_workspace(ctx); }
-    else if (!std::strcmp(key, "stage_copy") && (value == 0 || value == 1)) ctx->stage_copy = static_cast<int>(value);
-    else if (!std::strcmp(key, "stage_threads") && value >= 1 && value <= 64) ctx->stage_threads = static_cast<int>(value);
-    else if (!std::strcmp(key, "stage_uploads") && (value == 0 || value == 2)) ctx->stage_uploads = static_cast<int>(value);
-    else if (!std::strcmp(key, "pairwise_fuse") && (value == 0 || value == 2)) ctx->pairwise_fuse = static_cast<int>(value);
-    else if (!std::strcmp(key, "pairwise_pair") && value >= 0 && value <= 2) ctx->pairwise_pair = static_cast<int>(value);
-    else if (!std::strcmp(key, "pairwise_cluster") && (value == 0 || value == 1 || value == 2 || value == 4)) ctx->pairwise_cluster = static_cast<int>(value);
-    else if (!std::strcmp(key, "pairwise_stream") && value >= 0 && value <= 1) ctx->pairwise_stream = static_cast<int>(value);
-    else if (!std::strcmp(key, "pairwise_limbs") && value >= 0 && value <= 4) ctx->pairwise_limbs = static_cast<int>(value);
-    return MVS_OK;
+    // a key is accepted only with a value in its range; anything else is an error, never silently ignored
+    auto set = [&](const char* name, int64_t lo, int64_t hi, auto apply) -> int {
+        if (std::strcmp(key, name) != 0) return 1;                       // not this key
+        if (value < lo || value > hi) return MVS_ERR_INVALID_ARG;
+        apply();
+        return MVS_OK;
+    };
+    int r;
+    if ((r = set("slice_hashes", 1, INT64_MAX, [&] { ctx->slice_hashes = static_cast<uint64_t>(value); })) != 1) return r;
+    if ((r = set("slice_rows_bytes", 1, INT64_MAX, [&] { ctx->slice_rows_bytes = static_cast<uint64_t>(value); })) != 1) return r;
+    if ((r = set("stage_threads", 1, 64, [&] { ctx->stage_threads = static_cast<int>(value); })) != 1) return r;
+    if ((r = set("release_workspace", INT64_MIN, INT64_MAX, [&] { cudaSetDevice(ctx->device); cudaDeviceSynchronize(); release_workspace(ctx); })) != 1) return r;
+#ifdef MVS_EXPERIMENTS                           // A/B knobs of the experiment build (libmvs_b200_exp.so); the shipped library rejects them
+    if ((r = set("task_cap", 0, INT64_MAX, [&] { ctx->task_cap = static_cast<uint64_t>(value); })) != 1) return r;
+    if ((r = set("pairwise_path", 0, 2, [&] { ctx->pairwise_path = static_cast<int>(value); })) != 1) return r;
+    if ((r = set("stage_copy", 0, 1, [&] { ctx->stage_copy = static_cast<int>(value); })) != 1) return r;
+    if (!std::strcmp(key, "stage_uploads")) {
+        if (value != 0 && value != 2) return MVS_ERR_INVALID_ARG;
+        ctx->stage_uploads = static_cast<int>(value);
+        return MVS_OK;
+    }
+    if (!std::strcmp(key, "pairwise_fuse")) {
+        if (value != 0 && value != 2) return MVS_ERR_INVALID_ARG;
+        ctx->pairwise_fuse = static_cast<int>(value);
+        return MVS_OK;
+    }
+    if ((r = set("pairwise_pair", 0, 2, [&] { ctx->pairwise_pair = static_cast<int>(value); })) != 1) return r;
+    if (!std::strcmp(key, "pairwise_cluster")) {
+        if (value != 0 && value != 1 && value != 2 && value != 4) return MVS_ERR_INVALID_ARG;
+        ctx->pairwise_cluster = static_cast<int>(value);
+        return MVS_OK;
+    }
+    if ((r = set("pairwise_stream", 0, 1, [&] { ctx->pairwise_stream = static_cast<int>(value); })) != 1) return r;
+    if ((r = set("pairwise_limbs", 0, 4, [&] { ctx->pairwise_limbs = static_cast<int>(value); })) != 1) return r;
+#endif
+    return MVS_ERR_INVALID_ARG;                  // unknown key
+}
+
+int mvs_has_experiments(void)
+{
+#ifdef MVS_EXPERIMENTS
+    return 1;
+#else
+    return 0;
+#endif
 }
 
 }  // extern "C"

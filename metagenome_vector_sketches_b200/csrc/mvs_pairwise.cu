@@ -252,6 +252,7 @@ int prepare_operand(mvs_ctx* ctx, cudaStream_t st, Operand& op, int planes_slot,
     return MVS_OK;
 }
 
+#ifdef MVS_EXPERIMENTS
 mvs::ImmaPlan make_plan(int PA, int PB)
 {
     mvs::ImmaPlan plan{};
@@ -270,6 +271,7 @@ mvs::ImmaPlan make_plan(int PA, int PB)
     }
     return plan;
 }
+#endif
 
 // Rows [r0, r0 + mi) of A against all of B, operands resident in HBM.  Appends the kept triples
 // (row_base + i, col_base + j, dot) in (i, j) order to `out`; adds the CUDA-event times.
@@ -287,12 +289,17 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
     struct EvGuard { cudaEvent_t a, b, c; ~EvGuard() { cudaEventDestroy(a); cudaEventDestroy(b); cudaEventDestroy(c); } } guard{e0, e1, e2};
 
     const int64_t ldc = (mj + 3) & ~int64_t{3};
-    const int32_t* d_A = A.v + r0 * d;
+    [[maybe_unused]] const int32_t* d_A = A.v + r0 * d;   // int32 rows: read by the experiment GEMMs only
     const int nseg = static_cast<int>((mj + mvs::kPwSeg - 1) / mvs::kPwSeg);
     const unsigned seg_ctas = static_cast<unsigned>(((mi + mvs::kPwRows - 1) / mvs::kPwRows * nseg + 7) / 8);   // 8 warps per CTA
     bool fused = false;
     PW_CUDA(ctx, cudaEventRecord(e0, st));
-    if (A.P > 0 && mvs_internal_pairwise_path(ctx) == 0) {   // tcgen05 limb GEMM (TMA + TMEM)
+#ifdef MVS_EXPERIMENTS
+    const int path = mvs_internal_pairwise_path(ctx);
+#else
+    constexpr int path = 0;                      // the shipped library has ONE GEMM: the tcgen05 limb GEMM
+#endif
+    if (A.P > 0 && path == 0) {                  // tcgen05 limb GEMM (TMA + TMEM)
         mvs::UmmaPlan plan = make_umma_plan(A.P, B.P, mvs_internal_pairwise_stream(ctx) == 0);
 #ifdef MVS_UMMA_PROBE                            // diagnostic build only: switch kernel roles off (wrong results), see UmmaPlan::probe
         if (const char* e = std::getenv("MVS_UMMA_PROBE")) plan.probe = std::atoi(e);
@@ -309,8 +316,12 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
         // cluster shape: 1 x 1 by default.  Clusters of 1 x 2 / 2 x 2 CTAs sharing operand tiles by TMA multicast (option
         // "pairwise_cluster" = 2 / 4) halve the L2 reads but are NOT faster: the main loop is bound by the bytes an SM
         // can take in (~32 B/clk, the same with multicast), see DESIGN.md section 9
+#ifdef MVS_EXPERIMENTS
         int cshape = mvs_internal_pairwise_cluster(ctx);
         if (cshape == 0) cshape = 1;
+#else
+        constexpr int cshape = 1;
+#endif
         const int cm = cshape == 4 ? 2 : 1, cn = cshape >= 2 ? 2 : 1;
         // default: CTA pairs (tcgen05 cta_group::2, 256 x 128 super-tiles) whenever there are two tile rows to pair
         const int pair_opt = mvs_internal_pairwise_pair(ctx);
@@ -324,9 +335,12 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
         if (!make_tensor_map(A, mvs::kUmBM / cn, &tmA) || !make_tensor_map(B, mvs::kUmBN / cm, &tmB)) return MVS_ERR_CUDA;
         cudaError_t le;
         const bool f22 = plan.ngroups == 1 && plan.a_count == 2 && plan.b_count == 2;
+#ifdef MVS_EXPERIMENTS
         if (cshape == 4) le = launch_umma<2, 2, false>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n, filt);
         else if (cshape == 2) le = launch_umma<1, 2, false>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n, filt);
-        else if (f22) le = launch_umma<1, 1, true>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n, filt);
+        else
+#endif
+        if (f22) le = launch_umma<1, 1, true>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n, filt);
         else le = launch_umma<1, 1, false>(st, sms, smem, tmA, tmB, plan, A.k_pad, static_cast<int>(r0), mi, mj, d_C, ldc, tiles_m, tiles_n, filt);
         PW_CUDA(ctx, le);
 #ifdef MVS_UMMA_PROBE
@@ -341,7 +355,9 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
         }
 #endif
         }
-    } else if (A.P > 0) {                        // warp-level mma.sync limb GEMM
+    }
+#ifdef MVS_EXPERIMENTS
+    else if (A.P > 0) {                          // warp-level mma.sync limb GEMM
         const mvs::ImmaPlan plan = make_plan(A.P, B.P);
         const dim3 grid(static_cast<unsigned>((mj + mvs::kImBN - 1) / mvs::kImBN), static_cast<unsigned>((mi + mvs::kImBM - 1) / mvs::kImBM));
         mvs::pairwise_dot_imma_kernel<<<grid, mvs::kImThreads, mvs::kImSmemBytes, st>>>(
@@ -353,13 +369,21 @@ int pairwise_core(mvs_ctx* ctx, cudaStream_t st, const Operand& A, int64_t r0, i
         if (vec) mvs::pairwise_dot_kernel<true><<<grid, mvs::kPwThreads, 0, st>>>(d_A, mi, B.v, mj, d, d_C, ldc);
         else mvs::pairwise_dot_kernel<false><<<grid, mvs::kPwThreads, 0, st>>>(d_A, mi, B.v, mj, d, d_C, ldc);
     }
+#else
+    else return MVS_ERR_INVALID_ARG;             // operands are always split in the shipped build
+#endif
     PW_CUDA(ctx, cudaGetLastError());
     PW_CUDA(ctx, cudaEventRecord(e1, st));
+#ifdef MVS_EXPERIMENTS
     if (!fused) {
         mvs::pairwise_count_kernel<<<seg_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_segcount, nseg);
         PW_CUDA(ctx, cudaGetLastError());
         mvs_internal_count_launches(ctx, 1);
     }
+#else
+    (void)seg_ctas;
+    if (!fused) return MVS_ERR_INVALID_ARG;
+#endif
     const unsigned row_ctas = static_cast<unsigned>((mi + 7) / 8);                       // one warp per row
     mvs::pairwise_rowsum_kernel<<<row_ctas, 256, 0, st>>>(d_C, mi, mj, ldc, d, d_ni, d_nj, d_segcount, nseg, mvs::kUmMaybe, d_rowoff);
     PW_CUDA(ctx, cudaGetLastError());
@@ -426,7 +450,9 @@ int run_blocks(mvs_ctx* ctx, cudaStream_t st, Operand& A, int64_t begin, int64_t
         PW_CUDA(ctx, cudaStreamSynchronize(st));                      // the asynchronous upload is not part of prep_ms
         const auto t0 = std::chrono::steady_clock::now();
         PW_RC(mm.alloc(ctx, kWsMinmax, 8));
+#ifdef MVS_EXPERIMENTS
         PW_CUDA(ctx, cudaFuncSetAttribute(mvs::pairwise_dot_imma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mvs::kImSmemBytes));
+#endif
         PW_RC(prepare_operand(ctx, st, B, kWsPlanesB, d, mm.as<int>(), static_cast<int*>(h_pinned)));
         if (!same) PW_RC(prepare_operand(ctx, st, A, kWsPlanesA, d, mm.as<int>(), static_cast<int*>(h_pinned)));
         PW_CUDA(ctx, cudaStreamSynchronize(st));

@@ -48,6 +48,7 @@ __device__ __forceinline__ bool pw_keep(int32_t dot, int d, double ni, double nj
     return pw_keep_literal(dot, d, threshold);
 }
 
+#ifdef MVS_EXPERIMENTS                           // cross-check GEMM of the experiment build only (option "pairwise_path" = 1)
 // One 16-byte (4 x int32) slice of a row starting at column k (p = row + k); zero past the row end / for rows
 // outside the matrix.  VEC: d % 4 == 0 and 16-byte aligned base, so k < d implies k + 3 < d.
 template <bool VEC>
@@ -162,6 +163,8 @@ pairwise_dot_kernel(const int32_t* __restrict__ A, int64_t mi, const int32_t* __
     }
 }
 
+#endif  // MVS_EXPERIMENTS
+
 // ------------------------------------------------------------------------------------------------------
 // Tensor-core path: int32 = up to 4 balanced base-256 limbs, v = sum_p 256^p * s_p with s_p in [-128, 127]
 // (exact modulo 2^32), so   dot mod 2^32 = sum_{p + q <= 3} 256^(p+q) * (A_p . B_q)   with int8 x int8 -> int32
@@ -230,6 +233,7 @@ pairwise_split_kernel(const int32_t* __restrict__ V, int64_t n, int d, int P, in
     }
 }
 
+#ifdef MVS_EXPERIMENTS                           // warp-level mma.sync GEMM of the experiment build only (option "pairwise_path" = 2)
 __device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void* gsrc)
 {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");
@@ -365,6 +369,8 @@ pairwise_dot_imma_kernel(const int8_t* __restrict__ Ap, int64_t a_plane_stride, 
         }
 }
 
+#endif  // MVS_EXPERIMENTS
+
 // ------------------------------------------------------------------------------------------------------
 // Threshold + ordered compaction.  The columns of a row are cut into segments of 128; one warp owns one
 // (row, segment): lane L holds columns 4L..4L+3 of the segment (one 16-byte load).
@@ -420,10 +426,11 @@ __device__ __forceinline__ int4 pw_load_c4(const int32_t* __restrict__ crow, int
     return v;
 }
 
+constexpr int kPwRows = 8;
+#ifdef MVS_EXPERIMENTS                           // separate count pass (option "pairwise_fuse" = 2); the shipped path filters in the GEMM epilogue
 // One warp = one 128-column segment of kPwRows consecutive rows: the lane keeps its four column norms in registers,
 // has all kPwRows 16-byte loads of C in flight at once (the pass is HBM-bound: C is read exactly once), and the
 // per-row counts are reduced with one redux each.
-constexpr int kPwRows = 8;
 
 __global__ void __launch_bounds__(256)
 pairwise_count_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int64_t ldc, int d,
@@ -460,6 +467,7 @@ pairwise_count_kernel(const int32_t* __restrict__ C, int64_t mi, int64_t mj, int
         if (lane == 0) segcount[(row0 + r) * nseg + seg] = n;
     }
 }
+#endif  // MVS_EXPERIMENTS
 
 // One warp per row: reads the row's segment counts (coalesced), replaces every count marked `maybe` -- a segment the
 // GEMM's fused pre-filter (mvs_pairwise_umma.cuh) stored without deciding it -- by the exact count, and writes the

@@ -17,7 +17,7 @@ import math
 import numpy as np
 
 from . import _lib
-from ._lib import Timing, check, load_library
+from ._lib import Timing, check, load_library, load_experiments_library
 
 
 def _ptr(a):
@@ -27,8 +27,10 @@ def _ptr(a):
 class Sketcher:
     """One context = one GPU (mvs_create).  Not thread-safe; one per process/thread."""
 
-    def __init__(self, device=0):
-        self._lib = load_library()
+    def __init__(self, device=0, experiments=False):
+        """experiments=True binds the context to the experiment build (libmvs_b200_exp.so) whose set_option knows the
+        round-1 A/B knobs; the default is the shipped library."""
+        self._lib = load_experiments_library() if experiments else load_library()
         h = C.c_void_p()
         check(self._lib.mvs_create(C.byref(h), int(device)), "mvs_create")
         self._h = h
@@ -135,7 +137,7 @@ class Sketcher:
 def sketch_csr_multi(sketchers, hashes, offsets, d, seed=0, int16=False):
     """mvs_sketch_batch_multi: ONE call over several contexts (one per GPU; they may also share a device).
     Returns dict(vec | vec16, sumsq, ref_norms); rows are in input order."""
-    lib = load_library()
+    lib = sketchers[0]._lib
     hashes = np.ascontiguousarray(hashes, dtype=np.uint64)
     offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
     n = len(offsets) - 1

@@ -13,24 +13,14 @@ from oracle_util import (load_toy_ref, norms_sq_like_reference, oracle_pairwise,
 pytestmark = pytest.mark.gpu
 
 
-# every test runs on the tcgen05 limb GEMM (limbs from the data = FUSED stages, forced to 3 and 4 limbs = 8 and 10 limb
-# products streamed pair by pair; also as clusters of 1 x 2 and 2 x 2 CTAs with TMA multicast), on the mma.sync limb GEMM
-# and on the IMAD GEMM: all must give the reference's bits
-# "pair" = tcgen05 cta_group::2 (two SMs per 256 x 128 tile); entries: options pairwise_path, pairwise_limbs, pairwise_cluster,
-# pairwise_pair (2 = single CTAs), pairwise_fuse (2 = separate count pass instead of the keep-test in the GEMM epilogue)
-PATHS = {"default": (0, 0, 0, 0, 0), "umma": (0, 0, 0, 2, 0), "umma3": (0, 3, 0, 2, 0), "umma4": (0, 4, 0, 2, 0), "umma_1x2": (0, 0, 2, 2, 0),
-         "umma_2x2": (0, 0, 4, 2, 0), "umma4_2x2": (0, 4, 4, 2, 0), "pair": (0, 0, 0, 1, 0), "pair3": (0, 3, 0, 1, 0), "pair4": (0, 4, 0, 1, 0),
-         "umma_nofuse": (0, 0, 0, 2, 2), "pair_nofuse": (0, 0, 0, 1, 2), "mma": (2, 0, 0, 0, 0), "mma4": (2, 4, 0, 0, 0), "imad": (1, 0, 0, 0, 0)}
-
-
-@pytest.fixture(scope="module", params=list(PATHS))
-def sk(request):
+# The shipped library has ONE path per shape class: tcgen05 CTA pairs (cta_group::2, 256 x 128 tiles) when a block has
+# two tile rows, a single CTA otherwise, keep-test fused into the GEMM epilogue, limb count from the data (the cases
+# below reach 2, 3 and 4 limbs and both shape classes through their inputs).  The round-1 A/B variants (forced limbs,
+# clusters with TMA multicast, separate count pass, mma.sync and IMAD GEMMs) live in the experiment build and are
+# covered by tests/test_gpu_experiments.py, which re-runs every case of this module on them.
+@pytest.fixture(scope="module")
+def sk():
     s = mvs.Sketcher(0)
-    s.set_option("pairwise_path", PATHS[request.param][0])
-    s.set_option("pairwise_limbs", PATHS[request.param][1])
-    s.set_option("pairwise_cluster", PATHS[request.param][2])
-    s.set_option("pairwise_pair", PATHS[request.param][3])
-    s.set_option("pairwise_fuse", PATHS[request.param][4])
     yield s
     s.close()
 

@@ -299,10 +299,22 @@ def test_host_side_helpers_binding_write_combined_and_staging_modes(sk):
     big = np.empty(len(h) + 3, dtype=np.uint64)[3:]                       # pageable, 24 bytes off the allocation
     big[:] = h
     try:
-        for copy, threads in ((0, 4), (1, 1), (1, 3), (1, 8), (0, 64)):
-            sk.set_option("stage_copy", copy)
+        for threads in (1, 3, 8, 64):
             sk.set_option("stage_threads", threads)
             assert np.array_equal(sk.project_csr(big, off, 192), want)
     finally:
-        sk.set_option("stage_copy", 1)
         sk.set_option("stage_threads", 8)
+
+
+def test_set_option_rejects_unknown_keys_and_bad_values(sk):
+    """A mistyped knob must not silently test the default path: unknown keys, out-of-range values and the round-1
+    A/B knobs (which only exist in the experiment build) are MVS_ERR_INVALID_ARG in the shipped library."""
+    assert mvs.load_library().mvs_has_experiments() == 0
+    for key, value in (("no_such_option", 1), ("stage_thread", 4), ("stage_threads", 0), ("stage_threads", 65),
+                       ("slice_hashes", 0), ("slice_rows_bytes", -5), ("pairwise_path", 1), ("pairwise_path", 0),
+                       ("stage_copy", 0), ("stage_uploads", 2), ("task_cap", 1024), ("pairwise_limbs", 4), ("", 0)):
+        with pytest.raises(mvs.MvsError) as e:
+            sk.set_option(key, value)
+        assert e.value.status == -1, (key, value)
+    sk.set_option("stage_threads", 8)
+    sk.set_option("slice_hashes", 16 << 20)

@@ -7,7 +7,7 @@ rng = np.random.default_rng(1)
 h = rng.integers(0, 2**54, n*per, dtype=np.uint64)
 off = np.arange(n+1, dtype=np.uint64)*per
 out = np.empty((n, d), dtype=np.int32)
-sk = mvs.Sketcher(0)
+sk = mvs.Sketcher(0, experiments=True)       # knobs of the experiment build: make -C metagenome_vector_sketches_b200/csrc experiments
 for mode in (0, 2, 0, 2):
     sk.set_option("stage_uploads", mode)
     sk.project_csr(h, off, d, out=out)

@@ -9,7 +9,7 @@ from metagenome_vector_sketches_b200 import synthetic as syn
 from sweep import time_device
 
 dev = torch.device("cuda", 0)
-sk = mvs.Sketcher(0)
+sk = mvs.Sketcher(0, experiments=True)       # knobs of the experiment build: make -C metagenome_vector_sketches_b200/csrc experiments
 cases = []
 dh, off = syn.uniform_batch_torch(10000, 50000, dev, seed=0)
 cases.append(("c2", dh, off, 2048))

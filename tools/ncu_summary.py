@@ -2,8 +2,13 @@
 committed under profiles/ (selected raw metrics + per-opcode instruction and stall-sample table).
 
     python tools/ncu_summary.py gpurun_out/r01c_project.ncu-rep "header line ..." > profiles/r01c_project_kernel_ncu_full.txt
+    python tools/ncu_summary.py rep.ncu-rep --json profiles/project_kernel_profile.json --key <cubin key> \
+        --workload 10000x50000x2048 --source profiles/<summary>.txt "header ..." > profiles/<summary>.txt
 
-Runs in the build container (ncu reads reports without a GPU).  Tooling, not product code."""
+--json writes the machine-readable profile bench.py reads (instruction count, pipe utilisations, DRAM bytes of one
+launch), keyed by the sha256 of the projection cubin that was profiled (tools/cubin_key.py, recorded in the same
+gpurun call as the capture).  Runs in the build container (ncu reads reports without a GPU).  Tooling, not product code."""
+import json
 import collections
 import csv
 import io
@@ -33,13 +38,57 @@ def ncu_csv(rep, page):
     return list(csv.reader(io.StringIO(out)))
 
 
+def to_bytes(value, unit):
+    mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    return float(value.replace(",", "")) * mult[unit]
+
+
+def write_json(path, key, workload, source, hdr, units, vals):
+    ix = {h: i for i, h in enumerate(hdr)}
+
+    def num(name):
+        return float(vals[ix[name]].replace(",", ""))
+
+    dur_unit = units[ix["gpu__time_duration.sum"]]
+    dur_ms = num("gpu__time_duration.sum") * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(dur_unit, 1e-6)
+    prof = {
+        "cubin_sha256": key, "kernel": vals[ix["Kernel Name"]], "grid": vals[ix["Grid Size"]], "workload": workload,
+        "source": source,
+        "inst_executed": num("smsp__inst_executed.sum"),
+        "sm_cycles_elapsed_avg": num("sm__cycles_elapsed.avg"),
+        "sm_clock_ghz": num("sm__cycles_elapsed.avg.per_second"),
+        "duration_ms_under_ncu": dur_ms,
+        "issue_active_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+        "pipe_alu_pct": num("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
+        "pipe_fmaheavy_pct": num("sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed"),
+        "pipe_xu_pct": num("sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"),
+        "pipe_lsu_pct": num("sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active"),
+        "dram_bytes_read": to_bytes(vals[ix["dram__bytes_read.sum"]], units[ix["dram__bytes_read.sum"]]),
+        "dram_bytes_write": to_bytes(vals[ix["dram__bytes_write.sum"]], units[ix["dram__bytes_write.sum"]]),
+        "shared_bank_conflicts": num("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum"),
+        "registers_per_thread": num("launch__registers_per_thread"),
+    }
+    json.dump(prof, open(path, "w"), indent=1)
+    open(path, "a").write("\n")
+
+
 def main():
-    rep = sys.argv[1]
-    for line in sys.argv[2:]:
+    argv = sys.argv[1:]
+    opts = {}
+    for flag in ("--json", "--key", "--workload", "--source"):
+        if flag in argv:
+            i = argv.index(flag)
+            opts[flag] = argv[i + 1]
+            del argv[i:i + 2]
+    rep = argv[0]
+    for line in argv[1:]:
         print("# " + line)
     raw = ncu_csv(rep, "raw")
     hdr, units, vals = raw[0], raw[1], raw[2]
     ix = {h: i for i, h in enumerate(hdr)}
+    if "--json" in opts:
+        write_json(opts["--json"], opts.get("--key", ""), opts.get("--workload", ""), opts.get("--source", ""), hdr, units, vals)
+        print("# cubin key of the profiled library (tools/cubin_key.py): %s" % opts.get("--key", ""))
     print("# kernel: %s  grid %s block %s" % (vals[ix["Kernel Name"]], vals[ix["Grid Size"]], vals[ix["Block Size"]]))
     print("#\n# ---- selected raw metrics (ncu --page raw) ----")
     for h, u, v in zip(hdr, units, vals):
