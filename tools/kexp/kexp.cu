@@ -13,7 +13,10 @@
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA %s at %d\n", cudaGetErrorString(e_), __LINE__); exit(1); } } while (0)
 
 constexpr uint64_t kGolden = 0x9e3779b97f4a7c15ULL;
-constexpr int kPlanes = 12;
+#ifndef KPLANES
+#define KPLANES 14
+#endif
+constexpr int kPlanes = KPLANES;          // product: 14 (csrc/mvs_kernels.cuh); the round-1 tables were taken with 12
 
 struct Consts { uint32_t m4, m32, m2; };   // 2^(32-30), 2^(32-27), 2^(32-31): opaque to ptxas
 
@@ -146,16 +149,27 @@ __device__ __forceinline__ void group16(const uint64_t* __restrict__ sp, uint64_
 // with the low word of the first multiplier are the same for all 32 lanes, so the lane skips one
 // SHF + one LOP3 (ALU pipe) and one IMAD, and {0, M} is the 64-bit addend of the IMAD.WIDE.
 // V & 8 here: lane add as IMAD (FMA pipe).  V & 4: second multiply as wide + 2 mad.lo.
+// V & 512: record {lo32(hb), F, 0, M}: the second half is a ready-made 64-bit addend (M << 32) for the IMAD.WIDE, which
+//          then yields (lo, hi + M) at once; hi += l1 * K1hi follows as one IMAD.  One add less per (hash, lane).
+//          The exact path takes hb from the raw tile (rawv = raw hash + golden).
 template <int V, bool EXACT>
-__device__ __forceinline__ void mix_cooked(ulonglong2 c, uint32_t off, const Consts& kc, uint32_t& olo, uint32_t& ohi,
+__device__ __forceinline__ void mix_cooked(ulonglong2 c, uint64_t rawv, uint32_t off, const Consts& kc, uint32_t& olo, uint32_t& ohi,
                                            uint32_t& eacc)
 {
     uint32_t lo, hi;
     if constexpr (EXACT) {
-        const uint64_t x = c.x + off;
+        const uint64_t x = ((V & 512) ? rawv : c.x) + off;
         const uint64_t y = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ULL;
         lo = static_cast<uint32_t>(y);
         hi = static_cast<uint32_t>(y >> 32);
+    } else if constexpr (V & 512) {
+        const uint32_t xl = static_cast<uint32_t>(c.x) + off;
+        const uint32_t l1 = xl ^ static_cast<uint32_t>(c.x >> 32);
+        uint64_t y;
+        asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(y) : "r"(l1), "r"(0x1ce4e5b9u), "l"(c.y));
+        lo = static_cast<uint32_t>(y);
+        hi = static_cast<uint32_t>(y >> 32);
+        asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(hi) : "r"(l1), "r"(0xbf58476du));
     } else {
         uint32_t xl;
         if constexpr (V & 8) asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(xl) : "r"(off), "r"(kc.m2 >> 1), "r"(static_cast<uint32_t>(c.x)));
@@ -181,18 +195,31 @@ __device__ __forceinline__ void mix_cooked(ulonglong2 c, uint32_t off, const Con
 }
 
 template <int V, bool EXACT>
-__device__ __forceinline__ void group16c(const ulonglong2* __restrict__ sp, uint32_t off, const Consts& kc,
+__device__ __forceinline__ void group16c(const ulonglong2* __restrict__ sp, const uint64_t* __restrict__ raw, uint32_t off, const Consts& kc,
                                          uint32_t (&Plo)[kPlanes], uint32_t (&Phi)[kPlanes],
                                          uint32_t& c16lo, uint32_t& c16hi, uint32_t& eacc)
 {
-    uint32_t lo[16], hi[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) mix_cooked<V, EXACT>(sp[i], off, kc, lo[i], hi[i], eacc);
     uint32_t fl[4], fh[4];
+    if constexpr (V & 1024) {                    // source order: mix 4, compress 4, mix 4, ... (both pipes fed in every window)
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        fl[q] = hs4(Plo, lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
-        fh[q] = hs4(Phi, hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+        for (int q = 0; q < 4; ++q) {
+            uint32_t lo[4], hi[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                mix_cooked<V, EXACT>(sp[4 * q + i], (EXACT && (V & 512)) ? raw[4 * q + i] + kGolden : 0ull, off, kc, lo[i], hi[i], eacc);
+            fl[q] = hs4(Plo, lo[0], lo[1], lo[2], lo[3]);
+            fh[q] = hs4(Phi, hi[0], hi[1], hi[2], hi[3]);
+        }
+    } else {
+        uint32_t lo[16], hi[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            mix_cooked<V, EXACT>(sp[i], (EXACT && (V & 512)) ? raw[i] + kGolden : 0ull, off, kc, lo[i], hi[i], eacc);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            fl[q] = hs4(Plo, lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+            fh[q] = hs4(Phi, hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+        }
     }
     uint32_t eA, eB;
     csa(eA, Plo[2], Plo[2], fl[0], fl[1]);
@@ -201,6 +228,26 @@ __device__ __forceinline__ void group16c(const ulonglong2* __restrict__ sp, uint
     csa(eA, Phi[2], Phi[2], fh[0], fh[1]);
     csa(eB, Phi[2], Phi[2], fh[2], fh[3]);
     csa(c16hi, Phi[3], Phi[3], eA, eB);
+}
+
+// V & 4096: 64 hashes per loop trip: four groups with the carries merged directly (no pending-carry state, no branches)
+template <int V, bool EXACT>
+__device__ __forceinline__ void group64c(const ulonglong2* __restrict__ sp, const uint64_t* __restrict__ raw, uint32_t off, const Consts& kc,
+                                         uint32_t (&Plo)[kPlanes], uint32_t (&Phi)[kPlanes], uint32_t& eacc)
+{
+    uint32_t a_lo, a_hi, b_lo, b_hi, c32lo[2], c32hi[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        group16c<V, EXACT>(sp + 32 * h, raw + 32 * h, off, kc, Plo, Phi, a_lo, a_hi, eacc);
+        group16c<V, EXACT>(sp + 32 * h + 16, raw + 32 * h + 16, off, kc, Plo, Phi, b_lo, b_hi, eacc);
+        csa(c32lo[h], Plo[4], Plo[4], a_lo, b_lo);
+        csa(c32hi[h], Phi[4], Phi[4], a_hi, b_hi);
+    }
+    uint32_t c64lo, c64hi;
+    csa(c64lo, Plo[5], Plo[5], c32lo[0], c32lo[1]);
+    csa(c64hi, Phi[5], Phi[5], c32hi[0], c32hi[1]);
+    ripple<6>(Plo, c64lo);
+    ripple<6>(Phi, c64hi);
 }
 
 __device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc, uint32_t src_bytes)
@@ -218,8 +265,8 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // One warp = `per` hashes (multiple of 64) of one "sample" -> out row of 2048 int32.
-template <int V, int WARPS, int TILE>
-__global__ void __launch_bounds__(WARPS * 32)
+template <int V, int WARPS, int TILE, int MINB = 1>
+__global__ void __launch_bounds__(WARPS * 32, MINB)
 kexp_kernel(const uint64_t* __restrict__ hashes, uint32_t ntasks, uint32_t per, Consts kc, int32_t* __restrict__ out)
 {
     extern __shared__ __align__(16) uint64_t smem[];
@@ -269,7 +316,8 @@ kexp_kernel(const uint64_t* __restrict__ hashes, uint32_t ntasks, uint32_t per, 
                 const uint32_t xh = static_cast<uint32_t>(v >> 32);
                 const uint32_t m = (xh ^ (xh >> 30)) * 0x1ce4e5b9u;
                 const uint32_t f = (xl0 >> 30) | (xh << 2);
-                cooked[i * 32 + lane] = make_ulonglong2(v, (static_cast<uint64_t>(m) << 32) | ((V & 256) ? f : 0u));
+                if constexpr (V & 512) cooked[i * 32 + lane] = make_ulonglong2((static_cast<uint64_t>(f) << 32) | xl0, static_cast<uint64_t>(m) << 32);
+                else cooked[i * 32 + lane] = make_ulonglong2(v, (static_cast<uint64_t>(m) << 32) | ((V & 256) ? f : 0u));
             }
             tile_risky = __any_sync(0xffffffffu, risky);
             __syncwarp();
@@ -286,11 +334,17 @@ kexp_kernel(const uint64_t* __restrict__ hashes, uint32_t ntasks, uint32_t per, 
         }
         const uint32_t valid = min(per - t * TILE, static_cast<uint32_t>(TILE));
         const uint32_t ngroups = (valid + 15) >> 4;
+        if constexpr ((V & 4096) != 0) {         // per is a multiple of 64 in this bench
+            for (uint32_t gi = 0; gi < ngroups; gi += 4) {
+                if (tile_risky) group64c<V, true>(cooked + gi * 16, st + gi * 16, static_cast<uint32_t>(lane) << 6, kc, Plo, Phi, eacc);
+                else group64c<V, false>(cooked + gi * 16, st + gi * 16, static_cast<uint32_t>(lane) << 6, kc, Plo, Phi, eacc);
+            }
+        } else
         for (uint32_t gi = 0; gi < ngroups; ++gi, ++g) {
             uint32_t c16lo, c16hi;
             if constexpr (V & 128) {
-                if (tile_risky) group16c<V, true>(cooked + gi * 16, static_cast<uint32_t>(lane) << 6, kc, Plo, Phi, c16lo, c16hi, eacc);
-                else group16c<V, false>(cooked + gi * 16, static_cast<uint32_t>(lane) << 6, kc, Plo, Phi, c16lo, c16hi, eacc);
+                if (tile_risky) group16c<V, true>(cooked + gi * 16, st + gi * 16, static_cast<uint32_t>(lane) << 6, kc, Plo, Phi, c16lo, c16hi, eacc);
+                else group16c<V, false>(cooked + gi * 16, st + gi * 16, static_cast<uint32_t>(lane) << 6, kc, Plo, Phi, c16lo, c16hi, eacc);
             } else
             if ((V & 16) && tile_risky) group16<(V & ~16)>(st + gi * 16, cval, kc, Plo, Phi, c16lo, c16hi, eacc);
             else group16<V>(st + gi * 16, cval, kc, Plo, Phi, c16lo, c16hi, eacc);
@@ -469,13 +523,13 @@ static int32_t* d_out;
 static uint32_t g_ntasks, g_per;
 static int g_reps = 6;
 
-template <int V, int WARPS, int TILE>
+template <int V, int WARPS, int TILE, int MINB = 1>
 void run(const char* name)
 {
     const Consts kc{4u, 32u, 2u};
     const uint32_t grid = (g_ntasks + WARPS - 1) / WARPS;
     const size_t smem = static_cast<size_t>(WARPS) * 2 * TILE * 8 + ((V & 128) ? static_cast<size_t>(WARPS) * TILE * 16 : 0);
-    CK(cudaFuncSetAttribute(kexp_kernel<V, WARPS, TILE>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    CK(cudaFuncSetAttribute(kexp_kernel<V, WARPS, TILE, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
@@ -483,7 +537,7 @@ void run(const char* name)
     CK(cudaMemset(d_out, 0, static_cast<size_t>(g_ntasks) * 2048 * 4));
     for (int rep = 0; rep < g_reps; ++rep) {
         CK(cudaEventRecord(e0));
-        kexp_kernel<V, WARPS, TILE><<<grid, WARPS * 32, smem>>>(d_h, g_ntasks, g_per, kc, d_out);
+        kexp_kernel<V, WARPS, TILE, MINB><<<grid, WARPS * 32, smem>>>(d_h, g_ntasks, g_per, kc, d_out);
         CK(cudaEventRecord(e1));
         CK(cudaEventSynchronize(e1));
         CK(cudaGetLastError());
@@ -496,10 +550,10 @@ void run(const char* name)
     unsigned long long acc;
     CK(cudaMemcpy(&acc, d_acc, 8, cudaMemcpyDeviceToHost));
     cudaFuncAttributes fa;
-    CK(cudaFuncGetAttributes(&fa, kexp_kernel<V, WARPS, TILE>));
+    CK(cudaFuncGetAttributes(&fa, kexp_kernel<V, WARPS, TILE, MINB>));
     const double hashes = static_cast<double>(g_ntasks) * g_per;
-    printf("%-28s V=%2d W=%d T=%4d regs=%3d  %8.3f ms  %7.3f Ghash/s  clk/hash/warp=%6.2f  sum=%016llx\n", name, V, WARPS,
-           TILE, fa.numRegs, best, hashes / best / 1e6, 1.965e9 * 592.0 / (hashes / (best * 1e-3)), acc);
+    printf("%-34s V=%4d W=%d T=%4d minb=%d regs=%3d  %8.3f ms  %7.3f Ghash/s  clk/hash/warp=%6.2f  sum=%016llx\n", name, V, WARPS,
+           TILE, MINB, fa.numRegs, best, hashes / best / 1e6, 1.965e9 * 592.0 / (hashes / (best * 1e-3)), acc);
     fflush(stdout);
 }
 
