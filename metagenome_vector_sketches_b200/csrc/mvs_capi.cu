@@ -60,7 +60,7 @@ struct Geometry {
     int S = 1;                                   // hash slots per warp
     int passes = 1;                              // 32-block column passes
     uint64_t cap = 0;                            // max hashes per warp task
-    uint32_t quantum = 16;                       // 16 * S
+    uint32_t quantum = 64;                       // hashes of one loop trip of the kernel: chunk sizes are multiples of it
 };
 
 }  // namespace
@@ -73,6 +73,7 @@ struct mvs_ctx {
     // ring of CUDA-event triples (start, after projection, after reduce), one per
     // mvs_project_device call; mvs_get_timing averages the calls since the last query
     cudaEvent_t ev[kTimingRing][3] = {};
+    unsigned device_turn = 0;                    // mvs_project_device calls so far (slot rotation)
     uint64_t timing_calls = 0;                   // device-path calls recorded so far
     uint64_t timing_read = 0;                    // calls already consumed by mvs_get_timing
     mvs_timing timing{};
@@ -160,7 +161,8 @@ Geometry make_geometry(int d)
         g.passes = 1;
     }
     g.S = 32 >> g.lph_log2;
-    g.quantum = 16u * static_cast<uint32_t>(g.S);
+    // one trip = up to four Harley-Seal groups of 16 rounds for all S hash slots, never more than a staging tile
+    g.quantum = std::min<uint32_t>(64u * static_cast<uint32_t>(g.S), static_cast<uint32_t>(mvs::tile_hashes(g.lph_log2)));
     g.cap = static_cast<uint64_t>(mvs::kMaxRounds) * static_cast<uint64_t>(g.S);
     return g;
 }
@@ -169,21 +171,59 @@ struct PlanCounts {
     uint64_t tasks = 0, reduce = 0, prows = 0;
 };
 
+// How a batch is cut into warp tasks.  A sample larger than the cap is split into equal chunks (multiples of the
+// kernel's trip quantum).  The cap is NOT constant over the batch: tasks are launched in list order onto `workers`
+// resident warps, and equal-size tasks would leave the last wave mostly empty (config 3: 7168 tasks on 3552 warps =
+// 2.02 waves).  So the cap shrinks towards the end of the list like guided self-scheduling -- a task is at most
+// half of what would be left per worker -- down to `cap_min`; the tail of the launch is then made of short tasks.
+struct Chunker {
+    uint64_t cap_full, cap_min, quantum, workers, passes;
+    uint64_t remaining;                          // hashes x passes not yet planned
+
+    uint64_t cap_now() const
+    {
+        uint64_t c = remaining / (2 * workers);
+        c = c / quantum * quantum;
+        return std::min(cap_full, std::max(cap_min, c));
+    }
+    // chunks of a sample of n hashes: count and size
+    void split(uint64_t n, uint64_t& nchunks, uint64_t& per)
+    {
+        const uint64_t cap = cap_now();
+        nchunks = 1;
+        per = n;
+        if (n > cap) {
+            const uint64_t k = (n + cap - 1) / cap;
+            per = (n + k - 1) / k;
+            per = (per + quantum - 1) / quantum * quantum;
+            nchunks = (n + per - 1) / per;
+        }
+        remaining -= std::min(remaining, n * passes);
+    }
+};
+
+Chunker make_chunker(const uint64_t* offsets, int64_t s0, int64_t s1, const Geometry& g, uint64_t workers, uint64_t cap_min)
+{
+    Chunker c;
+    c.cap_full = g.cap;
+    c.quantum = g.quantum;
+    c.cap_min = std::min(g.cap, std::max<uint64_t>(cap_min / g.quantum * g.quantum, g.quantum));
+    c.workers = std::max<uint64_t>(workers, 1);
+    c.passes = static_cast<uint64_t>(g.passes);
+    c.remaining = (offsets[s1] - offsets[s0]) * c.passes;
+    return c;
+}
+
 // First pass: how many tasks / reduce items / partial rows does [s0, s1) need?
-int count_plan(const uint64_t* offsets, int64_t s0, int64_t s1, const Geometry& g, PlanCounts& pc)
+int count_plan(const uint64_t* offsets, int64_t s0, int64_t s1, const Geometry& g, Chunker ch, PlanCounts& pc)
 {
     pc = PlanCounts{};
     for (int64_t s = s0; s < s1; ++s) {
         if (offsets[s + 1] < offsets[s]) return MVS_ERR_INVALID_ARG;
         const uint64_t n = offsets[s + 1] - offsets[s];
         if (n >= (1ull << 31)) return MVS_ERR_TOO_LARGE;
-        uint64_t nchunks = 1;
-        if (n > g.cap) {
-            uint64_t k = (n + g.cap - 1) / g.cap;
-            uint64_t per = (n + k - 1) / k;
-            per = (per + g.quantum - 1) / g.quantum * g.quantum;
-            nchunks = (n + per - 1) / per;
-        }
+        uint64_t nchunks, per;
+        ch.split(n, nchunks, per);
         pc.tasks += nchunks * static_cast<uint64_t>(g.passes);
         if (nchunks > 1) {
             pc.reduce += 1;
@@ -194,22 +234,17 @@ int count_plan(const uint64_t* offsets, int64_t s0, int64_t s1, const Geometry& 
     return MVS_OK;
 }
 
-// Second pass: emit.  `hash_base` is subtracted from the CSR offsets (index of the first
-// hash present in the device array), `row_base` from the sample index (first output row).
+// Second pass: emit (same Chunker state as the first pass, so the same cuts).  `hash_base` is subtracted from the CSR
+// offsets (index of the first hash present in the device array), `row_base` from the sample index (first output row).
 void emit_plan(const uint64_t* offsets, int64_t s0, int64_t s1, uint64_t hash_base, int64_t row_base,
-               const Geometry& g, WarpTask* tasks, ReduceItem* reduce)
+               const Geometry& g, Chunker ch, WarpTask* tasks, ReduceItem* reduce)
 {
     uint64_t ti = 0, ri = 0, prow = 0;
     for (int64_t s = s0; s < s1; ++s) {
         const uint64_t n = offsets[s + 1] - offsets[s];
         const uint64_t b0 = offsets[s] - hash_base;
-        uint64_t nchunks = 1, per = n;
-        if (n > g.cap) {
-            uint64_t k = (n + g.cap - 1) / g.cap;
-            per = (n + k - 1) / k;
-            per = (per + g.quantum - 1) / g.quantum * g.quantum;
-            nchunks = (n + per - 1) / per;
-        }
+        uint64_t nchunks, per;
+        ch.split(n, nchunks, per);
         const uint32_t row = static_cast<uint32_t>(s - row_base);
         for (uint64_t c = 0; c < nchunks; ++c) {
             const uint64_t cb = c * per;
@@ -275,22 +310,33 @@ cudaError_t launch_project(const Geometry& g, cudaStream_t st, uint32_t ntasks, 
 // when rows_local, else sample 0.
 int run_range(mvs_ctx* ctx, Slot& sl, const uint64_t* d_hashes, const uint64_t* offsets, int64_t s0, int64_t s1,
               uint64_t hash_base, int64_t row_base, const Geometry& g_in, uint64_t seed, int32_t* d_out,
-              cudaStream_t st, bool record_timing)
+              cudaStream_t st, bool record_timing, cudaStream_t up = nullptr)
 {
+    // `up` (may equal st): stream that copies the plan to the device.  The device-resident entry point passes the
+    // slot's own stream, so that the copy runs while the caller's previous kernel is still busy on `st`.
+    if (!up) up = st;
     // Small batches: shrink the per-task hash cap so that the grid still fills the GPU for several
     // waves (a warp task is the unit of parallelism); large batches keep the full kMaxRounds cap.
     Geometry g = g_in;
+    const uint64_t workers = static_cast<uint64_t>(ctx->sm_count) * 24ull;                        // resident warps (6 CTAs x 4 per SM)
     {
         const uint64_t total = offsets[s1] - offsets[s0];
-        const uint64_t target_tasks = static_cast<uint64_t>(ctx->sm_count) * 24ull * 4ull;    // ~4 waves of resident warps
-        const uint64_t min_cap = 2048ull * static_cast<uint64_t>(g.S);                         // keeps the flush under ~5 %
+        const uint64_t target_tasks = workers * 4ull;                                              // ~4 waves of resident warps
+        const uint64_t min_cap = 2048ull * static_cast<uint64_t>(g.S);                             // keeps the flush under ~5 %
         uint64_t want = (total * static_cast<uint64_t>(g.passes) + target_tasks - 1) / target_tasks;
         want = (want + g.quantum - 1) / g.quantum * g.quantum;
         g.cap = std::min<uint64_t>(g.cap, std::max<uint64_t>(min_cap, want));
-        if (ctx->task_cap) g.cap = std::min<uint64_t>(g_in.cap, (ctx->task_cap + 15) / 16 * 16 * static_cast<uint64_t>(g.S));
+#ifdef MVS_EXPERIMENTS
+        if (ctx->task_cap) g.cap = std::min<uint64_t>(g_in.cap, (ctx->task_cap + 63) / 64 * 64 * static_cast<uint64_t>(g.S));
+#endif
     }
+    // the tail of the task list is cut finer (see Chunker), down to 512 rounds per lane
+    Chunker ch = make_chunker(offsets, s0, s1, g, workers, 512ull * static_cast<uint64_t>(g.S));
+#ifdef MVS_EXPERIMENTS
+    if (ctx->task_cap) ch.cap_min = ch.cap_full;                                                   // fixed caps for the sweep tool
+#endif
     PlanCounts pc;
-    int rc = count_plan(offsets, s0, s1, g, pc);
+    int rc = count_plan(offsets, s0, s1, g, ch, pc);
     if (rc != MVS_OK) return rc;
     if (pc.tasks == 0) return MVS_OK;
     if ((rc = ensure_pin(ctx, sl.h_tasks, pc.tasks * sizeof(WarpTask))) != MVS_OK) return rc;
@@ -299,14 +345,15 @@ int run_range(mvs_ctx* ctx, Slot& sl, const uint64_t* d_hashes, const uint64_t* 
     if ((rc = ensure_dev(ctx, sl.reduce, (pc.reduce + 1) * sizeof(ReduceItem))) != MVS_OK) return rc;
     if ((rc = ensure_dev(ctx, sl.partials, (pc.prows + 1) * static_cast<size_t>(g.d) * sizeof(int32_t))) != MVS_OK)
         return rc;
-    emit_plan(offsets, s0, s1, hash_base, row_base, g, static_cast<WarpTask*>(sl.h_tasks.p),
+    emit_plan(offsets, s0, s1, hash_base, row_base, g, ch, static_cast<WarpTask*>(sl.h_tasks.p),
               static_cast<ReduceItem*>(sl.h_reduce.p));
-    MVS_CUDA(ctx, cudaMemcpyAsync(sl.tasks.p, sl.h_tasks.p, pc.tasks * sizeof(WarpTask), cudaMemcpyHostToDevice, st));
+    MVS_CUDA(ctx, cudaMemcpyAsync(sl.tasks.p, sl.h_tasks.p, pc.tasks * sizeof(WarpTask), cudaMemcpyHostToDevice, up));
     if (pc.reduce)
         MVS_CUDA(ctx, cudaMemcpyAsync(sl.reduce.p, sl.h_reduce.p, pc.reduce * sizeof(ReduceItem),
-                                      cudaMemcpyHostToDevice, st));
-    MVS_CUDA(ctx, cudaEventRecord(sl.uploaded, st));
+                                      cudaMemcpyHostToDevice, up));
+    MVS_CUDA(ctx, cudaEventRecord(sl.uploaded, up));
     sl.upload_busy = true;
+    if (up != st) MVS_CUDA(ctx, cudaStreamWaitEvent(st, sl.uploaded, 0));
     cudaEvent_t* ev = ctx->ev[ctx->timing_calls % kTimingRing];
     if (record_timing) MVS_CUDA(ctx, cudaEventRecord(ev[0], st));
     MVS_CUDA(ctx, launch_project(g, st, static_cast<uint32_t>(pc.tasks), d_hashes,
@@ -555,14 +602,17 @@ int mvs_project_device(mvs_ctx* ctx, const uint64_t* d_hashes, const uint64_t* h
     if (n_samples >= 0xFFFFFFF0ll) return MVS_ERR_TOO_LARGE;
     if (!d_hashes && h_offsets[n_samples] > h_offsets[0]) return MVS_ERR_INVALID_ARG;
     MVS_CUDA(ctx, cudaSetDevice(ctx->device));
-    Slot& sl = ctx->slots[0];
-    // Only the pinned plan buffers must be free again; device buffers are protected by
-    // stream order (callers use one stream per context) and cudaFree synchronises.
+    // Calls rotate over the slots' plan buffers (pinned + device): the plan of call i is copied on the slot's own stream
+    // while the kernel of call i-1 still runs on the caller's stream, so back-to-back calls leave no copy-sized gap
+    // between kernels.  A slot is reused every kSlots calls: its previous plan copy must have left the pinned buffers
+    // (host wait), and its previous kernels must have finished with the device copy (stream wait on `done`).
+    Slot& sl = ctx->slots[ctx->device_turn++ % kSlots];
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->slots[0].stream;
     int rc = stream ? wait_upload(ctx, sl) : wait_slot(ctx, sl);
     if (rc != MVS_OK) return rc;
-    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : sl.stream;
+    if (sl.busy && sl.stream != st) MVS_CUDA(ctx, cudaStreamWaitEvent(sl.stream, sl.done, 0));
     const Geometry g = make_geometry(d);
-    rc = run_range(ctx, sl, d_hashes, h_offsets, 0, n_samples, 0, 0, g, seed, d_out, st, true);
+    rc = run_range(ctx, sl, d_hashes, h_offsets, 0, n_samples, 0, 0, g, seed, d_out, st, true, sl.stream);
     if (rc != MVS_OK) return rc;
     MVS_CUDA(ctx, cudaEventRecord(sl.done, st));
     sl.busy = true;

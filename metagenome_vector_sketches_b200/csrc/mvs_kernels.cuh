@@ -9,7 +9,7 @@
 // 64 columns) and feeds the two words into a Harley-Seal carry-save-adder tree whose
 // bit planes (weights 1,2,4,...,2^13: kPlanes = 14) live in registers; one CSA is two LOP3.  No
 // per-column add is ever issued in the loop; the planes are expanded into int32
-// columns once per warp task (<= kMaxRounds = 16368 hashes per lane).  No matrix is materialised,
+// columns once per warp task (<= kMaxRounds = 16320 hashes per lane).  No matrix is materialised,
 // no atomics are used, integer adds make every partition order bit-exact.
 //
 // Work decomposition: a *warp task* = (sample, contiguous hash range, 32-block column
@@ -57,7 +57,7 @@ constexpr int kWarpsPerCta = 4;
 __host__ __device__ constexpr int tile_hashes(int lph_log2) { return (32 >> lph_log2) * 16 > 256 ? (32 >> lph_log2) * 16 : 256; }
 constexpr int kStages = 2;
 constexpr int kPlanes = 14;                      // bit planes: counts up to 16383 per lane
-constexpr uint32_t kMaxRounds = 16368;           // hashes per lane per task (1023 groups of 16)
+constexpr uint32_t kMaxRounds = 16320;           // hashes per lane per task (255 trips of 64; 14 planes count to 16383)
 constexpr uint32_t kDirect = 0xFFFFFFFFu;
 constexpr uint64_t kGolden = 0x9e3779b97f4a7c15ULL;
 constexpr uint32_t kFold = 0x80000001u;          // passed as a kernel argument so that the multiply stays an IMAD
@@ -191,6 +191,69 @@ __device__ __forceinline__ void group16(const ulonglong2* __restrict__ sp, uint3
     csa(c16hi, Phi[3], Phi[3], eA, eB);
 }
 
+// One loop trip = TRIP consecutive Harley-Seal groups of this lane's stream (TRIP = 4, 2 or 1: as many as a tile holds,
+// at most 4).  With four groups per trip (d >= 1024) the carries of the groups meet inside the trip -- weight 16 pairwise
+// into weight 32, those into weight 64, rippled into planes 6.. -- so the loop carries no pending-carry state and has no
+// branch; shorter trips keep the pending words across trips (g = groups done so far, a multiple of TRIP).
+struct Pending { uint32_t c16lo, c16hi, c32lo, c32hi; };
+
+template <int S, bool EXACT, int TRIP>
+__device__ __forceinline__ void trip_groups(const ulonglong2* __restrict__ sp, uint32_t off, uint32_t fold,
+                                            uint32_t (&Plo)[kPlanes], uint32_t (&Phi)[kPlanes], Pending& pend, uint32_t g,
+                                            uint32_t& eacc)
+{
+    if constexpr (TRIP == 4) {
+        uint32_t c32lo[2], c32hi[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            uint32_t alo, ahi, blo, bhi;
+            group16<S, EXACT>(sp + (2 * h) * (16 * S), off, fold, Plo, Phi, alo, ahi, eacc);
+            group16<S, EXACT>(sp + (2 * h + 1) * (16 * S), off, fold, Plo, Phi, blo, bhi, eacc);
+            csa(c32lo[h], Plo[4], Plo[4], alo, blo);
+            csa(c32hi[h], Phi[4], Phi[4], ahi, bhi);
+        }
+        uint32_t c64lo, c64hi;
+        csa(c64lo, Plo[5], Plo[5], c32lo[0], c32lo[1]);
+        csa(c64hi, Phi[5], Phi[5], c32hi[0], c32hi[1]);
+        ripple<6>(Plo, c64lo);
+        ripple<6>(Phi, c64hi);
+    } else if constexpr (TRIP == 2) {
+        uint32_t alo, ahi, blo, bhi, c32lo, c32hi;
+        group16<S, EXACT>(sp, off, fold, Plo, Phi, alo, ahi, eacc);
+        group16<S, EXACT>(sp + 16 * S, off, fold, Plo, Phi, blo, bhi, eacc);
+        csa(c32lo, Plo[4], Plo[4], alo, blo);
+        csa(c32hi, Phi[4], Phi[4], ahi, bhi);
+        if ((g & 2u) == 0u) {
+            pend.c32lo = c32lo; pend.c32hi = c32hi;
+        } else {
+            uint32_t c64lo, c64hi;
+            csa(c64lo, Plo[5], Plo[5], pend.c32lo, c32lo);
+            csa(c64hi, Phi[5], Phi[5], pend.c32hi, c32hi);
+            ripple<6>(Plo, c64lo);
+            ripple<6>(Phi, c64hi);
+        }
+    } else {
+        uint32_t c16lo, c16hi;
+        group16<S, EXACT>(sp, off, fold, Plo, Phi, c16lo, c16hi, eacc);
+        if ((g & 1u) == 0u) {
+            pend.c16lo = c16lo; pend.c16hi = c16hi;
+        } else {
+            uint32_t c32lo, c32hi;
+            csa(c32lo, Plo[4], Plo[4], pend.c16lo, c16lo);
+            csa(c32hi, Phi[4], Phi[4], pend.c16hi, c16hi);
+            if ((g & 2u) == 0u) {
+                pend.c32lo = c32lo; pend.c32hi = c32hi;
+            } else {
+                uint32_t c64lo, c64hi;
+                csa(c64lo, Plo[5], Plo[5], pend.c32lo, c32lo);
+                csa(c64hi, Phi[5], Phi[5], pend.c32hi, c32hi);
+                ripple<6>(Plo, c64lo);
+                ripple<6>(Phi, c64hi);
+            }
+        }
+    }
+}
+
 __device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc, uint32_t src_bytes)
 {
     const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
@@ -214,6 +277,8 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
     constexpr int kTileHashes = tile_hashes(LPH_LOG2);
     constexpr int kGroupsPerTile = kTileHashes / (16 * S);
     static_assert(kGroupsPerTile >= 1, "a tile holds at least one group");
+    constexpr int kTrip = kGroupsPerTile >= 4 ? 4 : kGroupsPerTile;      // groups per loop trip (4, 2 or 1)
+    static_assert(kGroupsPerTile % kTrip == 0, "a tile is a whole number of trips");
 
     extern __shared__ __align__(16) uint64_t smem[];
     const int warp = threadIdx.x >> 5;
@@ -236,8 +301,8 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
     uint32_t Plo[kPlanes], Phi[kPlanes];
 #pragma unroll
     for (int p = 0; p < kPlanes; ++p) { Plo[p] = 0u; Phi[p] = 0u; }
-    uint32_t pend16lo = 0, pend16hi = 0, pend32lo = 0, pend32hi = 0;
-    uint32_t g = 0;                              // groups done (warp-uniform)
+    Pending pend{0u, 0u, 0u, 0u};
+    uint32_t g = 0;                              // groups done (warp-uniform, a multiple of kTrip)
     uint32_t eacc = 0;                           // sum of popc(hi * fold) over this lane's hashes
 
     const uint32_t ntiles = (count + kTileHashes - 1) / kTileHashes;
@@ -269,34 +334,20 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
         __syncwarp();
         const uint32_t valid = min(count - t * kTileHashes, static_cast<uint32_t>(kTileHashes));
         const uint32_t rounds = (valid + S - 1) / S;
-        const uint32_t ngroups = (rounds + 15) >> 4;           // <= kGroupsPerTile
-        for (uint32_t gi = 0; gi < ngroups; ++gi, ++g) {
-            uint32_t c16lo, c16hi;
-            if (exact) group16<S, true>(cooked + gi * (16 * S) + slot, off, fold, Plo, Phi, c16lo, c16hi, eacc);
-            else group16<S, false>(cooked + gi * (16 * S) + slot, off, fold, Plo, Phi, c16lo, c16hi, eacc);
-            if ((g & 1u) == 0u) {
-                pend16lo = c16lo; pend16hi = c16hi;
-            } else {
-                uint32_t c32lo, c32hi;
-                csa(c32lo, Plo[4], Plo[4], pend16lo, c16lo);
-                csa(c32hi, Phi[4], Phi[4], pend16hi, c16hi);
-                if ((g & 2u) == 0u) {
-                    pend32lo = c32lo; pend32hi = c32hi;
-                } else {
-                    uint32_t c64lo, c64hi;
-                    csa(c64lo, Plo[5], Plo[5], pend32lo, c32lo);
-                    csa(c64hi, Phi[5], Phi[5], pend32hi, c32hi);
-                    ripple<6>(Plo, c64lo);
-                    ripple<6>(Phi, c64hi);
-                }
-            }
+        const uint32_t ntrips = (rounds + 16 * kTrip - 1) / (16 * kTrip);   // the tile's tail is cooked zero padding
+        if (!exact) {
+            for (uint32_t ti = 0; ti < ntrips; ++ti, g += kTrip)
+                trip_groups<S, false, kTrip>(cooked + ti * (kTrip * 16 * S) + slot, off, fold, Plo, Phi, pend, g, eacc);
+        } else {                                 // 5e-4 of the tiles: plain 64-bit arithmetic, one group at a time (code size)
+#pragma unroll 1
+            for (uint32_t gi = 0; gi < ntrips * kTrip; ++gi, ++g)
+                trip_groups<S, true, 1>(cooked + gi * (16 * S) + slot, off, fold, Plo, Phi, pend, g, eacc);
         }
         __syncwarp();                            // stage and cooked tile may be overwritten next
     }
-    (void)kGroupsPerTile;
     // fold the pending carries (g = number of groups done)
-    if (g & 1u) { ripple<4>(Plo, pend16lo); ripple<4>(Phi, pend16hi); }
-    if (g & 2u) { ripple<5>(Plo, pend32lo); ripple<5>(Phi, pend32hi); }
+    if (g & 1u) { ripple<4>(Plo, pend.c16lo); ripple<4>(Phi, pend.c16hi); }
+    if (g & 2u) { ripple<5>(Plo, pend.c32lo); ripple<5>(Phi, pend.c32hi); }
 
     // padding correction: this lane consumed 16*g hashes of which `mine` were real; the
     // others were zeros whose mixer output is the per-lane constant z.

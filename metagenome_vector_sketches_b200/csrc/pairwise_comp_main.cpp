@@ -175,10 +175,12 @@ int main(int argc, char** argv)
         if (in) in >> dimension;
     }
     std::cout << "dtypeqs: " << dtype << std::endl;
-    if (dtype == "int16") {
-        std::cerr << "pairwise_comp_b200: int16 dbs are handled by the reference's pairwise_comp_optimized_16bits only" << std::endl;
-        return 2;
-    }
+    // int16 dbs (`project_everything sketch --int16`): the reference hands them to pairwise_comp_optimized_16bits
+    // (:876-879), a different tool with an older shard format (out of scope).  Here the int16 rows are
+    // widened to int32 on load and take the SAME path and writer as an int32 db: the shard files are the int32 tool's
+    // format, which query_pc_mat reads; the pairs are those the int32 tool finds on the saturated vectors.
+    const bool db_is_int16 = dtype == "int16";
+    if (db_is_int16) std::cerr << "pairwise_comp_b200: int16 db, rows widened to int32 (int32 shard format)" << std::endl;
     if (dimension <= 0) {
         std::cerr << "pairwise_comp_b200: bad dimension.txt" << std::endl;
         return 1;
@@ -209,7 +211,7 @@ int main(int argc, char** argv)
     const std::string matrix_file = a.db + "vectors.bin";
     std::ifstream vf(matrix_file, std::ios::ate | std::ios::binary);
     const int64_t file_size = vf ? static_cast<int64_t>(vf.tellg()) : 0;
-    const int total = static_cast<int>(file_size / bytes_per_vector);
+    const int total = static_cast<int>(file_size / (db_is_int16 ? bytes_per_vector / 2 : bytes_per_vector));
     std::cout << "Total vectors: " << total << std::endl;
     if (static_cast<size_t>(total) > norms_sq.size()) {
         std::cerr << "pairwise_comp_b200: vector_norms.txt has fewer lines than vectors.bin has vectors" << std::endl;
@@ -232,7 +234,17 @@ int main(int argc, char** argv)
         return 1;
     }
     vf.seekg(0);
-    vf.read(reinterpret_cast<char*>(db.get()), static_cast<std::streamsize>(db_count * sizeof(int32_t)));
+    if (db_is_int16) {                                                 // read into the upper half, widen front to back
+        char* half = reinterpret_cast<char*>(db.get()) + db_count * sizeof(int16_t);
+        vf.read(half, static_cast<std::streamsize>(db_count * sizeof(int16_t)));
+        for (size_t k = 0; k < db_count; ++k) {
+            int16_t v;
+            std::memcpy(&v, half + k * sizeof(int16_t), sizeof v);
+            db[k] = v;
+        }
+    } else {
+        vf.read(reinterpret_cast<char*>(db.get()), static_cast<std::streamsize>(db_count * sizeof(int32_t)));
+    }
     vf.close();
     const double read_s = since(t0);
 

@@ -310,6 +310,25 @@ def test_pairwise_cli_feeds_query_pc_mat_kat4(tmp_path, toy_hash_file):
     assert _neighbours(r.stdout) == _neighbours(golden["stdout"])
 
 
+def test_pairwise_cli_accepts_an_int16_db(tmp_path, toy_hash_file):
+    """`sketch --int16` writes a db our own all-pairs tool must be able to read (the reference routes such dbs to its
+    older 16-bit tool): the rows are widened on load, so without saturation the shard files equal the int32 db's."""
+    if not os.path.exists(PWB):
+        pytest.skip("pairwise_comp_b200 not prebuilt")
+    outs = {}
+    for tag, extra in (("i32", []), ("i16", ["--int16"])):
+        db = tmp_path / ("db_" + tag)
+        assert run([PE, "sketch", toy_hash_file, str(db), "-d", "2048", "--quiet"] + extra).returncode == 0
+        mat = tmp_path / ("mat_" + tag)
+        mat.mkdir()
+        r = run([PWB, "--db", str(db) + "/", "--output_folder", str(mat) + "/", "--max_memory_gb", "12", "--num_threads", "1",
+                 "--num_shards", "1", "--shard_idx", "0"])
+        assert r.returncode == 0, r.stderr
+        outs[tag] = {f: (mat / "shard_0" / f).read_bytes() for f in SHARD_FILES}
+    assert (tmp_path / "db_i16" / "dtype.txt").read_text() == "int16\n"
+    assert outs["i16"] == outs["i32"] and len(outs["i32"]["matrix.bin"]) > 8
+
+
 def test_pairwise_cli_grammar(tmp_path):
     if not os.path.exists(PWB):
         pytest.skip("pairwise_comp_b200 not prebuilt")

@@ -495,6 +495,103 @@ __global__ void __launch_bounds__(256) mix_kernel(uint32_t* sink, int iters, uin
     if (x == 0x12345u) sink[0] = x;
 }
 
+// ---- the projection loop's own instruction mix without its data dependencies -------------------------------------
+// Per (hash, lane) round the product kernel issues 9 LOP3, 3 SHF, 5 IMAD, 3 IMAD.IADD, 2 IMAD.WIDE, 1 POPC, 1 LDS.128
+// (+ ~1 of loop overhead): profiles/r02a_project_kernel_ncu_full.txt.  loopmix_kernel issues exactly that mix on 4
+// independent register sets per thread, so the time per round is what the issue ports / pipes allow for this mix when
+// no instruction ever waits for an operand.  DROP bits remove one ingredient (1: WIDE -> IMAD, 2: no POPC, 4: no LDS,
+// 8: IMAD.IADD -> nothing, 16: 3 fewer LOP3) to price it.
+template <int DROP>
+__global__ void __launch_bounds__(128) loopmix_kernel(uint32_t* sink, int iters, uint32_t k0, uint32_t k1, uint32_t one)
+{
+    __shared__ uint4 tab[64];
+    if (threadIdx.x < 64) tab[threadIdx.x] = make_uint4(threadIdx.x * k0, k1, k0 ^ threadIdx.x, k1 + threadIdx.x);
+    __syncthreads();
+    uint32_t a[4], b[4], c[4], e[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { a[i] = threadIdx.x * 2654435761u + i * k0 + blockIdx.x; b[i] = a[i] ^ k1; c[i] = a[i] + k0; e[i] = i; }
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            uint4 t = make_uint4(k0, k1, k0, k1);
+            if (!(DROP & 4)) t = tab[(it + i) & 63];                                      // LDS.128, warp-uniform address
+            asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(a[i]) : "r"(one), "r"(a[i]), "r"(t.x));   // IMAD.IADD (lane add)
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(t.y), "r"(k0));          // ^ F
+            asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(b[i]) : "r"(a[i]), "r"(k1), "r"(t.w));    // l1 * K1hi + M
+            if (DROP & 1) {
+                asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(c[i]) : "r"(a[i]), "r"(k0), "r"(c[i]));
+            } else {
+                unsigned long long w;
+                asm volatile("mul.wide.u32 %0, %1, %2;" : "=l"(w) : "r"(a[i]), "r"(k0));   // IMAD.WIDE
+                a[i] = static_cast<uint32_t>(w);
+                c[i] = static_cast<uint32_t>(w >> 32);
+            }
+            if (!(DROP & 8)) asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(c[i]) : "r"(one), "r"(c[i]), "r"(b[i]));  // hi + t
+            asm volatile("shf.r.wrap.b32 %0, %1, %2, 27;" : "=r"(b[i]) : "r"(a[i]), "r"(c[i]));       // funnel 27
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(b[i]), "r"(k1));
+            asm volatile("shf.r.clamp.b32 %0, %1, %2, 27;" : "=r"(b[i]) : "r"(c[i]), "r"(k0));        // hi >> 27
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(c[i]) : "r"(b[i]), "r"(k0));
+            asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(b[i]) : "r"(c[i]), "r"(k0), "r"(k1));     // yh * K2lo
+            asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(b[i]) : "r"(a[i]), "r"(k1), "r"(b[i]));   // + yl * K2hi
+            if (DROP & 1) {
+                asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(c[i]) : "r"(a[i]), "r"(k1), "r"(c[i]));
+            } else {
+                unsigned long long w;
+                asm volatile("mul.wide.u32 %0, %1, %2;" : "=l"(w) : "r"(a[i]), "r"(k1));
+                a[i] = static_cast<uint32_t>(w);
+                c[i] = static_cast<uint32_t>(w >> 32);
+            }
+            if (!(DROP & 8)) asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(c[i]) : "r"(one), "r"(c[i]), "r"(b[i]));
+            asm volatile("shf.r.wrap.b32 %0, %1, %2, 31;" : "=r"(b[i]) : "r"(a[i]), "r"(c[i]));       // funnel 31
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(b[i]), "r"(k1));
+            if (!(DROP & 2)) {
+                uint32_t p;
+                asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(p) : "r"(c[i]), "r"(k0), "r"(k1));    // hi * fold
+                asm volatile("popc.b32 %0, %0;" : "+r"(p));
+                if (!(DROP & 8)) asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(e[i]) : "r"(one), "r"(e[i]), "r"(p));
+                else e[i] ^= p;
+            }
+            // carry-save tree: ~4.5 LOP3 per round on two words
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(b[i]) : "r"(a[i]), "r"(c[i]));
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0xE8;" : "+r"(e[i]) : "r"(a[i]), "r"(c[i]));
+            if (!(DROP & 16)) {
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(b[i]) : "r"(e[i]), "r"(k0));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0xE8;" : "+r"(e[i]) : "r"(b[i]), "r"(k1));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(c[i]) : "r"(b[i]), "r"(e[i]));
+            }
+        }
+    }
+    uint32_t x = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) x ^= a[i] ^ b[i] ^ c[i] ^ e[i];
+    if (x == 0x12345u) sink[0] = x;
+}
+
+template <int DROP>
+void run_loopmix(const char* name)
+{
+    uint32_t* sink = reinterpret_cast<uint32_t*>(d_acc);
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    const int iters = 4096;
+    for (int ctas = 4; ctas <= 8; ctas += 2) {   // resident CTAs of 128 threads per SM: 4, 6 (the product's), 8 warps per scheduler
+        float best = 1e30f;
+        for (int rep = 0; rep < 4; ++rep) {
+            CK(cudaEventRecord(e0));
+            loopmix_kernel<DROP><<<148 * ctas, 128>>>(sink, iters, 0x9e3779b9u, 0x85ebca6bu, 1u);
+            CK(cudaEventRecord(e1));
+            CK(cudaEventSynchronize(e1));
+            float ms;
+            CK(cudaEventElapsedTime(&ms, e0, e1));
+            if (rep > 0 && ms < best) best = ms;
+        }
+        const double rounds = 148.0 * ctas * 4 /*warps*/ * iters * 4.0;        // (hash, lane) rounds per launch, all SMs
+        const double clk = best * 1e-3 * 1.965e9 * 592.0;
+        printf("loopmix %-34s drop=%2d  %d warps/scheduler  %7.3f ms  %6.2f clk per round\n", name, DROP, ctas, best, clk / rounds);
+    }
+}
+
 template <int MODE>
 void run_mix(const char* name, int per_iter)
 {
@@ -578,6 +675,15 @@ int main(int argc, char** argv)
         run_mix<6>("FFMA : LOP3 1:1", 2);
         run_mix<7>("FFMA : LOP3 : IMAD 1:1:1", 3);
         run_mix<8>("LOP3 IMAD LOP3 IMAD SHF", 5);
+    }
+    if (argc > 4) {
+        run_loopmix<0>("full mix");
+        run_loopmix<1>("WIDE -> IMAD");
+        run_loopmix<2>("no POPC (+IMAD)");
+        run_loopmix<4>("no LDS");
+        run_loopmix<8>("no IMAD.IADD");
+        run_loopmix<16>("3 LOP3 fewer");
+        run_loopmix<1 + 2 + 4>("no WIDE, POPC, LDS");
     }
 #include "variants.inc"
     return 0;
