@@ -242,7 +242,10 @@ def run_gpu(args):
     dh, off = syn.uniform_batch_torch(n, per, dev, seed=0, first_sample=rank * n)
     dout = torch.zeros((n, d), dtype=torch.int32, device=dev)
     total = n * per
-    stream = torch.cuda.current_stream().cuda_stream
+    # a real stream: stream 0 (torch's default) means "the context's own stream, synchronous" to mvs_project_device
+    tstream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
 
     def step_device():
         sk.project_device(dh.data_ptr(), off, d, dout.data_ptr(), seed=0, stream=stream)

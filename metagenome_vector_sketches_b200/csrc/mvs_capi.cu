@@ -163,7 +163,7 @@ Geometry make_geometry(int d)
     g.S = 32 >> g.lph_log2;
     // one trip = up to four Harley-Seal groups of 16 rounds for all S hash slots, never more than a staging tile
     g.quantum = std::min<uint32_t>(64u * static_cast<uint32_t>(g.S), static_cast<uint32_t>(mvs::tile_hashes(g.lph_log2)));
-    g.cap = static_cast<uint64_t>(mvs::kMaxRounds) * static_cast<uint64_t>(g.S);
+    g.cap = static_cast<uint64_t>(mvs::max_rounds(g.lph_log2)) * static_cast<uint64_t>(g.S);
     return g;
 }
 
@@ -182,6 +182,7 @@ struct Chunker {
 
     uint64_t cap_now() const
     {
+        if (remaining >= workers * cap_full) return cap_full;           // more than one full wave left
         uint64_t c = remaining / (2 * workers);
         c = c / quantum * quantum;
         return std::min(cap_full, std::max(cap_min, c));

@@ -58,6 +58,14 @@ __host__ __device__ constexpr int tile_hashes(int lph_log2) { return (32 >> lph_
 constexpr int kStages = 2;
 constexpr int kPlanes = 14;                      // bit planes: counts up to 16383 per lane
 constexpr uint32_t kMaxRounds = 16320;           // hashes per lane per task (255 trips of 64; 14 planes count to 16383)
+// The flush adds the S hash slots of a warp as PACKED pairs of 16-bit column counts, so a task may hold at most
+// 65535 hashes per 64-column block: rounds per lane <= 65535 / S, a multiple of 64 (S = 32: of 16, one group per trip).
+__host__ __device__ constexpr uint32_t max_rounds(int lph_log2)
+{
+    const uint32_t S = 32u >> lph_log2;
+    const uint32_t r = (65535u / S) / 64u * 64u;
+    return r < kMaxRounds ? r : kMaxRounds;
+}
 constexpr uint32_t kDirect = 0xFFFFFFFFu;
 constexpr uint64_t kGolden = 0x9e3779b97f4a7c15ULL;
 constexpr uint32_t kFold = 0x80000001u;          // passed as a kernel argument so that the multiply stays an IMAD
@@ -254,6 +262,26 @@ __device__ __forceinline__ void trip_groups(const ulonglong2* __restrict__ sp, u
     }
 }
 
+// Bit planes -> column counts.  A[p] = plane p (weight 2^p) of 32 columns, A[14] = A[15] = 0.  A 16 x 16 bit-matrix
+// transpose carried out in both 16-bit halves of the words at once (four butterfly stages of 8 row pairs; one stage of
+// a pair = 2 shifts + 2 bit-selects) leaves  A[c] = count(column c) | count(column 16 + c) << 16 : 128 instructions for
+// 32 columns instead of 3 per (column, plane).
+__device__ __forceinline__ void planes_to_packed_counts(uint32_t (&A)[16])
+{
+#pragma unroll
+    for (int stage = 0; stage < 4; ++stage) {
+        const int j = 8 >> stage;
+        const uint32_t m = stage == 0 ? 0x00FF00FFu : stage == 1 ? 0x0F0F0F0Fu : stage == 2 ? 0x33333333u : 0x55555555u;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            if (k & j) continue;
+            const uint32_t lo = A[k], hi = A[k + j];
+            A[k] = (lo & m) | ((hi << j) & ~m);
+            A[k + j] = (hi & ~m) | ((lo >> j) & m);
+        }
+    }
+}
+
 __device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc, uint32_t src_bytes)
 {
     const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
@@ -372,35 +400,51 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
 #pragma unroll
     for (int p = 0; p < kPlanes; ++p) col32 -= static_cast<uint32_t>(__popc(Phi[p] & 0x7FFFFFFFu)) << p;
 
+    // planes -> packed counts: A[c] = columns c | 16 + c of the low word, B[c] = columns 32 + c | 48 + c
+    uint32_t A[16], B[16];
 #pragma unroll
-    for (int w = 0; w < 2; ++w) {
+    for (int p = 0; p < 16; ++p) {
+        A[p] = p < kPlanes ? Plo[p] : 0u;
+        B[p] = p < kPlanes ? Phi[p] : 0u;
+    }
+    planes_to_packed_counts(A);
+    planes_to_packed_counts(B);
+    B[0] = (B[0] & 0xFFFF0000u) | col32;
+    if (__any_sync(0xffffffffu, npad != 0u)) {   // only the last chunk of a sample is padded
 #pragma unroll
-        for (int jq = 0; jq < 8; ++jq) {
-            int32_t v[4];
+        for (int c = 0; c < 16; ++c) {
+            A[c] -= npad * ((zlo >> c) & 0x00010001u);
+            B[c] -= npad * ((zhi >> c) & 0x00010001u);
+        }
+    }
+    // fold the S hash slots (packed adds: a task holds at most 65535 hashes per block, see max_rounds)
 #pragma unroll
-            for (int jj = 0; jj < 4; ++jj) {
-                const int j = jq * 4 + jj;
-                uint32_t val = 0;
+    for (int m = LPH; m < 32; m <<= 1) {
 #pragma unroll
-                for (int p = 0; p < kPlanes; ++p) {
-                    const uint32_t plane = w ? Phi[p] : Plo[p];
-                    val |= ((plane >> j) & 1u) << p;
+        for (int c = 0; c < 16; ++c) {
+            A[c] += __shfl_xor_sync(0xffffffffu, A[c], m);
+            B[c] += __shfl_xor_sync(0xffffffffu, B[c], m);
+        }
+    }
+    if (writer) {
+#pragma unroll
+        for (int part = 0; part < 4; ++part) {   // columns [16 * part, 16 * part + 16) of the block
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                int32_t v[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t w = (part & 2) ? B[4 * q + i] : A[4 * q + i];
+                    const uint32_t val = (part & 1) ? (w >> 16) : (w & 0xFFFFu);
+                    v[i] = direct ? (n_total - 2 * static_cast<int32_t>(val)) : static_cast<int32_t>(val);
                 }
-                if (w == 1 && j == 0) val = col32;
-                const uint32_t zbit = ((w ? zhi : zlo) >> j) & 1u;
-                val -= npad * zbit;
-#pragma unroll
-                for (int m = LPH; m < 32; m <<= 1) val += __shfl_xor_sync(0xffffffffu, val, m);
-                v[jj] = direct ? (n_total - 2 * static_cast<int32_t>(val)) : static_cast<int32_t>(val);
-            }
-            if (writer) {
-                const int col = blk * 64 + w * 32 + jq * 4;
+                const int col = blk * 64 + part * 16 + q * 4;
                 if (vec4) {
                     if (col < d) *reinterpret_cast<int4*>(row + col) = make_int4(v[0], v[1], v[2], v[3]);
                 } else {
 #pragma unroll
-                    for (int jj = 0; jj < 4; ++jj)
-                        if (col + jj < d) row[col + jj] = v[jj];
+                    for (int i = 0; i < 4; ++i)
+                        if (col + i < d) row[col + i] = v[i];
                 }
             }
         }

@@ -188,10 +188,14 @@ __device__ __forceinline__ void mix_cooked(ulonglong2 c, uint64_t rawv, uint32_t
     const uint32_t yhi = hi ^ (hi >> 27);
     mul64<V>(ylo, yhi, 0x133111ebu, 0x94d049bbu, lo, hi);
     olo = lo ^ __funnelshift_r(lo, hi, 31);
-    uint32_t t;
-    asm("mul.lo.u32 %0, %1, %2;" : "=r"(t) : "r"(hi), "r"(kc.m2 * 0x40000000u + 1u));
-    eacc += __popc(t);
-    ohi = hi;
+    if constexpr (V & 64) {
+        uint32_t t;
+        asm("mul.lo.u32 %0, %1, %2;" : "=r"(t) : "r"(hi), "r"(kc.m2 * 0x40000000u + 1u));
+        eacc += __popc(t);
+        ohi = hi;
+    } else {
+        ohi = hi ^ (hi >> 31);                   // the plain last xor-shift: SHF + LOP3 on the ALU pipe
+    }
 }
 
 template <int V, bool EXACT>

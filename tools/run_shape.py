@@ -28,7 +28,9 @@ def main():
     sk = mvs.Sketcher(0)
     dh, off = syn.uniform_batch_torch(a.samples, a.per, dev, seed=0)
     dout = torch.empty((a.samples, a.d), dtype=torch.int32, device=dev)
-    stream = torch.cuda.current_stream().cuda_stream
+    ts = torch.cuda.Stream(device=dev)           # stream 0 would make every call synchronous (the context's own stream)
+    torch.cuda.set_stream(ts)
+    stream = ts.cuda_stream
     for _ in range(3):
         sk.project_device(dh.data_ptr(), off, a.d, dout.data_ptr(), stream=stream)
     torch.cuda.synchronize()
