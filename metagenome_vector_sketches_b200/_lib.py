@@ -120,7 +120,7 @@ def load_experiments_library():
     """The experiment build (make -C csrc experiments), for tools/ and tests/test_gpu_experiments.py only."""
     global _explib
     if _explib is None:
-        path = os.path.join(_HERE, _EXPLIBNAME)
+        path = os.environ.get("MVS_EXP_LIB") or os.path.join(_HERE, _EXPLIBNAME)
         if not os.path.exists(path):
             raise ImportError("%s is not built: make -C metagenome_vector_sketches_b200/csrc experiments" % path)
         _explib = _bind(path)

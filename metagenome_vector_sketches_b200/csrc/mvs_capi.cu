@@ -13,6 +13,7 @@
 #include "mvs_internal.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -161,7 +162,8 @@ Geometry make_geometry(int d)
         g.passes = 1;
     }
     g.S = 32 >> g.lph_log2;
-    // one trip = up to four Harley-Seal groups of 16 rounds for all S hash slots, never more than a staging tile
+    // chunk sizes are multiples of 64 rounds (a multiple of the kernel's loop trip of one or two Harley-Seal groups of 16
+    // rounds for all S hash slots), never more than a staging tile
     g.quantum = std::min<uint32_t>(64u * static_cast<uint32_t>(g.S), static_cast<uint32_t>(mvs::tile_hashes(g.lph_log2)));
     g.cap = static_cast<uint64_t>(mvs::max_rounds(g.lph_log2)) * static_cast<uint64_t>(g.S);
     return g;
@@ -172,25 +174,13 @@ struct PlanCounts {
 };
 
 // How a batch is cut into warp tasks.  A sample larger than the cap is split into equal chunks (multiples of the
-// kernel's trip quantum).  The cap is NOT constant over the batch: tasks are launched in list order onto `workers`
-// resident warps, and equal-size tasks would leave the last wave mostly empty (config 3: 7168 tasks on 3552 warps =
-// 2.02 waves).  So the cap shrinks towards the end of the list like guided self-scheduling -- a task is at most
-// half of what would be left per worker -- down to `cap_min`; the tail of the launch is then made of short tasks.
+// kernel's trip quantum); the cap is chosen per launch by choose_cap below.
 struct Chunker {
-    uint64_t cap_full, cap_min, quantum, workers, passes;
-    uint64_t remaining;                          // hashes x passes not yet planned
+    uint64_t cap, quantum;
 
-    uint64_t cap_now() const
-    {
-        if (remaining >= workers * cap_full) return cap_full;           // more than one full wave left
-        uint64_t c = remaining / (2 * workers);
-        c = c / quantum * quantum;
-        return std::min(cap_full, std::max(cap_min, c));
-    }
     // chunks of a sample of n hashes: count and size
-    void split(uint64_t n, uint64_t& nchunks, uint64_t& per)
+    void split(uint64_t n, uint64_t& nchunks, uint64_t& per) const
     {
-        const uint64_t cap = cap_now();
         nchunks = 1;
         per = n;
         if (n > cap) {
@@ -199,24 +189,65 @@ struct Chunker {
             per = (per + quantum - 1) / quantum * quantum;
             nchunks = (n + per - 1) / per;
         }
-        remaining -= std::min(remaining, n * passes);
     }
 };
 
-Chunker make_chunker(const uint64_t* offsets, int64_t s0, int64_t s1, const Geometry& g, uint64_t workers, uint64_t cap_min)
+uint64_t count_tasks(const uint64_t* offsets, int64_t s0, int64_t s1, const Chunker& ch)
 {
-    Chunker c;
-    c.cap_full = g.cap;
-    c.quantum = g.quantum;
-    c.cap_min = std::min(g.cap, std::max<uint64_t>(cap_min / g.quantum * g.quantum, g.quantum));
-    c.workers = std::max<uint64_t>(workers, 1);
-    c.passes = static_cast<uint64_t>(g.passes);
-    c.remaining = (offsets[s1] - offsets[s0]) * c.passes;
-    return c;
+    uint64_t tasks = 0;
+    for (int64_t s = s0; s < s1; ++s) {
+        const uint64_t n = offsets[s + 1] - offsets[s];
+        tasks += n > ch.cap ? (n + ch.cap - 1) / ch.cap : 1;             // == nchunks of split() up to quantum rounding
+    }
+    return tasks;
+}
+
+// The per-launch task cap (hashes).  Large launches take the largest task the bit planes allow (fewest flushes and
+// partial rows).  Small launches are quantised by the machine: CTAs of kWarpsPerCta tasks are spread over the SMs, an
+// SM shares its issue slots evenly among its resident warps, so with equal tasks the launch lasts as long as the SM
+// that received the most CTAs -- time ~ ceil(CTAs / SMs) x (task + fixed cost per task).  Measured on config 3 at
+// d = 256 (1024 x 100 000 hashes, profiles/r02e_ab_kernel.jsonl): 3072 / 4096 / 7168 tasks = 6 / 7 / 13 CTAs on the
+// busiest SM run 0.60 / 0.52 / 0.53 ms, exactly this model.  So candidates on a geometric grid between 512 rounds and
+// the maximum are scored with it and the best one wins; launches with >= 64 CTAs per SM skip the search.
+uint64_t choose_cap(const uint64_t* offsets, int64_t s0, int64_t s1, const Geometry& g, int sm_count)
+{
+    const uint64_t cap_max = g.cap;
+    const uint64_t cap_min = std::min(cap_max, std::max<uint64_t>(512ull * g.S / g.quantum * g.quantum, g.quantum));
+    const uint64_t total = offsets[s1] - offsets[s0];
+    if (total == 0) return cap_max;
+    const double fixed = 96.0 * g.S;                                    // flush + start-up of a task, in hashes (~96 rounds)
+    const double sms = static_cast<double>(sm_count);
+    auto score = [&](uint64_t cap, uint64_t tasks) {
+        const double ctas = std::ceil(static_cast<double>(tasks) * g.passes / mvs::kWarpsPerCta);
+        const double per_sm = ctas / sms;
+        const double avg = static_cast<double>(total) / static_cast<double>(tasks);
+        return std::ceil(per_sm) / per_sm * (1.0 + fixed / avg);        // relative to perfectly divisible work
+    };
+    Chunker ch{cap_max, g.quantum};
+    const uint64_t tasks_max = count_tasks(offsets, s0, s1, ch);
+    if (static_cast<double>(tasks_max) * g.passes / mvs::kWarpsPerCta >= 64.0 * sms) return cap_max;
+    uint64_t best_cap = cap_max;
+    double best = score(cap_max, tasks_max);
+    constexpr int kGrid = 32;
+    const double ratio = static_cast<double>(cap_max) / static_cast<double>(cap_min);
+    uint64_t prev = cap_max;
+    for (int i = 1; i <= kGrid; ++i) {
+        uint64_t cap = static_cast<uint64_t>(static_cast<double>(cap_max) / std::pow(ratio, static_cast<double>(i) / kGrid));
+        cap = std::max(cap_min, cap / g.quantum * g.quantum);
+        if (cap == prev) continue;
+        prev = cap;
+        ch.cap = cap;
+        const double sc = score(cap, count_tasks(offsets, s0, s1, ch));
+        if (sc < best * 0.995) {                                        // prefer the larger cap on ties
+            best = sc;
+            best_cap = cap;
+        }
+    }
+    return best_cap;
 }
 
 // First pass: how many tasks / reduce items / partial rows does [s0, s1) need?
-int count_plan(const uint64_t* offsets, int64_t s0, int64_t s1, const Geometry& g, Chunker ch, PlanCounts& pc)
+int count_plan(const uint64_t* offsets, int64_t s0, int64_t s1, const Geometry& g, const Chunker& ch, PlanCounts& pc)
 {
     pc = PlanCounts{};
     for (int64_t s = s0; s < s1; ++s) {
@@ -235,10 +266,10 @@ int count_plan(const uint64_t* offsets, int64_t s0, int64_t s1, const Geometry& 
     return MVS_OK;
 }
 
-// Second pass: emit (same Chunker state as the first pass, so the same cuts).  `hash_base` is subtracted from the CSR
+// Second pass: emit.  `hash_base` is subtracted from the CSR
 // offsets (index of the first hash present in the device array), `row_base` from the sample index (first output row).
 void emit_plan(const uint64_t* offsets, int64_t s0, int64_t s1, uint64_t hash_base, int64_t row_base,
-               const Geometry& g, Chunker ch, WarpTask* tasks, ReduceItem* reduce)
+               const Geometry& g, const Chunker& ch, WarpTask* tasks, ReduceItem* reduce)
 {
     uint64_t ti = 0, ri = 0, prow = 0;
     for (int64_t s = s0; s < s1; ++s) {
@@ -316,25 +347,10 @@ int run_range(mvs_ctx* ctx, Slot& sl, const uint64_t* d_hashes, const uint64_t* 
     // `up` (may equal st): stream that copies the plan to the device.  The device-resident entry point passes the
     // slot's own stream, so that the copy runs while the caller's previous kernel is still busy on `st`.
     if (!up) up = st;
-    // Small batches: shrink the per-task hash cap so that the grid still fills the GPU for several
-    // waves (a warp task is the unit of parallelism); large batches keep the full kMaxRounds cap.
-    Geometry g = g_in;
-    const uint64_t workers = static_cast<uint64_t>(ctx->sm_count) * 24ull;                        // resident warps (6 CTAs x 4 per SM)
-    {
-        const uint64_t total = offsets[s1] - offsets[s0];
-        const uint64_t target_tasks = workers * 4ull;                                              // ~4 waves of resident warps
-        const uint64_t min_cap = 2048ull * static_cast<uint64_t>(g.S);                             // keeps the flush under ~5 %
-        uint64_t want = (total * static_cast<uint64_t>(g.passes) + target_tasks - 1) / target_tasks;
-        want = (want + g.quantum - 1) / g.quantum * g.quantum;
-        g.cap = std::min<uint64_t>(g.cap, std::max<uint64_t>(min_cap, want));
+    const Geometry& g = g_in;
+    Chunker ch{choose_cap(offsets, s0, s1, g, ctx->sm_count), g.quantum};
 #ifdef MVS_EXPERIMENTS
-        if (ctx->task_cap) g.cap = std::min<uint64_t>(g_in.cap, (ctx->task_cap + 63) / 64 * 64 * static_cast<uint64_t>(g.S));
-#endif
-    }
-    // the tail of the task list is cut finer (see Chunker), down to 512 rounds per lane
-    Chunker ch = make_chunker(offsets, s0, s1, g, workers, 512ull * static_cast<uint64_t>(g.S));
-#ifdef MVS_EXPERIMENTS
-    if (ctx->task_cap) ch.cap_min = ch.cap_full;                                                   // fixed caps for the sweep tool
+    if (ctx->task_cap) ch.cap = std::min<uint64_t>(g.cap, (ctx->task_cap + 63) / 64 * 64 * static_cast<uint64_t>(g.S));   // fixed caps for the sweep tools
 #endif
     PlanCounts pc;
     int rc = count_plan(offsets, s0, s1, g, ch, pc);

@@ -305,7 +305,13 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
     constexpr int kTileHashes = tile_hashes(LPH_LOG2);
     constexpr int kGroupsPerTile = kTileHashes / (16 * S);
     static_assert(kGroupsPerTile >= 1, "a tile holds at least one group");
-    constexpr int kTrip = kGroupsPerTile >= 4 ? 4 : kGroupsPerTile;      // groups per loop trip (4, 2 or 1)
+    // groups per loop trip: 2 when a tile holds at least 4 groups (d >= 512), else 1.  Measured on the full kernel
+    // (profiles/r02e_ab_kernel.jsonl, same task caps): config 2 14.61 ms with 2, 14.66 with 1, 16.68 with 4 -- the four-group
+    // body that wins by 2 % in the isolated loop (tools/kexp) loses 13 % here; d = 256 prefers 1 (0.517 vs 0.528 ms).
+#ifndef MVS_TRIP_MAX
+#define MVS_TRIP_MAX 2
+#endif
+    constexpr int kTrip = kGroupsPerTile >= 4 ? (MVS_TRIP_MAX < 4 ? MVS_TRIP_MAX : 4) : 1;
     static_assert(kGroupsPerTile % kTrip == 0, "a tile is a whole number of trips");
 
     extern __shared__ __align__(16) uint64_t smem[];
