@@ -59,8 +59,8 @@ def load_kernel_profile(n, per, d):
     key = projection_cubin_key()
     if key is None:
         return None, "cubin key unavailable (cuobjdump missing)"
-    if key != prof.get("cubin_sha256"):
-        return None, "stale: profile is of cubin %s..., library is %s..." % (str(prof.get("cubin_sha256"))[:12], key[:12])
+    if key != prof.get("kernel_sass_sha256"):
+        return None, "stale: profile is of cubin %s..., library is %s..." % (str(prof.get("kernel_sass_sha256"))[:12], key[:12])
     if prof.get("workload") != "%dx%dx%d" % (n, per, d):
         return None, "profile is of workload %s" % prof.get("workload")
     return prof, "cubin %s..., %s" % (key[:12], prof.get("source"))
@@ -310,6 +310,30 @@ def run_gpu(args):
     if checksum_host != checksum_dev:
         raise SystemExit("bench: device-resident and host paths disagree (%d vs %d)" % (checksum_dev, checksum_host))
 
+    # ---- the same batch through mvs_sketch_batch_packed56: 7 bytes per hash on the host link (all synthetic hashes
+    # are < 2^54, like FracMinHash hashes at scaled = 1000).  Packing is the producer's job (a parser would emit it
+    # directly); its cost here is reported, not timed into the step.  N = 1 only (another 3.5 GB of pinned memory).
+    packed_ms = pack_s = None
+    if world == 1 and not args.no_packed:
+        pk = torch.empty(7 * total, dtype=torch.uint8, pin_memory=True)
+        pk_np = pk.numpy()
+        t0 = time.perf_counter()
+        mvs.pack56(h_np, out=pk_np)
+        pack_s = time.perf_counter() - t0
+        for _ in range(2):
+            sk.project_csr_packed56(pk_np, off, d, out=out_np)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            sk.project_csr_packed56(pk_np, off, d, out=out_np)
+        torch.cuda.synchronize()
+        packed_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+        tp = sk.timing()
+        packed_h2d = int(tp["h2d_bytes"])
+        if int(out_np.sum(dtype=np.int64)) != checksum_dev:
+            raise SystemExit("bench: packed56 host path disagrees with the device-resident path")
+        del pk, pk_np
+
     # ---- the same call with PAGEABLE host buffers (what a caller with a std::vector has); extra information ----
     pageable_ms = None                           # single-GPU runs only: N ranks would hold N more 4 GB host copies
     if world == 1:
@@ -474,6 +498,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--wc-input", action="store_true", help="experiment: write-combined pinned input buffer")
     ap.add_argument("--no-bind", action="store_true", help="skip mvs_bind_host_to_device (A/B of the host locality)")
+    ap.add_argument("--no-packed", action="store_true", help="skip the packed56 end-to-end leg (N = 1)")
     ap.add_argument("--no-config3", action="store_true", help="skip the BASELINE configs[2] dimension sweep (N = 1 leg)")
     ap.add_argument("--c4-samples", type=int, default=100000,
                     help="samples of the BASELINE configs[3] heavy-tailed leg (0 = skip; 100000 = the full config)")
@@ -538,6 +563,20 @@ def main():
                 "frac": alg_bytes / k_s / 1e9 / hbm_peak, "peak_how": hbm_how,
                 "algorithmic_bytes_per_launch": alg_bytes},
     }
+    # Mix limit: the loop's own opcode mix without data dependencies (mvs_loop_mix_peak, live).  One warp round = one
+    # hash x 32 lanes = 2048 columns, so a launch of this workload is `total * ceil(d/2048)` rounds.
+    mix_rounds_per_s = sk.loop_mix_peak()
+    rounds_per_launch = total * ((d + 2047) // 2048) if d >= 2048 else None
+    if rounds_per_launch:
+        roofline["mix_limit"] = {
+            "achieved": rounds_per_launch / k_s / 1e9, "peak": mix_rounds_per_s / 1e9, "unit": "Gwarp-round/s",
+            "frac": rounds_per_launch / k_s / mix_rounds_per_s,
+            "clk_per_round": {"kernel": 4.0 * sm_count * clk_mhz * 1e6 * k_s / rounds_per_launch,
+                              "mix_without_dependencies": 4.0 * sm_count * clk_mhz * 1e6 / mix_rounds_per_s},
+            "how": "live microbenchmark mvs_loop_mix_peak: the projection loop's opcodes in the same proportions (8.5 LOP3, "
+                   "3 SHF, 4 IMAD, 3 IMAD add, 2 IMAD.WIDE, 1 POPC, 1 LDS.128 per round) on independent registers at the "
+                   "same residency -- what the issue ports and integer pipes sustain for this mix; the kernel sits on it, so "
+                   "the idle issue slots of `frac` are the machine's for this mix, not stalls of the kernel (DESIGN.md 4)"}
     if g["config3"] is not None:
         for row in g["config3"]["rows"]:
             row["frac_algorithmic"] = row["hashes_per_s"] * work_per_hash(row["d"]) / p_int
@@ -568,6 +607,12 @@ def main():
                     "host_binding": {"how": "mvs_bind_host_to_device per rank before the pinned buffers are allocated "
                                             "(applied: 1 = CPU affinity, 2 = preferred memory node)",
                                      "per_rank_ms_node_applied": g["per_rank"]},
+                    "packed56_host_buffers": None if g["packed_ms"] is None else {
+                        "value": g["total"] / (g["packed_ms"] * 1e-3), "unit": UNIT, "ms_per_step": g["packed_ms"],
+                        "h2d_bytes_per_step": g["packed_h2d"], "pack_seconds_once": g["pack_s"],
+                        "how": "mvs_sketch_batch_packed56: the same batch as 7 little-endian bytes per hash in pinned memory "
+                               "(12.5 % fewer bytes on the PCIe link that bounds e2e), widened on the device; packing "
+                               "(mvs_pack56, host threads) happens once outside the timed steps"},
                     "pageable_host_buffers": None if g["pageable_ms"] is None else {
                         "value": g["total"] / (g["pageable_ms"] * 1e-3), "unit": UNIT, "ms_per_step": g["pageable_ms"],
                         "how": "same call, numpy (pageable) arrays in and out: the library stages them through a pinned "

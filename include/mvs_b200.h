@@ -86,6 +86,17 @@ int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offse
                      int64_t n_samples, int d, uint64_t seed, int32_t* out, int16_t* out16,
                      uint64_t* sumsq, float* ref_norms);
 
+/* The same with the CSR payload PACKED: hash k occupies bytes [7k, 7k+7) of `packed`, little endian (offsets still count
+ * hashes).  Every hash must be below 2^56 -- FracMinHash hashes are below 2^64 / scaled, i.e. below 2^56 for any
+ * scaled >= 256 (sourmash's default 1000 gives 2^54.03).  The host link carries 7 instead of 8 bytes per hash and the
+ * device widens them (unpack56_kernel): the end-to-end rate of a batch call is bounded by that link, so it rises by
+ * the same 12.5 %.  mvs_pack56 is the reference packer (MVS_ERR_INVALID_ARG if a hash does not fit; `packed` holds 7*n
+ * bytes).  The u64 entry points are untouched. */
+int mvs_sketch_batch_packed56(mvs_ctx* ctx, const unsigned char* packed, const uint64_t* offsets,
+                              int64_t n_samples, int d, uint64_t seed, int32_t* out, int16_t* out16,
+                              uint64_t* sumsq, float* ref_norms);
+int mvs_pack56(const uint64_t* hashes, uint64_t n, unsigned char* packed);
+
 /* The same over several GPUs in ONE call (SURVEY 8b "one call may use all GPUs"; the reference's analogue is
  * the dynamic OpenMP schedule of src/project_everything.cpp:289): the batch is cut into n_ctx contiguous
  * size-balanced shards (mvs_partition_samples), each context projects its shard on its own host thread and
@@ -251,6 +262,12 @@ int mvs_get_timing(mvs_ctx* ctx, mvs_timing* t);    /* synchronises the context'
  *        9 = LOP3:SHF 1:1.  Writes 32-bit lane-instructions per second (mode 5 issues one
  *        IMAD.WIDE + one LOP3 per counted op). */
 int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second);
+
+/* Second roofline denominator: warp rounds per second (one round = one hash x 32 lanes x 64 columns) that the GPU
+ * sustains for the projection loop's own instruction mix when no instruction waits for an operand (loop_mix_kernel:
+ * the same opcodes in the same proportions on independent register sets, same residency).  The projection kernel
+ * cannot run faster than this without issuing fewer instructions. */
+int mvs_loop_mix_peak(mvs_ctx* ctx, double* rounds_per_second);
 
 /* Tuning knobs.  Returns MVS_ERR_INVALID_ARG for an unknown key or a value outside the key's range (nothing is
  * ever ignored silently).  The shipped library knows:

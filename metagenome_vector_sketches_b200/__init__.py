@@ -12,10 +12,10 @@ or a B200 is missing.
 from ._lib import MvsError, load_library, library_path          # noqa: F401
 from .projection import (Sketcher, transform_set_into_vector,   # noqa: F401
                          norm_from_sumsq, format_norm, bind_host_to_device,
-                         sketch_csr_multi, reference_norms)
+                         sketch_csr_multi, reference_norms, pack56)
 from . import synthetic                                           # noqa: F401
 from . import pairwise                                            # noqa: F401
 
 __all__ = ["MvsError", "load_library", "library_path", "Sketcher",
            "transform_set_into_vector", "norm_from_sumsq", "format_norm", "bind_host_to_device", "sketch_csr_multi",
-           "reference_norms", "synthetic", "pairwise"]
+           "reference_norms", "pack56", "synthetic", "pairwise"]

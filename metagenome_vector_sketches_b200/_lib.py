@@ -48,6 +48,9 @@ SIGNATURES = {
     "mvs_project_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64, C.c_void_p]),
     "mvs_sketch_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64, C.c_void_p,
                                    C.c_void_p, C.c_void_p, C.c_void_p]),
+    "mvs_sketch_batch_packed56": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64, C.c_void_p,
+                                            C.c_void_p, C.c_void_p, C.c_void_p]),
+    "mvs_pack56": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p]),
     "mvs_sketch_batch_multi": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int,
                                          C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "mvs_project_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_uint64,
@@ -84,6 +87,7 @@ SIGNATURES = {
     "mvs_bind_host_to_device": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "mvs_get_timing": (C.c_int, [C.c_void_p, C.POINTER(Timing)]),
     "mvs_int_issue_peak": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),
+    "mvs_loop_mix_peak": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "mvs_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "mvs_has_experiments": (C.c_int, []),
 }

@@ -50,7 +50,7 @@ struct Slot {
     cudaEvent_t uploaded = nullptr;              // the pinned plan buffers have been read by the copy engine
     bool busy = false;
     bool upload_busy = false;
-    DevBuf hashes, out, partials, tasks, reduce, sumsq, out16, refnorm;
+    DevBuf hashes, out, partials, tasks, reduce, sumsq, out16, refnorm, packed;
     PinBuf h_tasks, h_reduce;
 };
 
@@ -591,7 +591,7 @@ void mvs_destroy(mvs_ctx* ctx)
     cudaSetDevice(ctx->device);
     for (auto& sl : ctx->slots) {
         if (sl.stream) cudaStreamSynchronize(sl.stream);
-        for (DevBuf* b : {&sl.hashes, &sl.out, &sl.partials, &sl.tasks, &sl.reduce, &sl.sumsq, &sl.out16, &sl.refnorm})
+        for (DevBuf* b : {&sl.hashes, &sl.out, &sl.partials, &sl.tasks, &sl.reduce, &sl.sumsq, &sl.out16, &sl.refnorm, &sl.packed})
             if (b->p) cudaFree(b->p);
         for (PinBuf* b : {&sl.h_tasks, &sl.h_reduce})
             if (b->p) cudaFreeHost(b->p);
@@ -637,14 +637,17 @@ int mvs_project_device(mvs_ctx* ctx, const uint64_t* d_hashes, const uint64_t* h
     return MVS_OK;
 }
 
-int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offsets, int64_t n_samples, int d,
-                     uint64_t seed, int32_t* out, int16_t* out16, uint64_t* sumsq, float* ref_norms)
+// hashes: the CSR payload as u64 (packed56 == false) or as 7 little-endian bytes per hash (packed56 == true)
+static int sketch_batch_impl(mvs_ctx* ctx, const void* hashes_any, bool packed56, const uint64_t* offsets, int64_t n_samples,
+                             int d, uint64_t seed, int32_t* out, int16_t* out16, uint64_t* sumsq, float* ref_norms)
 {
+    const uint64_t* hashes = packed56 ? nullptr : static_cast<const uint64_t*>(hashes_any);
+    const unsigned char* packed = packed56 ? static_cast<const unsigned char*>(hashes_any) : nullptr;
     if (!ctx || !offsets || n_samples < 0 || d <= 0 || (!out && !out16 && !sumsq && !ref_norms && n_samples > 0))
         return MVS_ERR_INVALID_ARG;
     if (n_samples == 0) return MVS_OK;
     if (n_samples >= 0xFFFFFFF0ll) return MVS_ERR_TOO_LARGE;
-    if (!hashes && offsets[n_samples] > offsets[0]) return MVS_ERR_INVALID_ARG;
+    if (!hashes_any && offsets[n_samples] > offsets[0]) return MVS_ERR_INVALID_ARG;
     for (int64_t s = 0; s < n_samples; ++s)
         if (offsets[s + 1] < offsets[s]) return MVS_ERR_INVALID_ARG;
     MVS_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -671,9 +674,19 @@ int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offse
         if (sumsq && (rc = ensure_dev(ctx, sl.sumsq, static_cast<size_t>(rows) * sizeof(uint64_t))) != MVS_OK) break;
         if (out16 && (rc = ensure_dev(ctx, sl.out16, static_cast<size_t>(rows) * row_bytes / 2)) != MVS_OK) break;
         if (ref_norms && (rc = ensure_dev(ctx, sl.refnorm, static_cast<size_t>(rows) * sizeof(float))) != MVS_OK) break;
-        if (nh) {
+        if (nh && !packed56) {
             if ((rc = mvs_internal_upload(ctx, sl.stream, sl.hashes.p, hashes + h0, nh * sizeof(uint64_t))) != MVS_OK) break;
             ctx->timing.h2d_bytes += nh * sizeof(uint64_t);
+        } else if (nh) {                         // 7 bytes per hash over the link, widened on the device
+            if ((rc = ensure_dev(ctx, sl.packed, nh * 7 + 16)) != MVS_OK) break;
+            if ((rc = mvs_internal_upload(ctx, sl.stream, sl.packed.p, packed + 7 * h0, nh * 7)) != MVS_OK) break;
+            ctx->timing.h2d_bytes += nh * 7;
+            const uint64_t grid = (nh + 255) / 256;
+            mvs::unpack56_kernel<<<static_cast<unsigned>(grid), 256, 0, sl.stream>>>(
+                static_cast<const uint64_t*>(sl.packed.p), nh, static_cast<uint64_t*>(sl.hashes.p));
+            cudaError_t ue = cudaGetLastError();
+            if (ue != cudaSuccess) { ctx->last_cuda = ue; rc = MVS_ERR_CUDA; break; }
+            ctx->launches += 1;
         }
         rc = run_range(ctx, sl, static_cast<const uint64_t*>(sl.hashes.p), offsets, s0, s1, h0, s0, g, seed,
                        static_cast<int32_t*>(sl.out.p), sl.stream, false);
@@ -717,6 +730,31 @@ int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offse
         if (rc == MVS_OK) rc = r2;
     }
     return rc;
+}
+
+int mvs_sketch_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offsets, int64_t n_samples, int d,
+                     uint64_t seed, int32_t* out, int16_t* out16, uint64_t* sumsq, float* ref_norms)
+{
+    return sketch_batch_impl(ctx, hashes, false, offsets, n_samples, d, seed, out, out16, sumsq, ref_norms);
+}
+
+int mvs_sketch_batch_packed56(mvs_ctx* ctx, const unsigned char* packed, const uint64_t* offsets, int64_t n_samples, int d,
+                              uint64_t seed, int32_t* out, int16_t* out16, uint64_t* sumsq, float* ref_norms)
+{
+    return sketch_batch_impl(ctx, packed, true, offsets, n_samples, d, seed, out, out16, sumsq, ref_norms);
+}
+
+int mvs_pack56(const uint64_t* hashes, uint64_t n, unsigned char* packed)
+{
+    if ((!hashes || !packed) && n) return MVS_ERR_INVALID_ARG;
+    uint64_t bad = 0;
+#pragma omp parallel for schedule(static) reduction(| : bad)
+    for (int64_t i = 0; i < static_cast<int64_t>(n); ++i) {
+        const uint64_t v = hashes[i];
+        bad |= v >> 56;
+        for (int b = 0; b < 7; ++b) packed[7 * static_cast<uint64_t>(i) + b] = static_cast<unsigned char>(v >> (8 * b));
+    }
+    return bad ? MVS_ERR_INVALID_ARG : MVS_OK;   // a hash >= 2^56 does not fit: use the u64 entry point
 }
 
 int mvs_project_batch(mvs_ctx* ctx, const uint64_t* hashes, const uint64_t* offsets, int64_t n_samples, int d,
@@ -976,6 +1014,41 @@ int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second)
     cudaEventDestroy(e1);
     const double ops = static_cast<double>(grid) * 256.0 * static_cast<double>(iters) * 32.0;
     *ops_per_second = ops / (static_cast<double>(best) * 1e-3);
+    return MVS_OK;
+}
+
+int mvs_loop_mix_peak(mvs_ctx* ctx, double* rounds_per_second)
+{
+    if (!ctx || !rounds_per_second) return MVS_ERR_INVALID_ARG;
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->slots[0].stream;
+    const int iters = 4096;
+    const unsigned grid = static_cast<unsigned>(ctx->sm_count) * 6u;     // the projection's residency: 6 CTAs of 4 warps per SM
+    cudaEvent_t e0, e1;
+    MVS_CUDA(ctx, cudaEventCreate(&e0));
+    MVS_CUDA(ctx, cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+        cudaEventRecord(e0, st);
+        mvs::loop_mix_kernel<<<grid, 128, 0, st>>>(ctx->d_sink, iters, 0x9e3779b9u, 0x85ebca6bu, 1u);
+        cudaEventRecord(e1, st);
+        cudaError_t e = cudaEventSynchronize(e1);
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) {
+            ctx->last_cuda = e;
+            cudaEventDestroy(e0);
+            cudaEventDestroy(e1);
+            return MVS_ERR_CUDA;
+        }
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (rep > 0) best = std::min(best, ms);
+        ctx->launches += 1;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    const double rounds = static_cast<double>(grid) * 4.0 /*warps*/ * static_cast<double>(iters) * 4.0;   // warp rounds
+    *rounds_per_second = rounds / (static_cast<double>(best) * 1e-3);
     return MVS_OK;
 }
 

@@ -562,6 +562,26 @@ finalize_kernel(const int32_t* __restrict__ vec, int64_t n_rows, int d,
 }
 
 // ------------------------------------------------------------------------------------
+// Packed input: hashes below 2^56 travel as 7 little-endian bytes each (12.5 % fewer bytes on the host link, which
+// bounds the end-to-end rate) and are widened to the u64 array the projection reads.  Thread t reads the two aligned
+// 8-byte words that hold bytes [7t, 7t + 7) of the packed slice (the slice starts at an 8-byte aligned device address
+// and is over-allocated by 16 bytes) and writes hashes[t]: 7 B read + 8 B written per hash, HBM-bound, ~0.3 % of the
+// projection's time.
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+unpack56_kernel(const uint64_t* __restrict__ packed_words, uint64_t n, uint64_t* __restrict__ hashes)
+{
+    const uint64_t t = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const uint64_t byte = 7ull * t;
+    const uint64_t w = byte >> 3;
+    const unsigned sh = static_cast<unsigned>(byte & 7ull) * 8u;
+    const uint64_t lo = packed_words[w], hi = packed_words[w + 1];
+    const uint64_t v = sh ? ((lo >> sh) | (hi << (64u - sh))) : lo;
+    hashes[t] = v & 0x00FFFFFFFFFFFFFFull;
+}
+
+// ------------------------------------------------------------------------------------
 // Integer issue-rate microbenchmarks (roofline denominator).
 // ------------------------------------------------------------------------------------
 template <int MODE>
@@ -609,6 +629,64 @@ issue_bench_kernel(uint32_t* sink, int iters, uint32_t k0, uint32_t k1)
 #pragma unroll
     for (int i = 0; i < 8; ++i) x ^= a[i];
     if (x == 0x12345u) sink[0] = x;              // practically never; keeps the chains alive
+}
+
+// ------------------------------------------------------------------------------------
+// The projection loop's own instruction mix WITHOUT its data dependencies: per (hash, lane) round project_kernel issues
+// ~8.3 LOP3, 3 SHF, 4 IMAD, 3 IMAD.IADD, 2 IMAD.WIDE, 1 POPC, 1 LDS.128 and ~0.5 IADD3 (SASS of the hot loop; ncu
+// per-opcode table in profiles/).  This kernel issues that mix (8 LOP3 + 1 every other round, the adds as multiply-adds
+// by an opaque 1 so that they stay on the FMA-heavy pipe like ptxas places them) on four independent register sets per
+// thread, 6 CTAs of 128 threads per SM like the projection.  Its time per round is what the SM's issue ports and integer
+// pipes allow for this mix when no instruction ever waits for an operand: the denominator of roofline.mix_limit.
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+loop_mix_kernel(uint32_t* sink, int iters, uint32_t k0, uint32_t k1, uint32_t one)
+{
+    __shared__ uint4 tab[64];
+    if (threadIdx.x < 64) tab[threadIdx.x] = make_uint4(threadIdx.x * k0, k1, k0 ^ threadIdx.x, k1 + threadIdx.x);
+    __syncthreads();
+    uint32_t a[4], b[4], c[4], e[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { a[i] = threadIdx.x * 2654435761u + i * k0 + blockIdx.x; b[i] = a[i] ^ k1; c[i] = a[i] + k0; e[i] = i; }
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint4 t = tab[(it + i) & 63];                                                       // LDS.128
+            asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(a[i]) : "r"(one), "r"(a[i]), "r"(t.x));   // lane add
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(t.y), "r"(k0));          // ^ F
+            asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(b[i]) : "r"(a[i]), "r"(k1), "r"(t.w));    // l1 * K1hi + M
+            unsigned long long w;
+            asm volatile("mul.wide.u32 %0, %1, %2;" : "=l"(w) : "r"(a[i]), "r"(k0));                  // IMAD.WIDE
+            a[i] = static_cast<uint32_t>(w);
+            c[i] = static_cast<uint32_t>(w >> 32);
+            asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(c[i]) : "r"(one), "r"(c[i]), "r"(b[i]));  // hi + t
+            asm volatile("shf.r.wrap.b32 %0, %1, %2, 27;" : "=r"(b[i]) : "r"(a[i]), "r"(c[i]));       // xor-shift 27
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(b[i]), "r"(k1));
+            asm volatile("shf.r.clamp.b32 %0, %1, %2, 27;" : "=r"(b[i]) : "r"(c[i]), "r"(k0));
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(c[i]) : "r"(b[i]), "r"(k0));
+            asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(b[i]) : "r"(c[i]), "r"(k0), "r"(k1));     // yh * K2lo
+            asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(b[i]) : "r"(a[i]), "r"(k1), "r"(b[i]));   // + yl * K2hi
+            asm volatile("mul.wide.u32 %0, %1, %2;" : "=l"(w) : "r"(a[i]), "r"(k1));                  // IMAD.WIDE
+            a[i] = static_cast<uint32_t>(w);
+            c[i] = static_cast<uint32_t>(w >> 32);
+            asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(c[i]) : "r"(one), "r"(c[i]), "r"(b[i]));  // hi add
+            asm volatile("shf.r.wrap.b32 %0, %1, %2, 31;" : "=r"(b[i]) : "r"(a[i]), "r"(c[i]));       // xor-shift 31, low word
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(b[i]), "r"(k1));
+            uint32_t p;
+            asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(p) : "r"(c[i]), "r"(k0), "r"(k1));        // hi * fold
+            asm volatile("popc.b32 %0, %0;" : "+r"(p));
+            e[i] += p;                                                                                // running popcount sum
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(b[i]) : "r"(a[i]), "r"(c[i]));       // carry-save tree
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0xE8;" : "+r"(e[i]) : "r"(a[i]), "r"(c[i]));
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(b[i]) : "r"(e[i]), "r"(k0));
+            asm volatile("lop3.b32 %0, %0, %1, %2, 0xE8;" : "+r"(c[i]) : "r"(b[i]), "r"(k1));
+            if (it & 1) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(c[i]) : "r"(b[i]), "r"(e[i]));
+        }
+    }
+    uint32_t x = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) x ^= a[i] ^ b[i] ^ c[i] ^ e[i];
+    if (x == 0x12345u) sink[0] = x;
 }
 
 }  // namespace mvs

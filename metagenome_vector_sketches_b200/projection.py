@@ -70,6 +70,20 @@ class Sketcher:
                                           C.c_uint64(seed), _ptr(out)), "mvs_project_batch", self._h)
         return out
 
+    def project_csr_packed56(self, packed, offsets, d, seed=0, out=None):
+        """mvs_sketch_batch_packed56: the CSR payload as 7 little-endian bytes per hash (see pack56)."""
+        packed = np.ascontiguousarray(packed, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        n = len(offsets) - 1
+        if n and 7 * int(offsets[-1]) > len(packed):
+            raise ValueError("offsets index past the end of the packed hashes")
+        if out is None:
+            out = np.empty((n, d), dtype=np.int32)
+        assert out.dtype == np.int32 and out.flags.c_contiguous and out.size == n * d
+        check(self._lib.mvs_sketch_batch_packed56(self._h, _ptr(packed), _ptr(offsets), n, int(d), C.c_uint64(seed),
+                                                  _ptr(out), None, None, None), "mvs_sketch_batch_packed56", self._h)
+        return out
+
     def project_sets(self, sets, d, seed=0):
         """List of iterables of hashes -> (len(sets), d) int32.  Dedupes each set (reference: unordered_set)."""
         uniq = [np.unique(np.asarray(list(s) if not isinstance(s, np.ndarray) else s, dtype=np.uint64))
@@ -130,6 +144,11 @@ class Sketcher:
         check(self._lib.mvs_int_issue_peak(self._h, int(which), C.byref(v)), "mvs_int_issue_peak", self._h)
         return v.value
 
+    def loop_mix_peak(self):
+        v = C.c_double()
+        check(self._lib.mvs_loop_mix_peak(self._h, C.byref(v)), "mvs_loop_mix_peak", self._h)
+        return v.value
+
     def set_option(self, key, value):
         check(self._lib.mvs_set_option(self._h, key.encode(), int(value)), "mvs_set_option", self._h)
 
@@ -151,6 +170,15 @@ def sketch_csr_multi(sketchers, hashes, offsets, d, seed=0, int16=False):
           sketchers[0]._h)
     out = {"sumsq": sumsq, "ref_norms": ref}
     out["vec16" if int16 else "vec"] = vec16 if int16 else vec
+    return out
+
+
+def pack56(hashes, out=None):
+    """mvs_pack56: uint64 hashes (all < 2^56) -> 7 little-endian bytes each."""
+    h = np.ascontiguousarray(hashes, dtype=np.uint64)
+    if out is None:
+        out = np.empty(7 * len(h), dtype=np.uint8)
+    check(load_library().mvs_pack56(_ptr(h), len(h), _ptr(out)), "mvs_pack56")
     return out
 
 

@@ -219,7 +219,7 @@ def test_reference_driver_linked_against_our_shim(tmp_path, toy_hash_file):
         assert (db / f).read_bytes() == (live / f).read_bytes(), f
 
 
-@pytest.mark.parametrize("threads,serial", [(1, False), (8, False), (24, False), (8, True)])
+@pytest.mark.parametrize("threads,serial", [(1, False), (24, False), (8, True)])
 def test_shim_called_concurrently_from_openmp_threads(threads, serial):
     """The a4 sample loop (project_everything.cpp:287-298) over in-memory sets: our replacement of
     transform_set_into_vector, one context per calling thread, against the reference's function."""

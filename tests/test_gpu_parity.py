@@ -289,6 +289,32 @@ def test_device_resident_calls_back_to_back_on_a_user_stream(sk):
         assert np.array_equal(dout.cpu().numpy(), oracle_csr(h, off, d)), (len(off) - 1, d)
 
 
+def test_packed56_input_gives_the_same_vectors(sk):
+    """7-byte packed hashes (mvs_sketch_batch_packed56): ragged samples, empty samples, slices that start at every
+    byte phase, values up to 2^56 - 1 -- the same rows as the u64 path and the oracle; a hash >= 2^56 is refused."""
+    rng = np.random.default_rng(56)
+    sizes = [0, 1, 2, 7, 8, 9, 1000, 0, 33333, 5, 70001, 0]
+    sets = [np.unique(rng.integers(0, 2 ** 56, n, dtype=np.uint64)) for n in sizes]
+    sets[3][-1] = np.uint64(2 ** 56 - 1)
+    sets[4][0] = np.uint64(0)
+    offsets = np.zeros(len(sets) + 1, dtype=np.uint64)
+    offsets[1:] = np.cumsum([len(x) for x in sets])
+    h = np.concatenate(sets)
+    packed = mvs.pack56(h)
+    assert packed.tobytes() == h.astype("<u8").view(np.uint8).reshape(-1, 8)[:, :7].tobytes()    # the format, restated
+    sk.set_option("slice_hashes", 4099)                                   # many slices, odd starts
+    try:
+        for d in (2048, 200):
+            want = oracle_csr(h, offsets, d)
+            assert np.array_equal(sk.project_csr_packed56(packed, offsets, d), want)
+            assert np.array_equal(sk.project_csr(h, offsets, d), want)
+    finally:
+        sk.set_option("slice_hashes", 16 << 20)
+    assert np.array_equal(sk.project_csr_packed56(packed, offsets, 64), oracle_csr(h, offsets, 64))
+    with pytest.raises(mvs.MvsError):
+        mvs.pack56(np.array([1, 2 ** 56], dtype=np.uint64))
+
+
 def test_live_reference_if_built(sk):
     if ref_lib() is None:
         pytest.skip("oracle/_ref not present on this host")

@@ -52,7 +52,7 @@ def write_json(path, key, workload, source, hdr, units, vals):
     dur_unit = units[ix["gpu__time_duration.sum"]]
     dur_ms = num("gpu__time_duration.sum") * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(dur_unit, 1e-6)
     prof = {
-        "cubin_sha256": key, "kernel": vals[ix["Kernel Name"]], "grid": vals[ix["Grid Size"]], "workload": workload,
+        "kernel_sass_sha256": key, "kernel": vals[ix["Kernel Name"]], "grid": vals[ix["Grid Size"]], "workload": workload,
         "source": source,
         "inst_executed": num("smsp__inst_executed.sum"),
         "sm_cycles_elapsed_avg": num("sm__cycles_elapsed.avg"),
