@@ -340,19 +340,16 @@ cudaError_t launch_project(const Geometry& g, cudaStream_t st, uint32_t ntasks, 
 // Plan [s0, s1) into the slot's pinned buffers, upload, launch projection (+ reduce).
 // d_hashes holds the hashes from index `hash_base` on; d_out row 0 = sample `s0`
 // when rows_local, else sample 0.
-int run_range(mvs_ctx* ctx, Slot& sl, const uint64_t* d_hashes, const uint64_t* offsets, int64_t s0, int64_t s1,
-              uint64_t hash_base, int64_t row_base, const Geometry& g_in, uint64_t seed, int32_t* d_out,
-              cudaStream_t st, bool record_timing, cudaStream_t up = nullptr)
+// Plan [s0, s1) into the slot's pinned buffers and copy the plan to the device on stream `up`.  The copy needs nothing
+// from the device, so callers enqueue it BEFORE the (much larger) hash upload of the same slice: the host-to-device
+// copy queue then never holds a small copy that waits for a kernel while the next slice's hashes queue up behind it.
+int plan_range(mvs_ctx* ctx, Slot& sl, const uint64_t* offsets, int64_t s0, int64_t s1, uint64_t hash_base, int64_t row_base,
+               const Geometry& g, cudaStream_t up, PlanCounts& pc)
 {
-    // `up` (may equal st): stream that copies the plan to the device.  The device-resident entry point passes the
-    // slot's own stream, so that the copy runs while the caller's previous kernel is still busy on `st`.
-    if (!up) up = st;
-    const Geometry& g = g_in;
     Chunker ch{choose_cap(offsets, s0, s1, g, ctx->sm_count), g.quantum};
 #ifdef MVS_EXPERIMENTS
     if (ctx->task_cap) ch.cap = std::min<uint64_t>(g.cap, (ctx->task_cap + 63) / 64 * 64 * static_cast<uint64_t>(g.S));   // fixed caps for the sweep tools
 #endif
-    PlanCounts pc;
     int rc = count_plan(offsets, s0, s1, g, ch, pc);
     if (rc != MVS_OK) return rc;
     if (pc.tasks == 0) return MVS_OK;
@@ -370,6 +367,17 @@ int run_range(mvs_ctx* ctx, Slot& sl, const uint64_t* d_hashes, const uint64_t* 
                                       cudaMemcpyHostToDevice, up));
     MVS_CUDA(ctx, cudaEventRecord(sl.uploaded, up));
     sl.upload_busy = true;
+    ctx->timing.warp_tasks = pc.tasks;
+    ctx->timing.partial_rows = pc.prows;
+    return MVS_OK;
+}
+
+// Launch projection (+ reduce) of a planned range on `st`.  d_hashes holds the hashes from index `hash_base` (of the
+// plan) on; d_out row 0 = sample `row_base`.  `up`: the stream the plan was copied on.
+int launch_range(mvs_ctx* ctx, Slot& sl, const PlanCounts& pc, const uint64_t* d_hashes, const Geometry& g, uint64_t seed,
+                 int32_t* d_out, cudaStream_t st, bool record_timing, cudaStream_t up)
+{
+    if (pc.tasks == 0) return MVS_OK;
     if (up != st) MVS_CUDA(ctx, cudaStreamWaitEvent(st, sl.uploaded, 0));
     cudaEvent_t* ev = ctx->ev[ctx->timing_calls % kTimingRing];
     if (record_timing) MVS_CUDA(ctx, cudaEventRecord(ev[0], st));
@@ -391,8 +399,6 @@ int run_range(mvs_ctx* ctx, Slot& sl, const uint64_t* d_hashes, const uint64_t* 
         MVS_CUDA(ctx, cudaEventRecord(ev[2], st));
         ctx->timing_calls += 1;
     }
-    ctx->timing.warp_tasks = pc.tasks;
-    ctx->timing.partial_rows = pc.prows;
     return MVS_OK;
 }
 
@@ -629,8 +635,9 @@ int mvs_project_device(mvs_ctx* ctx, const uint64_t* d_hashes, const uint64_t* h
     if (rc != MVS_OK) return rc;
     if (sl.busy && sl.stream != st) MVS_CUDA(ctx, cudaStreamWaitEvent(sl.stream, sl.done, 0));
     const Geometry g = make_geometry(d);
-    rc = run_range(ctx, sl, d_hashes, h_offsets, 0, n_samples, 0, 0, g, seed, d_out, st, true, sl.stream);
-    if (rc != MVS_OK) return rc;
+    PlanCounts pc;
+    if ((rc = plan_range(ctx, sl, h_offsets, 0, n_samples, 0, 0, g, sl.stream, pc)) != MVS_OK) return rc;
+    if ((rc = launch_range(ctx, sl, pc, d_hashes, g, seed, d_out, st, true, sl.stream)) != MVS_OK) return rc;
     MVS_CUDA(ctx, cudaEventRecord(sl.done, st));
     sl.busy = true;
     if (!stream) MVS_CUDA(ctx, cudaStreamSynchronize(st));
@@ -674,6 +681,8 @@ static int sketch_batch_impl(mvs_ctx* ctx, const void* hashes_any, bool packed56
         if (sumsq && (rc = ensure_dev(ctx, sl.sumsq, static_cast<size_t>(rows) * sizeof(uint64_t))) != MVS_OK) break;
         if (out16 && (rc = ensure_dev(ctx, sl.out16, static_cast<size_t>(rows) * row_bytes / 2)) != MVS_OK) break;
         if (ref_norms && (rc = ensure_dev(ctx, sl.refnorm, static_cast<size_t>(rows) * sizeof(float))) != MVS_OK) break;
+        PlanCounts pc;                           // plan first: its small copy must not queue behind a kernel (see plan_range)
+        if ((rc = plan_range(ctx, sl, offsets, s0, s1, h0, s0, g, sl.stream, pc)) != MVS_OK) break;
         if (nh && !packed56) {
             if ((rc = mvs_internal_upload(ctx, sl.stream, sl.hashes.p, hashes + h0, nh * sizeof(uint64_t))) != MVS_OK) break;
             ctx->timing.h2d_bytes += nh * sizeof(uint64_t);
@@ -688,8 +697,8 @@ static int sketch_batch_impl(mvs_ctx* ctx, const void* hashes_any, bool packed56
             if (ue != cudaSuccess) { ctx->last_cuda = ue; rc = MVS_ERR_CUDA; break; }
             ctx->launches += 1;
         }
-        rc = run_range(ctx, sl, static_cast<const uint64_t*>(sl.hashes.p), offsets, s0, s1, h0, s0, g, seed,
-                       static_cast<int32_t*>(sl.out.p), sl.stream, false);
+        rc = launch_range(ctx, sl, pc, static_cast<const uint64_t*>(sl.hashes.p), g, seed, static_cast<int32_t*>(sl.out.p),
+                          sl.stream, false, sl.stream);
         if (rc != MVS_OK) break;
         ctx->timing.h2d_bytes += ctx->timing.warp_tasks * sizeof(WarpTask);
         cudaError_t e = cudaSuccess;
