@@ -253,6 +253,27 @@ def test_properties_at_scale(sk):
     assert np.array_equal(merged[0], full.sum(axis=0, dtype=np.int64).astype(np.int32))
 
 
+def test_sketch_batch_multi_on_all_visible_devices(sk):
+    """On a box with several B200s: one context per device (what `--gpus N` does), same rows as one context."""
+    import torch
+    ndev = torch.cuda.device_count()
+    if ndev < 2:
+        pytest.skip("one visible GPU: the fan-out is covered by the contexts-on-one-device test")
+    ctxs = [sk] + [mvs.Sketcher(g) for g in range(1, ndev)]
+    try:
+        sizes = [int(x) for x in mvs.synthetic.lognormal_sizes(300, seed=5, median=3000, lo=1, hi=40000)]
+        sizes[0] = 0
+        sizes[100] = 500_000
+        h, off = mvs.synthetic.ragged_batch(sizes, seed=8)
+        want = oracle_csr(h, off, 2048)
+        got = mvs.sketch_csr_multi(ctxs, h, off, 2048)
+        assert np.array_equal(got["vec"], want)
+        assert np.array_equal(got["ref_norms"].view(np.uint32), oracle_reference_norms(want).view(np.uint32))
+    finally:
+        for c in ctxs[1:]:
+            c.close()
+
+
 def test_device_resident_entry_point(sk):
     import torch
     h, off = mvs.synthetic.uniform_batch(64, 20000, seed=2)
