@@ -282,6 +282,43 @@ def run_gpu(args):
     else:
         hh = torch.empty(total, dtype=torch.int64, pin_memory=True)
     hh.copy_(dh)
+    # ---- host-link probe and upload relay (N > 1): every rank copies 256 MB x 4 to its GPU at the same time; if the
+    # ranks' rates differ by more than 25 % (unequal PCIe roots, profiles/r02l_h2d_matrix_8gpu.json), the slow half
+    # routes its hash slices through a partner of the fast half (option relay_device: host -> partner GPU -> NVLink)
+    relay = {"mode": args.relay, "probe_GBps": None, "via": None}
+    if world > 1 and args.relay != "off":
+        probe_dst = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+        probe_src = hh[: (256 << 20) // 8].view(torch.uint8)
+        probe_dst.copy_(probe_src, non_blocking=True)
+        barrier()
+        pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        pe0.record()
+        for _ in range(4):
+            probe_dst.copy_(probe_src, non_blocking=True)
+        pe1.record()
+        torch.cuda.synchronize()
+        rate = 4 * (256 << 20) / (pe0.elapsed_time(pe1) * 1e-3) / 1e9
+        rt = torch.tensor([rate], dtype=torch.float64, device=dev)
+        allr = [torch.zeros_like(rt) for _ in range(world)]
+        dist.all_gather(allr, rt)
+        rates = [float(x.item()) for x in allr]
+        relay["probe_GBps"] = rates
+        order = sorted(range(world), key=lambda r: rates[r])             # slowest first
+        via = None
+        if args.relay.startswith("force:"):
+            via = int(args.relay.split(":")[1])
+        elif min(rates) < 0.75 * max(rates) and world % 2 == 0:
+            pos = order.index(rank)
+            if pos < world // 2:
+                via = order[world - 1 - pos]                              # slowest pairs with fastest
+        if via is not None and via != local:
+            sk.set_option("relay_device", via)
+            relay["via"] = via
+        viat = torch.tensor([-1.0 if relay["via"] is None else float(relay["via"])], dtype=torch.float64, device=dev)
+        allv = [torch.zeros_like(viat) for _ in range(world)]
+        dist.all_gather(allv, viat)
+        relay["via_per_rank"] = [int(x.item()) for x in allv]
+        del probe_dst
     hout = torch.empty((n, d), dtype=torch.int32, pin_memory=True)
     h_np = hh.numpy().view(np.uint64)
     out_np = hout.numpy()
@@ -498,6 +535,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--wc-input", action="store_true", help="experiment: write-combined pinned input buffer")
     ap.add_argument("--no-bind", action="store_true", help="skip mvs_bind_host_to_device (A/B of the host locality)")
+    ap.add_argument("--relay", default="auto",
+                    help="N > 1 end-to-end leg: auto = probe the ranks' concurrent H2D rates and route the slow half through "
+                         "partners of the fast half (relay_device); off; force:<device> = every rank relays through that device")
     ap.add_argument("--no-packed", action="store_true", help="skip the packed56 end-to-end leg (N = 1)")
     ap.add_argument("--no-config3", action="store_true", help="skip the BASELINE configs[2] dimension sweep (N = 1 leg)")
     ap.add_argument("--c4-samples", type=int, default=100000,
@@ -604,6 +644,7 @@ def main():
                     "h2d_bytes_per_step": int(tb["h2d_bytes"]), "d2h_bytes_per_step": int(tb["d2h_bytes"]),
                     "api": "mvs_project_batch (%s host CSR in, pinned host int32 rows out)"
                            % ("write-combined pinned" if args.wc_input else "pinned"),
+                    "relay": g["relay"],
                     "host_binding": {"how": "mvs_bind_host_to_device per rank before the pinned buffers are allocated "
                                             "(applied: 1 = CPU affinity, 2 = preferred memory node)",
                                      "per_rank_ms_node_applied": g["per_rank"]},

@@ -274,6 +274,12 @@ int mvs_loop_mix_peak(mvs_ctx* ctx, double* rounds_per_second);
  *   "slice_hashes" (> 0): hashes per streamed slice of mvs_project_batch / mvs_sketch_batch (default 16 Mi = 128 MB);
  *   "slice_rows_bytes" (> 0): output bytes per streamed slice (default 256 MB);
  *   "stage_threads" (1..64): host threads that copy a pageable caller buffer into the pinned staging ring (default 8);
+ *   "relay_device" (-1 = off, default; else a peer device index with P2P access): the hash slices of the batch entry
+ *       points travel host -> peer device -> this device (cudaMemcpyAsync into a staging buffer on the peer, then
+ *       cudaMemcpyPeerAsync over NVLink) instead of over this device's own PCIe link.  For hosts whose PCIe roots have
+ *       unequal host-memory ceilings: ranks on the starved root route through a partner on the other one (bench.py
+ *       probes the ranks' concurrent H2D rates and pairs them).  Pinned sources only; pageable
+ *       ones keep the direct path;
  *   "release_workspace" (any value): frees the device and pinned buffers the pairwise entry points keep between calls
  *       (they are grow-only and otherwise live until mvs_destroy).
  * The A/B knobs of round 1 ("task_cap", "pairwise_path", "pairwise_limbs", "pairwise_pair", "pairwise_cluster",

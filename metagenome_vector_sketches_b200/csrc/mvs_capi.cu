@@ -54,6 +54,20 @@ struct Slot {
     PinBuf h_tasks, h_reduce;
 };
 
+// Upload relay (option "relay_device"): the hash slices of this context travel host -> PEER device -> this device
+// (cudaMemcpyAsync into a staging buffer on the peer, then cudaMemcpyPeerAsync over NVLink) instead of over this
+// device's own PCIe link.  For hosts whose PCIe roots have unequal ceilings (profiles/r02l_h2d_matrix_8gpu.json: the
+// four GPUs of the first root share 116 GB/s, the other four get 54 GB/s each and NVLink idles): ranks on the starved
+// root route through a partner on the other one.  One staging buffer, stream and event per slice slot.
+struct Relay {
+    int device = -1;
+    void* buf[kSlots] = {nullptr, nullptr, nullptr};
+    size_t cap[kSlots] = {0, 0, 0};
+    cudaStream_t stream[kSlots] = {nullptr, nullptr, nullptr};
+    cudaEvent_t landed[kSlots] = {nullptr, nullptr, nullptr};
+    uint64_t bytes = 0;                          // relayed by the last batch call
+};
+
 struct Geometry {
     int d = 0;
     int nb = 0;                                  // 64-column blocks
@@ -75,6 +89,7 @@ struct mvs_ctx {
     // mvs_project_device call; mvs_get_timing averages the calls since the last query
     cudaEvent_t ev[kTimingRing][3] = {};
     unsigned device_turn = 0;                    // mvs_project_device calls so far (slot rotation)
+    Relay relay;
     uint64_t timing_calls = 0;                   // device-path calls recorded so far
     uint64_t timing_read = 0;                    // calls already consumed by mvs_get_timing
     mvs_timing timing{};
@@ -402,6 +417,85 @@ int launch_range(mvs_ctx* ctx, Slot& sl, const PlanCounts& pc, const uint64_t* d
     return MVS_OK;
 }
 
+void relay_release(mvs_ctx* ctx)
+{
+    Relay& r = ctx->relay;
+    if (r.device >= 0) {
+        cudaSetDevice(r.device);
+        for (int k = 0; k < kSlots; ++k) {
+            if (r.stream[k]) { cudaStreamSynchronize(r.stream[k]); cudaStreamDestroy(r.stream[k]); }
+            if (r.landed[k]) cudaEventDestroy(r.landed[k]);
+            if (r.buf[k]) cudaFree(r.buf[k]);
+            r.stream[k] = nullptr; r.landed[k] = nullptr; r.buf[k] = nullptr; r.cap[k] = 0;
+        }
+        cudaSetDevice(ctx->device);
+        cudaGetLastError();
+    }
+    r.device = -1;
+}
+
+int relay_setup(mvs_ctx* ctx, int peer)
+{
+    relay_release(ctx);
+    if (peer < 0) return MVS_OK;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || peer >= ndev || peer == ctx->device) { cudaGetLastError(); return MVS_ERR_INVALID_ARG; }
+    int can = 0;
+    if (cudaDeviceCanAccessPeer(&can, ctx->device, peer) != cudaSuccess || !can) { cudaGetLastError(); return MVS_ERR_INVALID_ARG; }
+    auto enable = [](int from, int to) {
+        cudaSetDevice(from);
+        const cudaError_t e = cudaDeviceEnablePeerAccess(to, 0);
+        if (e != cudaSuccess) cudaGetLastError();
+        return e == cudaSuccess || e == cudaErrorPeerAccessAlreadyEnabled;
+    };
+    const bool ok = enable(ctx->device, peer) && enable(peer, ctx->device);
+    cudaError_t e = cudaSetDevice(peer);
+    for (int k = 0; k < kSlots && e == cudaSuccess; ++k) {
+        e = cudaStreamCreateWithFlags(&ctx->relay.stream[k], cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->relay.landed[k], cudaEventDisableTiming);
+    }
+    cudaSetDevice(ctx->device);
+    ctx->relay.device = peer;
+    if (!ok || e != cudaSuccess) {
+        ctx->last_cuda = static_cast<int>(e);
+        relay_release(ctx);
+        return MVS_ERR_CUDA;
+    }
+    return MVS_OK;
+}
+
+// One slice of hashes host -> device on the slot's stream: over the relay when it is on and the source is pinned
+// (the DMA engine of the peer reads it), else the direct path (which also stages pageable sources).
+int upload_slice(mvs_ctx* ctx, Slot& sl, int k, void* dst, const void* src, size_t bytes)
+{
+    Relay& r = ctx->relay;
+    bool pinned = false;
+    if (r.device >= 0 && bytes >= (1u << 20)) {
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, src) == cudaSuccess) pinned = at.type == cudaMemoryTypeHost;
+        else cudaGetLastError();
+    }
+    if (!pinned) return mvs_internal_upload(ctx, sl.stream, dst, src, bytes);
+    MVS_CUDA(ctx, cudaSetDevice(r.device));
+    cudaError_t e = cudaSuccess;
+    if (r.cap[k] < bytes) {
+        if (r.buf[k]) e = cudaFree(r.buf[k]);
+        r.buf[k] = nullptr;
+        r.cap[k] = 0;
+        if (e == cudaSuccess) e = cudaMalloc(&r.buf[k], bytes + bytes / 8 + 256);
+        if (e == cudaSuccess) r.cap[k] = bytes + bytes / 8 + 256;
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(r.buf[k], src, bytes, cudaMemcpyHostToDevice, r.stream[k]);
+    if (e == cudaSuccess) e = cudaEventRecord(r.landed[k], r.stream[k]);
+    const cudaError_t back = cudaSetDevice(ctx->device);
+    if (e == cudaSuccess) e = back;
+    MVS_CUDA(ctx, e);
+    MVS_CUDA(ctx, cudaStreamWaitEvent(sl.stream, r.landed[k], 0));
+    MVS_CUDA(ctx, cudaMemcpyPeerAsync(dst, ctx->device, r.buf[k], r.device, bytes, sl.stream));
+    r.bytes += bytes;
+    return MVS_OK;
+}
+
 int wait_slot(mvs_ctx* ctx, Slot& sl)
 {
     if (sl.busy) {
@@ -609,6 +703,7 @@ void mvs_destroy(mvs_ctx* ctx)
         for (auto& e : e3)
             if (e) cudaEventDestroy(e);
     if (ctx->d_sink) cudaFree(ctx->d_sink);
+    relay_release(ctx);
     release_workspace(ctx);
     for (auto& e : ctx->stage_ev)
         if (e) cudaEventDestroy(e);
@@ -663,6 +758,7 @@ static int sketch_batch_impl(mvs_ctx* ctx, const void* hashes_any, bool packed56
     const int64_t max_rows = std::max<int64_t>(1, static_cast<int64_t>(ctx->slice_rows_bytes / row_bytes));
     ctx->timing.h2d_bytes = 0;
     ctx->timing.d2h_bytes = 0;
+    ctx->relay.bytes = 0;
 
     int rc = MVS_OK;
     int64_t s0 = 0;
@@ -684,11 +780,11 @@ static int sketch_batch_impl(mvs_ctx* ctx, const void* hashes_any, bool packed56
         PlanCounts pc;                           // plan first: its small copy must not queue behind a kernel (see plan_range)
         if ((rc = plan_range(ctx, sl, offsets, s0, s1, h0, s0, g, sl.stream, pc)) != MVS_OK) break;
         if (nh && !packed56) {
-            if ((rc = mvs_internal_upload(ctx, sl.stream, sl.hashes.p, hashes + h0, nh * sizeof(uint64_t))) != MVS_OK) break;
+            if ((rc = upload_slice(ctx, sl, (turn - 1) % kSlots, sl.hashes.p, hashes + h0, nh * sizeof(uint64_t))) != MVS_OK) break;
             ctx->timing.h2d_bytes += nh * sizeof(uint64_t);
         } else if (nh) {                         // 7 bytes per hash over the link, widened on the device
             if ((rc = ensure_dev(ctx, sl.packed, nh * 7 + 16)) != MVS_OK) break;
-            if ((rc = mvs_internal_upload(ctx, sl.stream, sl.packed.p, packed + 7 * h0, nh * 7)) != MVS_OK) break;
+            if ((rc = upload_slice(ctx, sl, (turn - 1) % kSlots, sl.packed.p, packed + 7 * h0, nh * 7)) != MVS_OK) break;
             ctx->timing.h2d_bytes += nh * 7;
             const uint64_t grid = (nh + 255) / 256;
             mvs::unpack56_kernel<<<static_cast<unsigned>(grid), 256, 0, sl.stream>>>(
@@ -1075,6 +1171,13 @@ int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value)
     if ((r = set("slice_hashes", 1, INT64_MAX, [&] { ctx->slice_hashes = static_cast<uint64_t>(value); })) != 1) return r;
     if ((r = set("slice_rows_bytes", 1, INT64_MAX, [&] { ctx->slice_rows_bytes = static_cast<uint64_t>(value); })) != 1) return r;
     if ((r = set("stage_threads", 1, 64, [&] { ctx->stage_threads = static_cast<int>(value); })) != 1) return r;
+    if (!std::strcmp(key, "relay_device")) {     // -1 = off; a peer device index = route hash uploads through it
+        if (value < -1 || value > 1023) return MVS_ERR_INVALID_ARG;
+        cudaSetDevice(ctx->device);
+        for (auto& sl : ctx->slots)
+            if (sl.stream) cudaStreamSynchronize(sl.stream);
+        return relay_setup(ctx, static_cast<int>(value));
+    }
     if ((r = set("release_workspace", INT64_MIN, INT64_MAX, [&] { cudaSetDevice(ctx->device); cudaDeviceSynchronize(); release_workspace(ctx); })) != 1) return r;
 #ifdef MVS_EXPERIMENTS                           // A/B knobs of the experiment build (libmvs_b200_exp.so); the shipped library rejects them
     if ((r = set("task_cap", 0, INT64_MAX, [&] { ctx->task_cap = static_cast<uint64_t>(value); })) != 1) return r;

@@ -274,6 +274,38 @@ def test_sketch_batch_multi_on_all_visible_devices(sk):
             c.close()
 
 
+def test_upload_relay_through_a_peer_device(sk):
+    """Option relay_device: hash slices go host -> peer GPU -> this GPU (NVLink).  Same rows, u64 and packed; on a
+    1-GPU box the option must be refused (no peer), never silently ignored."""
+    import torch
+    from metagenome_vector_sketches_b200.projection import pinned_empty
+    if torch.cuda.device_count() < 2:
+        with pytest.raises(mvs.MvsError):
+            sk.set_option("relay_device", 1)
+        with pytest.raises(mvs.MvsError):
+            sk.set_option("relay_device", 0)                              # itself
+        sk.set_option("relay_device", -1)
+        return
+    sizes = [200000, 0, 7, 1500000, 33, 900001]
+    h, off = mvs.synthetic.ragged_batch(sizes, seed=77)
+    want = oracle_csr(h, off, 2048)
+    pin = pinned_empty(len(h), np.uint64)
+    pin.a[:] = h
+    pk = pinned_empty(7 * len(h), np.uint8)
+    mvs.pack56(h, out=pk.a)
+    sk.set_option("slice_hashes", 1 << 19)
+    try:
+        sk.set_option("relay_device", 1)
+        assert np.array_equal(sk.project_csr(pin.a, off, 2048), want)
+        assert np.array_equal(sk.project_csr_packed56(pk.a, off, 2048), want)
+        assert np.array_equal(sk.project_csr(h, off, 2048), want)         # pageable source: direct path
+        sk.set_option("relay_device", -1)
+        assert np.array_equal(sk.project_csr(pin.a, off, 2048), want)
+    finally:
+        sk.set_option("relay_device", -1)
+        sk.set_option("slice_hashes", 16 << 20)
+
+
 def test_device_resident_entry_point(sk):
     import torch
     h, off = mvs.synthetic.uniform_batch(64, 20000, seed=2)
