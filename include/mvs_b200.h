@@ -263,6 +263,14 @@ int mvs_get_timing(mvs_ctx* ctx, mvs_timing* t);    /* synchronises the context'
  *        IMAD.WIDE + one LOP3 per counted op). */
 int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second);
 
+/* The planner of the projection without a device (needs no GPU): how a CSR batch would be cut into warp tasks --
+ * (sample, hash range, 32-block column pass) -- on a GPU with `sm_count` SMs at dimension d.  Writes the chosen cap
+ * (hashes per task), the number of tasks and of partial rows; if the four task arrays are given (room for max_tasks
+ * entries) also the task list (begin = index into the batch's hash array).  For tests and capacity planning. */
+int mvs_plan_tasks(const uint64_t* offsets, int64_t n_samples, int d, int sm_count, uint64_t* cap_hashes,
+                   uint64_t* n_tasks, uint64_t* n_partial_rows, uint64_t* task_begin, uint32_t* task_count,
+                   uint32_t* task_sample, uint32_t* task_pass, uint64_t max_tasks);
+
 /* Second roofline denominator: warp rounds per second (one round = one hash x 32 lanes x 64 columns) that the GPU
  * sustains for the projection loop's own instruction mix when no instruction waits for an operand (loop_mix_kernel:
  * the same opcodes in the same proportions on independent register sets, same residency).  The projection kernel

@@ -87,6 +87,8 @@ SIGNATURES = {
     "mvs_bind_host_to_device": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "mvs_get_timing": (C.c_int, [C.c_void_p, C.POINTER(Timing)]),
     "mvs_int_issue_peak": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),
+    "mvs_plan_tasks": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                 C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]),
     "mvs_loop_mix_peak": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "mvs_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "mvs_has_experiments": (C.c_int, []),

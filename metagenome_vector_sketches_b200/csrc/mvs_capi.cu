@@ -1122,6 +1122,35 @@ int mvs_int_issue_peak(mvs_ctx* ctx, int which, double* ops_per_second)
     return MVS_OK;
 }
 
+// The planner without a device: how a batch would be cut into warp tasks on a GPU with `sm_count` SMs.  Host only.
+int mvs_plan_tasks(const uint64_t* offsets, int64_t n_samples, int d, int sm_count, uint64_t* cap_hashes, uint64_t* n_tasks,
+                   uint64_t* n_partial_rows, uint64_t* task_begin, uint32_t* task_count, uint32_t* task_sample,
+                   uint32_t* task_pass, uint64_t max_tasks)
+{
+    if (!offsets || n_samples < 0 || d <= 0 || sm_count <= 0) return MVS_ERR_INVALID_ARG;
+    const Geometry g = make_geometry(d);
+    const Chunker ch{choose_cap(offsets, 0, n_samples, g, sm_count), g.quantum};
+    PlanCounts pc;
+    const int rc = count_plan(offsets, 0, n_samples, g, ch, pc);
+    if (rc != MVS_OK) return rc;
+    if (cap_hashes) *cap_hashes = ch.cap;
+    if (n_tasks) *n_tasks = pc.tasks;
+    if (n_partial_rows) *n_partial_rows = pc.prows;
+    if (task_begin && task_count && task_sample && task_pass) {
+        if (pc.tasks > max_tasks) return MVS_ERR_TOO_LARGE;
+        std::vector<WarpTask> tasks(static_cast<size_t>(pc.tasks) + 1);
+        std::vector<ReduceItem> reduce(static_cast<size_t>(pc.reduce) + 1);
+        emit_plan(offsets, 0, n_samples, offsets[0], 0, g, ch, tasks.data(), reduce.data());
+        for (uint64_t i = 0; i < pc.tasks; ++i) {
+            task_begin[i] = tasks[i].begin;
+            task_count[i] = tasks[i].count;
+            task_sample[i] = tasks[i].sample;
+            task_pass[i] = tasks[i].pass;
+        }
+    }
+    return MVS_OK;
+}
+
 int mvs_loop_mix_peak(mvs_ctx* ctx, double* rounds_per_second)
 {
     if (!ctx || !rounds_per_second) return MVS_ERR_INVALID_ARG;

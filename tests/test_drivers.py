@@ -229,6 +229,71 @@ def test_partition_is_contiguous_balanced_cover():
     assert b[0] == 0 and b[-1] == 10 and np.all(np.diff(b) >= 0)
 
 
+def _plan(offsets, d, sm_count=148):
+    lib = mvs.load_library()
+    off = np.ascontiguousarray(offsets, dtype=np.uint64)
+    n = len(off) - 1
+    cap, nt, pr = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    assert lib.mvs_plan_tasks(off.ctypes.data, n, d, sm_count, C.byref(cap), C.byref(nt), C.byref(pr), None, None, None, None, 0) == 0
+    t = int(nt.value)
+    begin, count = np.zeros(t + 1, np.uint64), np.zeros(t + 1, np.uint32)
+    sample, pas = np.zeros(t + 1, np.uint32), np.zeros(t + 1, np.uint32)
+    assert lib.mvs_plan_tasks(off.ctypes.data, n, d, sm_count, C.byref(cap), C.byref(nt), C.byref(pr), begin.ctypes.data,
+                              count.ctypes.data, sample.ctypes.data, pas.ctypes.data, t) == 0
+    return int(cap.value), t, int(pr.value), begin[:t], count[:t], sample[:t], pas[:t]
+
+
+@pytest.mark.parametrize("d", [1, 64, 200, 256, 512, 2048, 2049, 4096, 5000])
+def test_planner_tasks_cover_every_hash_exactly_once_per_pass(d):
+    """The host-side planner (no GPU): every (sample, column pass) is covered by contiguous chunks that partition the
+    sample's hash range; chunk sizes respect the kernel's limits (multiple of the trip quantum except the last chunk of
+    a sample, at most 65535 hashes per 64-column block and 16320 rounds per lane)."""
+    rng = np.random.default_rng(d)
+    sizes = np.concatenate([[0, 1, 63, 64, 65, 16320, 16321, 70000, 0, 1_300_000], rng.integers(0, 40000, 300)])
+    off = np.zeros(len(sizes) + 1, dtype=np.uint64)
+    off[1:] = np.cumsum(sizes)
+    off += np.uint64(12345)                                           # offsets[0] need not be 0
+    cap, t, prows, begin, count, sample, pas = _plan(off, d)
+    nb = (d + 63) // 64
+    passes = (nb + 31) // 32
+    lph = 32 if nb >= 32 else 1 << max(0, (nb - 1).bit_length())
+    S = 32 // lph
+    max_rounds = min(16320, (65535 // S) // 64 * 64)
+    quantum = min(64 * S, max(256, 16 * S))
+    assert cap <= max_rounds * S and cap % quantum == 0
+    assert count.max() <= cap
+    covered = {}
+    for b, c, s_, p_ in zip(begin, count, sample, pas):
+        covered.setdefault((int(s_), int(p_)), []).append((int(b), int(c)))
+    for s_ in range(len(sizes)):
+        for p_ in range(passes):
+            chunks = sorted(covered.get((s_, p_), []))
+            assert chunks, (s_, p_)
+            pos = int(off[s_] - off[0])
+            for i, (b, c) in enumerate(chunks):
+                assert b == pos and (c % quantum == 0 or i == len(chunks) - 1)
+                pos += c
+            assert pos == int(off[s_ + 1] - off[0])
+    assert t == sum(len(v) for v in covered.values())
+    assert prows == sum(len(v) for (s_, p_), v in covered.items() if p_ == 0 and len(v) > 1)
+
+
+def test_planner_avoids_a_nearly_empty_last_wave():
+    """BASELINE configs[2] at d = 256 (1024 x 100 000 hashes): round 1 cut 7168 tasks = 13 CTAs on the busiest of 148
+    SMs with the 13th almost alone; the SM-quantisation model picks 4096 (7 per SM), which is also what the GPU
+    measured as fastest (profiles/r02e_ab_kernel.jsonl).  Big launches keep the largest task the bit planes allow."""
+    off = np.arange(1025, dtype=np.uint64) * np.uint64(100000)
+    cap, t, *_ = _plan(off, 256)
+    assert t == 4096
+    off2 = np.arange(10001, dtype=np.uint64) * np.uint64(50000)        # configs[1]
+    cap2, t2, *_ = _plan(off2, 2048)
+    assert cap2 == 16320 and t2 == 40000
+    # a tiny batch is cut fine enough to occupy many SMs
+    off3 = np.arange(4, dtype=np.uint64) * np.uint64(40000)
+    cap3, t3, *_ = _plan(off3, 2048)
+    assert cap3 == 512 and t3 >= 3 * 78
+
+
 def test_cli_grammar_and_exit_codes(tmp_path):
     pe = os.path.join(BIN, "project_everything")
     sp = os.path.join(BIN, "standalone_projection")
