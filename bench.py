@@ -314,6 +314,15 @@ def run_gpu(args):
         if via is not None and via != local:
             sk.set_option("relay_device", via)
             relay["via"] = via
+            if args.relay_percent >= 0:
+                pct = args.relay_percent
+            else:
+                # balanced split for rates that stay as probed: a slow rank (rate s_) keeps x = 2 s_/(f_ + s_) of its
+                # bytes on its own link and relays 1 - x, so that its link and its partner's (own 4 GB + relayed) finish together
+                s_, f_ = rates[rank], rates[via] if via < world else max(rates)
+                pct = int(round(100.0 * max(0.0, 1.0 - 2.0 * s_ / (f_ + s_))))
+            sk.set_option("relay_percent", pct)
+            relay["percent"] = pct
         viat = torch.tensor([-1.0 if relay["via"] is None else float(relay["via"])], dtype=torch.float64, device=dev)
         allv = [torch.zeros_like(viat) for _ in range(world)]
         dist.all_gather(allv, viat)
@@ -538,6 +547,8 @@ def main():
     ap.add_argument("--relay", default="auto",
                     help="N > 1 end-to-end leg: auto = probe the ranks' concurrent H2D rates and route the slow half through "
                          "partners of the fast half (relay_device); off; force:<device> = every rank relays through that device")
+    ap.add_argument("--relay-percent", type=int, default=-1,
+                    help="share of a relaying rank's slice bytes that takes the relay (default: from the probe, 1 - 2s/(f+s))")
     ap.add_argument("--no-packed", action="store_true", help="skip the packed56 end-to-end leg (N = 1)")
     ap.add_argument("--no-config3", action="store_true", help="skip the BASELINE configs[2] dimension sweep (N = 1 leg)")
     ap.add_argument("--c4-samples", type=int, default=100000,

@@ -288,6 +288,9 @@ int mvs_loop_mix_peak(mvs_ctx* ctx, double* rounds_per_second);
  *       unequal host-memory ceilings: ranks on the starved root route through a partner on the other one (bench.py
  *       probes the ranks' concurrent H2D rates and pairs them).  Pinned sources only; pageable
  *       ones keep the direct path;
+ *   "relay_percent" (0..100, default 100): share of the slice bytes that takes the relay, the rest keeps this device's
+ *       own link (slices alternate by error diffusion) -- when both PCIe roots still add bandwidth to each other the
+ *       balanced split is 1 - 2s/(f+s) of a slow rank's bytes for concurrent rates s (slow) and f (fast);
  *   "release_workspace" (any value): frees the device and pinned buffers the pairwise entry points keep between calls
  *       (they are grow-only and otherwise live until mvs_destroy).
  * The A/B knobs of round 1 ("task_cap", "pairwise_path", "pairwise_limbs", "pairwise_pair", "pairwise_cluster",

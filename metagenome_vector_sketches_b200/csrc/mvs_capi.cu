@@ -66,6 +66,8 @@ struct Relay {
     cudaStream_t stream[kSlots] = {nullptr, nullptr, nullptr};
     cudaEvent_t landed[kSlots] = {nullptr, nullptr, nullptr};
     uint64_t bytes = 0;                          // relayed by the last batch call
+    int percent = 100;                           // share of the slice bytes that takes the relay (the rest goes direct)
+    int64_t credit = 0;                          // error-diffusion accumulator of that share
 };
 
 struct Geometry {
@@ -474,6 +476,11 @@ int upload_slice(mvs_ctx* ctx, Slot& sl, int k, void* dst, const void* src, size
         cudaPointerAttributes at{};
         if (cudaPointerGetAttributes(&at, src) == cudaSuccess) pinned = at.type == cudaMemoryTypeHost;
         else cudaGetLastError();
+    }
+    if (pinned && r.percent < 100) {             // split by bytes: this slice takes the relay when its share is due
+        r.credit += static_cast<int64_t>(bytes / 1024) * r.percent;
+        if (r.credit >= static_cast<int64_t>(bytes / 1024) * 50) r.credit -= static_cast<int64_t>(bytes / 1024) * 100;
+        else pinned = false;
     }
     if (!pinned) return mvs_internal_upload(ctx, sl.stream, dst, src, bytes);
     MVS_CUDA(ctx, cudaSetDevice(r.device));
@@ -1207,6 +1214,7 @@ int mvs_set_option(mvs_ctx* ctx, const char* key, int64_t value)
             if (sl.stream) cudaStreamSynchronize(sl.stream);
         return relay_setup(ctx, static_cast<int>(value));
     }
+    if ((r = set("relay_percent", 0, 100, [&] { ctx->relay.percent = static_cast<int>(value); ctx->relay.credit = 0; })) != 1) return r;
     if ((r = set("release_workspace", INT64_MIN, INT64_MAX, [&] { cudaSetDevice(ctx->device); cudaDeviceSynchronize(); release_workspace(ctx); })) != 1) return r;
 #ifdef MVS_EXPERIMENTS                           // A/B knobs of the experiment build (libmvs_b200_exp.so); the shipped library rejects them
     if ((r = set("task_cap", 0, INT64_MAX, [&] { ctx->task_cap = static_cast<uint64_t>(value); })) != 1) return r;
