@@ -48,7 +48,8 @@ typedef enum mvs_status {
     MVS_ERR_CUDA = -3,          /* a CUDA call failed: see mvs_last_cuda_error() */
     MVS_ERR_OOM = -4,           /* host or device allocation failed */
     MVS_ERR_TOO_LARGE = -5,     /* a sample has >= 2^31 hashes (int32 accumulator, as the reference) */
-    MVS_ERR_IO = -6             /* file could not be opened / written (driver helpers) */
+    MVS_ERR_IO = -6,            /* file could not be opened / written (driver helpers) */
+    MVS_ERR_SCRATCH_LIMIT = -7  /* mvs_project_device_static: the call needs more than MVS_STATIC_SCRATCH_BYTES */
 } mvs_status;
 
 /* ---- lifetime --------------------------------------------------------------------- */
@@ -111,6 +112,30 @@ int mvs_sketch_batch_multi(mvs_ctx* const* ctxs, int n_ctx, const uint64_t* hash
  * context's own stream).  Asynchronous w.r.t. the host unless `stream` is NULL.      */
 int mvs_project_device(mvs_ctx* ctx, const uint64_t* d_hashes, const uint64_t* h_offsets,
                        int64_t n_samples, int d, uint64_t seed, int32_t* d_out, void* stream);
+
+/* mvs_project_device WITHOUT ANY ALLOCATION.  This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arguments, same result (bit-identical rows) as mvs_project_device, but the
+ * launch's scratch -- warp tasks, reduce items and the partial rows of samples that are split over several warps --
+ * lives in a file-scope `static __device__` array of MVS_STATIC_SCRATCH_BYTES inside the library, which every GPU
+ * that loads the library holds until the process exits.  The call performs no cudaMalloc / cudaFree / cudaMallocHost
+ * and calls no allocating library routine; the plan is built in a static host image and copied with one
+ * cudaMemcpyAsync from pageable memory (the host therefore waits for earlier work on `stream` before the call returns).
+ *   limit    the plan must fit the array: 32 B per warp task (>= one per sample and 32-block column pass),
+ *            16 B per split sample, d * 4 B per partial row.  `*scratch_needed` (may be NULL) receives the bytes
+ *            this call needs; beyond MVS_STATIC_SCRATCH_BYTES the call does nothing and returns
+ *            MVS_ERR_SCRATCH_LIMIT -- use mvs_project_device for such batches.
+ *   sharing  ALL calls on one GPU (any context, any stream) use the same array.  Calls on one stream are ordered by
+ *            the stream; calls whose kernels may overlap on the GPU (different streams, different contexts or host
+ *            threads on one device) RACE on it and produce garbage: serialise them.  The array keeps the last
+ *            call's contents; nothing in it has to start at zero (every partial row is stored in full before it is
+ *            read), so nothing is cleared.
+ *   first call per device resolves the array's address (cudaGetSymbolAddress) and may load the CUDA module: issue
+ *   one call before entering a region that forbids it. */
+#define MVS_STATIC_SCRATCH_BYTES (16u << 20)
+int mvs_project_device_static(mvs_ctx* ctx, const uint64_t* d_hashes, const uint64_t* h_offsets,
+                              int64_t n_samples, int d, uint64_t seed, int32_t* d_out, void* stream,
+                              uint64_t* scratch_needed);
 
 /* Epilogue of sketch() on device-resident vectors (reference
  * src/project_everything.cpp:327-347): per row the exact integer sum of squares, the reference's

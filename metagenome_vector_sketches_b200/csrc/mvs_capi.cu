@@ -18,6 +18,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -539,6 +540,8 @@ const char* mvs_strerror(int status)
         case MVS_ERR_OOM: return "out of memory";
         case MVS_ERR_TOO_LARGE: return "sample or batch too large (>= 2^31 hashes in one sample, or >= 2^32 tasks)";
         case MVS_ERR_IO: return "I/O error";
+        case MVS_ERR_SCRATCH_LIMIT:
+            return "the call needs more scratch than MVS_STATIC_SCRATCH_BYTES (mvs_project_device_static): use mvs_project_device";
         default: return "unknown mvs status";
     }
 }
@@ -742,6 +745,107 @@ int mvs_project_device(mvs_ctx* ctx, const uint64_t* d_hashes, const uint64_t* h
     if ((rc = launch_range(ctx, sl, pc, d_hashes, g, seed, d_out, st, true, sl.stream)) != MVS_OK) return rc;
     MVS_CUDA(ctx, cudaEventRecord(sl.done, st));
     sl.busy = true;
+    if (!stream) MVS_CUDA(ctx, cudaStreamSynchronize(st));
+    return MVS_OK;
+}
+
+}  // extern "C"
+
+// ---- mvs_project_device_static: the device path without any allocation -------------------------------------------
+// No counterpart in the reference; added for callers that may not allocate
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The three scratch areas of a projection
+// launch -- warp tasks, reduce items, partial rows (what Slot::tasks / reduce / partials hold on the allocating paths)
+// -- live in ONE file-scope device array of MVS_STATIC_SCRATCH_BYTES that every GPU which loads this library holds
+// until the process exits.  In host code `g_static_scratch` is only the host-side stand-in of the symbol, never a device
+// address: static_scratch_base() resolves it with cudaGetSymbolAddress once per device, with that device current, and
+// only that pointer reaches cudaMemcpyAsync and the kernels.
+static __device__ __align__(256) unsigned char g_static_scratch[MVS_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mutex;                                   // guards the two tables below (host side only)
+void* g_static_scratch_base[kStaticMaxDevices] = {};         // device address of g_static_scratch, per device
+// host image of the plan (tasks + reduce items) of the call being issued: a pageable cudaMemcpyAsync has left it when
+// it returns (the driver stages it), so one image serves all calls; .bss, pages are touched only as far as plans reach
+alignas(256) unsigned char g_static_plan_image[MVS_STATIC_SCRATCH_BYTES];
+
+constexpr size_t align256(size_t x) { return (x + 255) & ~static_cast<size_t>(255); }
+
+// device must be current; caller holds g_static_mutex
+int static_scratch_base(mvs_ctx* ctx, unsigned char** base)
+{
+    if (ctx->device < 0 || ctx->device >= kStaticMaxDevices) return MVS_ERR_INVALID_ARG;
+    void*& slot = g_static_scratch_base[ctx->device];
+    if (!slot) {
+        void* p = nullptr;
+        MVS_CUDA(ctx, cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p || (reinterpret_cast<uintptr_t>(p) & 255) != 0) return MVS_ERR_CUDA;
+        slot = p;
+    }
+    *base = static_cast<unsigned char*>(slot);
+    return MVS_OK;
+}
+
+struct StaticLayout {
+    size_t reduce_off = 0, partials_off = 0, total = 0;
+};
+
+StaticLayout static_layout(const PlanCounts& pc, int d)
+{
+    StaticLayout l;
+    l.reduce_off = align256(pc.tasks * sizeof(WarpTask));
+    l.partials_off = align256(l.reduce_off + pc.reduce * sizeof(ReduceItem));
+    l.total = l.partials_off + pc.prows * static_cast<size_t>(d) * sizeof(int32_t);
+    return l;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mvs_project_device_static(mvs_ctx* ctx, const uint64_t* d_hashes, const uint64_t* h_offsets, int64_t n_samples,
+                              int d, uint64_t seed, int32_t* d_out, void* stream, uint64_t* scratch_needed)
+{
+    if (scratch_needed) *scratch_needed = 0;
+    if (!ctx || !h_offsets || n_samples < 0 || d <= 0 || (!d_out && n_samples > 0)) return MVS_ERR_INVALID_ARG;
+    if (n_samples == 0) return MVS_OK;
+    if (n_samples >= 0xFFFFFFF0ll) return MVS_ERR_TOO_LARGE;
+    if (!d_hashes && h_offsets[n_samples] > h_offsets[0]) return MVS_ERR_INVALID_ARG;
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->slots[0].stream;
+    const Geometry g = make_geometry(d);
+
+    // the planner's cap first (same tasks as mvs_project_device); if its partial rows do not fit, the largest cap
+    Chunker ch{choose_cap(h_offsets, 0, n_samples, g, ctx->sm_count), g.quantum};
+    PlanCounts pc;
+    int rc = count_plan(h_offsets, 0, n_samples, g, ch, pc);
+    if (rc != MVS_OK) return rc;
+    StaticLayout lay = static_layout(pc, d);
+    if (lay.total > MVS_STATIC_SCRATCH_BYTES && ch.cap < g.cap) {
+        ch.cap = g.cap;
+        if ((rc = count_plan(h_offsets, 0, n_samples, g, ch, pc)) != MVS_OK) return rc;
+        lay = static_layout(pc, d);
+    }
+    if (scratch_needed) *scratch_needed = lay.total;
+    if (lay.total > MVS_STATIC_SCRATCH_BYTES) return MVS_ERR_SCRATCH_LIMIT;
+    if (pc.tasks == 0) return MVS_OK;
+
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    unsigned char* base = nullptr;
+    if ((rc = static_scratch_base(ctx, &base)) != MVS_OK) return rc;
+    emit_plan(h_offsets, 0, n_samples, 0, 0, g, ch, reinterpret_cast<WarpTask*>(g_static_plan_image),
+              reinterpret_cast<ReduceItem*>(g_static_plan_image + lay.reduce_off));
+    // one copy: tasks, padding, reduce items.  Stream order puts it after the previous call's kernels on `st`.
+    const size_t plan_bytes = lay.reduce_off + pc.reduce * sizeof(ReduceItem);
+    MVS_CUDA(ctx, cudaMemcpyAsync(base, g_static_plan_image, plan_bytes, cudaMemcpyHostToDevice, st));
+    // Nothing in the scratch has to start at zero: the projection kernel STORES every column of every partial row of
+    // this plan before the reduce kernel reads it, and rows of earlier calls are never read.
+    Slot view;                                               // pointers into the static array, nothing owned
+    view.tasks.p = base;
+    view.reduce.p = base + lay.reduce_off;
+    view.partials.p = base + lay.partials_off;
+    if ((rc = launch_range(ctx, view, pc, d_hashes, g, seed, d_out, st, false, st)) != MVS_OK) return rc;
     if (!stream) MVS_CUDA(ctx, cudaStreamSynchronize(st));
     return MVS_OK;
 }

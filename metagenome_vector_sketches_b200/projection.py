@@ -110,6 +110,18 @@ class Sketcher:
                                            C.c_void_p(stream) if stream else None),
               "mvs_project_device", self._h)
 
+    def project_device_static(self, d_hashes_ptr, h_offsets, d, d_out_ptr, seed=0, stream=None):
+        """mvs_project_device_static: project_device with the scratch in the library's static device array -- no
+        allocation in the call.  Returns the scratch bytes the call needed; MvsError (status -7) beyond the limit."""
+        h_offsets = np.ascontiguousarray(h_offsets, dtype=np.uint64)
+        n = len(h_offsets) - 1
+        needed = C.c_uint64(0)
+        check(self._lib.mvs_project_device_static(self._h, C.c_void_p(d_hashes_ptr), _ptr(h_offsets), n, int(d),
+                                                  C.c_uint64(seed), C.c_void_p(d_out_ptr),
+                                                  C.c_void_p(stream) if stream else None, C.byref(needed)),
+              "mvs_project_device_static", self._h)
+        return int(needed.value)
+
     def finalize_device(self, d_vec_ptr, n, d, d_sumsq_ptr, d_out16_ptr=None, stream=None, d_ref_norms_ptr=None):
         check(self._lib.mvs_finalize_device(self._h, C.c_void_p(d_vec_ptr), int(n), int(d),
                                             C.c_void_p(d_sumsq_ptr) if d_sumsq_ptr else None,
