@@ -333,6 +333,40 @@ def run_gpu(args):
     out_np = hout.numpy()
     for _ in range(min(args.warmup, 3)):
         sk.project_csr(h_np, off, d, out=out_np)
+    # ---- relay share: two more untimed steps balance it.  The probe's rates do not stay as probed once the relay runs
+    # (the host side of both PCIe roots is shared), so the split is corrected from what the steps themselves show: one
+    # step at the probe's share p0, one at p0 + 15, both all-gathered as (relaying ranks' time - direct ranks' time);
+    # that difference is linear in the share (profiles/r02s_*: 166.8 | 127.6 ms at 10 %, 155.6 | 141.7 at 21 %,
+    # 143.0 | 152.1 at 35 %, 114.3 | 152.1 at 50 %), its root is the share at which both groups finish together.
+    if world > 1 and args.relay_percent < 0 and any(v >= 0 for v in relay.get("via_per_rank", [])):
+        def one_step_gap(pct):
+            if relay["via"] is not None:
+                sk.set_option("relay_percent", pct)
+            barrier()
+            t0 = time.perf_counter()
+            sk.project_csr(h_np, off, d, out=out_np)
+            ms = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
+            allm = [torch.zeros_like(ms) for _ in range(world)]
+            dist.all_gather(allm, ms)
+            allm = [float(x.item()) for x in allm]
+            slow = max(m for m, v in zip(allm, relay["via_per_rank"]) if v >= 0)
+            fast = max(m for m, v in zip(allm, relay["via_per_rank"]) if v < 0)
+            return slow - fast
+        pcts = torch.tensor([float(relay.get("percent", -1))], dtype=torch.float64, device=dev)
+        allp = [torch.zeros_like(pcts) for _ in range(world)]
+        dist.all_gather(allp, pcts)
+        p0 = int(round(max(float(x.item()) for x in allp)))              # the same for every relaying rank up to probe noise
+        p1 = min(100, p0 + 15) if p0 <= 85 else p0 - 15
+        g0, g1 = one_step_gap(p0), one_step_gap(p1)
+        tuned = p0
+        if abs(g1 - g0) > 1e-3:
+            tuned = int(round(min(100.0, max(0.0, p0 - g0 * (p1 - p0) / (g1 - g0)))))
+        if relay["via"] is not None:
+            sk.set_option("relay_percent", tuned)
+        relay["percent_probe"] = p0
+        relay["percent"] = tuned
+        relay["tuning_gap_ms"] = [[p0, g0], [p1, g1]]
+        sk.project_csr(h_np, off, d, out=out_np)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
@@ -548,7 +582,8 @@ def main():
                     help="N > 1 end-to-end leg: auto = probe the ranks' concurrent H2D rates and route the slow half through "
                          "partners of the fast half (relay_device); off; force:<device> = every rank relays through that device")
     ap.add_argument("--relay-percent", type=int, default=-1,
-                    help="share of a relaying rank's slice bytes that takes the relay (default: from the probe, 1 - 2s/(f+s))")
+                    help="share of a relaying rank's slice bytes that takes the relay (default -1: 1 - 2s/(f+s) from the probe, then "
+                         "balanced over two untimed steps)")
     ap.add_argument("--no-packed", action="store_true", help="skip the packed56 end-to-end leg (N = 1)")
     ap.add_argument("--no-config3", action="store_true", help="skip the BASELINE configs[2] dimension sweep (N = 1 leg)")
     ap.add_argument("--c4-samples", type=int, default=100000,
