@@ -6,17 +6,16 @@
 //
 // The N^2 * d part -- the block products and the keep-test (reference :57-160, :949-983) -- runs on the GPU through
 // mvs_pairwise_shard.  The succinct shard files (reference :645-817) are written here on the host from the kept
-// pairs with the SAME containers the reference uses: std::unordered_map for the per-row grouping (its iteration
-// order decides the row order inside matrix.bin) and the third-party `bits` library the reference vendors
-// (bits/include/compact_vector.hpp, rice_sequence.hpp; -I<reference>/bits/include at build time, like Eigen for
-// the a1 shim).  Feeding the map in the reference's order -- block pair by block pair, rows then columns inside a
-// block, with the reference's chunk size max_bytes / (4d)^2 -- makes shard_K/{matrix.bin,row_index.bin,
+// pairs: std::unordered_map for the per-row grouping like the reference (its iteration order decides the row order
+// inside matrix.bin) and the in-tree writers of mvs_succinct.h for the two containers of the third-party `bits`
+// library the reference vendors (compact_vector, rice_sequence; pinned byte for byte against those headers by
+// tests/test_succinct.py).  Feeding the map in the reference's order -- block pair by block pair, rows then columns
+// inside a block, with the reference's chunk size max_bytes / (4d)^2 -- makes shard_K/{matrix.bin,row_index.bin,
 // neighbor_start.bin} byte-identical to the reference's, which tests/test_gpu_cli.py checks.
 // --max_memory_gb only fixes that order; the GPU tiling is independent of it.  --num_threads is accepted and unused.
 #include "../../include/mvs_b200.h"
 
-#include "compact_vector.hpp"
-#include "rice_sequence.hpp"
+#include "mvs_succinct.h"
 
 #include <algorithm>
 #include <chrono>
@@ -117,12 +116,12 @@ void write_shard(const std::string& folder, const std::vector<Pair>& ordered, co
         row_pos[at] = static_cast<uint64_t>(matrix.tellp());
         first_neighbor[at] = neighbors[0].first;
         ++at;
-        bits::compact_vector cv;
+        mvs_succinct::CompactVector cv;
         cv.build(jac.begin(), jac.size());
         cv.save(matrix);
         jaccard_bytes += cv.num_bytes();
         if (neighbors.size() == 1) continue;                           // a lone neighbour has no gap sequence
-        bits::rice_sequence<> rs;
+        mvs_succinct::RiceSequence rs;
         rs.encode(gaps.begin(), gaps.size());
         rs.save(matrix);
         neighbor_bytes += rs.num_bytes();
@@ -130,18 +129,18 @@ void write_shard(const std::string& folder, const std::vector<Pair>& ordered, co
     matrix.flush();
     matrix.close();
 
-    bits::compact_vector cv_rows;
+    mvs_succinct::CompactVector cv_rows;
     cv_rows.build(row_ids.begin(), row_ids.size());
     cv_rows.save(index);
     std::vector<uint64_t> pos_gaps(nrows ? nrows - 1 : 0);
     for (size_t i = 1; i < nrows; ++i) pos_gaps[i - 1] = row_pos[i] - row_pos[i - 1];
-    bits::compact_vector cv_pos;
+    mvs_succinct::CompactVector cv_pos;
     cv_pos.build(pos_gaps.begin(), pos_gaps.size());
     cv_pos.save(index);
     index.close();
 
     std::ofstream starts(folder + "neighbor_start.bin", std::ios::binary);
-    bits::rice_sequence<> rs_start;
+    mvs_succinct::RiceSequence rs_start;
     rs_start.encode(first_neighbor.begin(), first_neighbor.size());
     rs_start.save(starts);
     starts.close();
