@@ -172,6 +172,16 @@ typedef struct mvs_hash_batch {
 int mvs_parse_hash_file(const char* path, int named, mvs_hash_batch** out);
 void mvs_free_hash_batch(mvs_hash_batch* b);
 
+/* Binary form of a parsed hash file (the optional ".u64 sidecar" of SURVEY 8f rank 1; the reference has only the text
+ * form, src/project_everything.cpp:257-284): 64-byte header (magic "MVSU64\0\1", n_samples, n_hashes, names_bytes,
+ * payload_offset), u64 offsets[n_samples + 1], the names as NUL-terminated strings, zero padding to a multiple of
+ * 4096, then the CSR payload as u64 -- the batch exactly as mvs_parse_hash_file returned it.  mvs_parse_hash_file
+ * (and with it mvs_sketch_file, mvs_standalone_file and the CLIs) recognises the magic and loads such a file instead
+ * of parsing text: the same batch, hence the same db, without the parse.  A file whose sizes or offsets are
+ * inconsistent is refused with MVS_ERR_IO; a file without names where names are needed with MVS_ERR_INVALID_ARG.
+ * CLI: `project_everything pack <hash_file> <binary_file>`.  Needs no GPU. */
+int mvs_write_hash_batch(const mvs_hash_batch* b, const char* path);
+
 /* db/ writer of sketch() (reference src/project_everything.cpp:306-361): vectors.bin (int32
  * rows, or int16 if vec16 != NULL), vector_norms.txt ("<name> <norm>", %g), dimension.txt, dtype.txt.
  * The norm column is ref_norms (the reference's float32 value, file identical to the reference's) when

@@ -66,6 +66,7 @@ SIGNATURES = {
     "mvs_get_norms_mode": (C.c_int, []),
     "mvs_parse_hash_file": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.POINTER(HashBatch))]),
     "mvs_free_hash_batch": (None, [C.POINTER(HashBatch)]),
+    "mvs_write_hash_batch": (C.c_int, [C.POINTER(HashBatch), C.c_char_p]),
     "mvs_write_db": (C.c_int, [C.c_char_p, C.c_int64, C.c_int, C.POINTER(C.c_char_p), C.c_void_p, C.c_void_p,
                                C.c_void_p, C.c_void_p]),
     "mvs_partition_samples": (None, [C.c_void_p, C.c_int64, C.c_int, C.c_void_p]),

@@ -278,6 +278,50 @@ void host_free_any(void* p, int pinned)
     else std::free(p);
 }
 
+// ---- binary hash file (".u64 sidecar") ---------------------------------------------------------------
+// The parsed batch as it sits in memory, so that a second run over the same samples skips the text parse:
+//   header (64 B)   magic "MVSU64\0\1" | u64 n_samples | u64 n_hashes | u64 names_bytes | u64 payload_offset | zeros
+//   offsets         u64[n_samples + 1]
+//   names           n_samples NUL-terminated strings, names_bytes in total (0 = a file without names)
+//   padding         zeros up to payload_offset (a multiple of 4096)
+//   payload         u64[n_hashes], the CSR payload exactly as mvs_parse_hash_file returns it
+// Little endian like everything else here.  mvs_parse_hash_file recognises the magic (no text hash file starts with
+// it) and reads the payload straight into the pinned CSR buffer with parallel pread calls.
+constexpr char kBinMagic[8] = {'M', 'V', 'S', 'U', '6', '4', '\0', '\1'};
+constexpr uint64_t kBinHeader = 64, kBinAlign = 4096;
+
+struct BinHeader {
+    char magic[8];
+    uint64_t n_samples, n_hashes, names_bytes, payload_offset;
+    uint64_t reserved[3];
+};
+static_assert(sizeof(BinHeader) == kBinHeader, "binary hash file header is 64 bytes");
+
+bool write_all(int fd, const void* p, size_t n)
+{
+    const char* c = static_cast<const char*>(p);
+    while (n) {
+        const ssize_t w = ::write(fd, c, std::min<size_t>(n, size_t(1) << 30));
+        if (w <= 0) return false;
+        c += w;
+        n -= static_cast<size_t>(w);
+    }
+    return true;
+}
+
+bool pread_all(int fd, void* p, size_t n, uint64_t at)
+{
+    char* c = static_cast<char*>(p);
+    while (n) {
+        const ssize_t r = ::pread(fd, c, std::min<size_t>(n, size_t(1) << 30), static_cast<off_t>(at));
+        if (r <= 0) return false;
+        c += r;
+        n -= static_cast<size_t>(r);
+        at += static_cast<uint64_t>(r);
+    }
+    return true;
+}
+
 std::string format_g(double x)                   // default ostream formatting of a double (precision 6)
 {
     char buf[64];
@@ -301,6 +345,96 @@ void mvs_free_hash_batch(mvs_hash_batch* b)
     std::free(b);
 }
 
+// Binary hash file -> batch.  Everything a hostile or truncated file could break is checked before a byte of the
+// payload is trusted: sizes against the file size, monotone offsets ending at n_hashes, one NUL per name.
+static int load_binary_batch(int fd, const char* data, size_t size, int named, bool want_pinned, mvs_hash_batch** out)
+{
+    BinHeader h;
+    std::memcpy(&h, data, sizeof h);
+    const uint64_t n = h.n_samples;
+    if (n >= (uint64_t(1) << 40) || h.n_hashes >= (uint64_t(1) << 48) || h.names_bytes >= (uint64_t(1) << 40)) return MVS_ERR_IO;
+    const uint64_t off_bytes = (n + 1) * sizeof(uint64_t);
+    const uint64_t names_at = kBinHeader + off_bytes;
+    if (h.payload_offset % kBinAlign || h.payload_offset < names_at + h.names_bytes ||
+        h.payload_offset + h.n_hashes * sizeof(uint64_t) != size)
+        return MVS_ERR_IO;
+    if (named && n > 0 && h.names_bytes == 0) return MVS_ERR_INVALID_ARG;       // sketch() needs the names
+    const uint64_t* off = reinterpret_cast<const uint64_t*>(data + kBinHeader);   // 8-byte aligned: mmap base + 64
+    if (off[0] != 0 || off[n] != h.n_hashes) return MVS_ERR_IO;
+    for (uint64_t i = 0; i < n; ++i)
+        if (off[i + 1] < off[i]) return MVS_ERR_IO;
+
+    mvs_hash_batch* b = static_cast<mvs_hash_batch*>(std::calloc(1, sizeof(mvs_hash_batch)));
+    if (!b) return MVS_ERR_OOM;
+    b->n_samples = static_cast<int64_t>(n);
+    b->n_hashes = h.n_hashes;
+    b->offsets = static_cast<uint64_t*>(std::malloc(off_bytes));
+    if (!b->offsets) { mvs_free_hash_batch(b); return MVS_ERR_OOM; }
+    std::memcpy(b->offsets, off, off_bytes);
+    if (named) {
+        b->names = static_cast<char**>(std::calloc(static_cast<size_t>(n ? n : 1), sizeof(char*)));
+        if (!b->names) { mvs_free_hash_batch(b); return MVS_ERR_OOM; }
+        const char* p = data + names_at;
+        const char* e = p + h.names_bytes;
+        for (uint64_t i = 0; i < n; ++i) {
+            const char* z = static_cast<const char*>(std::memchr(p, 0, static_cast<size_t>(e - p)));
+            if (!z) { mvs_free_hash_batch(b); return MVS_ERR_IO; }
+            b->names[i] = static_cast<char*>(std::malloc(static_cast<size_t>(z - p) + 1));
+            if (!b->names[i]) { mvs_free_hash_batch(b); return MVS_ERR_OOM; }
+            std::memcpy(b->names[i], p, static_cast<size_t>(z - p) + 1);
+            p = z + 1;
+        }
+    }
+    const size_t bytes = sizeof(uint64_t) * (h.n_hashes + 2);
+    if (want_pinned) {
+        b->hashes = static_cast<uint64_t*>(host_alloc_any(bytes, &b->hashes_pinned));
+    } else {
+        b->hashes_pinned = 0;
+        b->hashes = static_cast<uint64_t*>(std::malloc(bytes));
+    }
+    if (!b->hashes) { mvs_free_hash_batch(b); return MVS_ERR_OOM; }
+    // payload: parallel pread into the (pinned) buffer, 64 MB pieces
+    const uint64_t total = h.n_hashes * sizeof(uint64_t), piece = uint64_t(64) << 20;
+    const int64_t pieces = static_cast<int64_t>((total + piece - 1) / piece);
+    int failed = 0;
+#pragma omp parallel for schedule(dynamic, 1) num_threads(std::min(8, omp_get_max_threads()))
+    for (int64_t k = 0; k < pieces; ++k) {
+        const uint64_t at = static_cast<uint64_t>(k) * piece, len = std::min(piece, total - at);
+        if (!pread_all(fd, reinterpret_cast<char*>(b->hashes) + at, len, h.payload_offset + at)) {
+#pragma omp atomic write
+            failed = 1;
+        }
+    }
+    if (failed) { mvs_free_hash_batch(b); return MVS_ERR_IO; }
+    *out = b;
+    return MVS_OK;
+}
+
+int mvs_write_hash_batch(const mvs_hash_batch* b, const char* path)
+{
+    if (!b || !path || b->n_samples < 0 || !b->offsets || (!b->hashes && b->n_hashes > 0)) return MVS_ERR_INVALID_ARG;
+    const uint64_t n = static_cast<uint64_t>(b->n_samples);
+    if (b->offsets[0] != 0 || b->offsets[n] != b->n_hashes) return MVS_ERR_INVALID_ARG;
+    BinHeader h{};
+    std::memcpy(h.magic, kBinMagic, sizeof kBinMagic);
+    h.n_samples = n;
+    h.n_hashes = b->n_hashes;
+    std::string names;
+    if (b->names)
+        for (uint64_t i = 0; i < n; ++i) names.append(b->names[i] ? b->names[i] : "").push_back('\0');
+    h.names_bytes = names.size();
+    const uint64_t head = kBinHeader + (n + 1) * sizeof(uint64_t) + names.size();
+    h.payload_offset = (head + kBinAlign - 1) / kBinAlign * kBinAlign;
+    const int fd = ::open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (fd < 0) return MVS_ERR_IO;
+    const std::string pad(static_cast<size_t>(h.payload_offset - head), '\0');
+    const bool ok = write_all(fd, &h, sizeof h) && write_all(fd, b->offsets, (n + 1) * sizeof(uint64_t)) &&
+                    write_all(fd, names.data(), names.size()) && write_all(fd, pad.data(), pad.size()) &&
+                    write_all(fd, b->hashes, b->n_hashes * sizeof(uint64_t));
+    const bool closed = ::close(fd) == 0;
+    return ok && closed ? MVS_OK : MVS_ERR_IO;
+}
+
 static int parse_hash_file_impl(const char* path, int named, bool want_pinned, mvs_hash_batch** out);
 
 int mvs_parse_hash_file(const char* path, int named, mvs_hash_batch** out)
@@ -314,6 +448,8 @@ static int parse_hash_file_impl(const char* path, int named, bool want_pinned, m
     *out = nullptr;
     Mapped mf(path);
     if (!mf.ok) return MVS_ERR_IO;
+    if (mf.size >= kBinHeader && std::memcmp(mf.data, kBinMagic, sizeof kBinMagic) == 0)
+        return load_binary_batch(mf.fd, mf.data, mf.size, named, want_pinned, out);
 
     // 1. line index + an upper bound of every line's token count (both parallel)
     const bool timing = std::getenv("MVS_TIMING") != nullptr;

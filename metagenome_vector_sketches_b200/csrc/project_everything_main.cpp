@@ -2,6 +2,8 @@
 //
 //   project_everything sketch  <hash_file> <index_folder> [-t N] [-d D] [--int16]     (reference grammar)
 //   project_everything convert <signature_folder> <hash_file> [-t N]
+//   project_everything pack    <hash_file> <binary_file>          (additive: the parsed batch in binary form, see
+//                                                                   mvs_write_hash_batch; sketch reads either form)
 // additive, all optional:      [-s|--seed S] [--gpus G | --devices a,b,..] [--norms reference|exact] [--quiet]
 // README / BASELINE spelling:  project_everything <input> <db>/ [-t N] [-d D] [-s S]
 //   (<input> a hash file -> sketch; a folder of *.sig.zip -> convert to <db>/hashes.txt.tmp, then sketch)
@@ -30,6 +32,8 @@ void usage(const char* argv0)
                  "      signature_folder : Path to folder containing signature files\n"
                  "      hash_file        : Output hash file path\n"
                  "      -t, --threads    : Number of threads (default: 1)\n\n"
+                 "  Pack mode (optional: a binary hash file that sketch reads without parsing text):\n"
+                 "    %s pack <hash_file> <binary_file>\n\n"
                  "  Sketch mode:\n"
                  "    %s sketch <hash_file> <index_folder> [-t threads] [-d dimension] [--int16]\n"
                  "      hash_file        : Input hash file path\n"
@@ -43,7 +47,7 @@ void usage(const char* argv0)
                  "      --norms          : reference (default: vector_norms.txt as the reference binary prints it\n"
                  "                         on this host) | exact (sqrt of the exact integer sum of squares / d)\n"
                  "      --quiet          : no per-sample progress lines\n",
-                 argv0, argv0);
+                 argv0, argv0, argv0);
 }
 
 bool parse_int(const char* s, long long& v)
@@ -64,7 +68,7 @@ bool is_dir(const std::string& p)
 
 int main(int argc, char** argv)
 {
-    enum { NONE, CONVERT, SKETCH, ONESHOT } mode = NONE;
+    enum { NONE, CONVERT, SKETCH, PACK, ONESHOT } mode = NONE;
     std::vector<std::string> pos;
     long long t = 1, d = 2048, gpus = 1;
     unsigned long long seed = 0;
@@ -75,6 +79,7 @@ int main(int argc, char** argv)
     int i = 1;
     if (argc > 1 && !std::strcmp(argv[1], "convert")) { mode = CONVERT; i = 2; }
     else if (argc > 1 && !std::strcmp(argv[1], "sketch")) { mode = SKETCH; i = 2; }
+    else if (argc > 1 && !std::strcmp(argv[1], "pack")) { mode = PACK; i = 2; }
     else if (argc > 1) mode = ONESHOT;
     for (; i < argc && !bad; ++i) {
         const std::string a = argv[i];
@@ -126,6 +131,20 @@ int main(int argc, char** argv)
     if (mode == CONVERT) {
         const int rc = mvs_convert_signatures(input.c_str(), output.c_str(), static_cast<int>(t), quiet ? 0 : 1);
         if (rc != MVS_OK) std::fprintf(stderr, "convert: %s\n", mvs_strerror(rc));
+        return 0;
+    }
+    if (mode == PACK) {                                                         // host only: parse, write the binary form
+        mvs_hash_batch* hb = nullptr;
+        int rc = mvs_parse_hash_file(input.c_str(), 1, &hb);
+        if (rc == MVS_OK) rc = mvs_write_hash_batch(hb, output.c_str());
+        if (rc == MVS_OK && !quiet)
+            std::printf("Packed %lld samples, %llu hashes into %s\n", static_cast<long long>(hb->n_samples),
+                        static_cast<unsigned long long>(hb->n_hashes), output.c_str());
+        mvs_free_hash_batch(hb);
+        if (rc != MVS_OK) {
+            std::fprintf(stderr, "pack: %s\n", mvs_strerror(rc));
+            return 2;
+        }
         return 0;
     }
     std::string tmp_hash_file;

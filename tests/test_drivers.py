@@ -121,6 +121,106 @@ def test_parser_toy_roundtrip(tmp_path):
         assert np.array_equal(s, np.unique(hashes[int(offsets[i]):int(offsets[i + 1])]))
 
 
+def _raw_batch(path, named):
+    """mvs_parse_hash_file -> (names, offsets, hashes) exactly as returned (no sorting)."""
+    lib = mvs.load_library()
+    hb = C.POINTER(_lib.HashBatch)()
+    rc = lib.mvs_parse_hash_file(str(path).encode(), int(named), C.byref(hb))
+    if rc != 0:
+        return rc, None
+    b = hb.contents
+    n = b.n_samples
+    off = np.ctypeslib.as_array(b.offsets, shape=(n + 1,)).copy()
+    hashes = np.ctypeslib.as_array(b.hashes, shape=(max(1, int(b.n_hashes)),))[: int(b.n_hashes)].copy()
+    names = [b.names[i] for i in range(n)] if named else None
+    lib.mvs_free_hash_batch(hb)
+    return 0, (names, off, hashes)
+
+
+def _write_text_case(path):
+    """ragged text hash file: empty sets, names with spaces, duplicates, a line without ':' (skipped), a long sample"""
+    rng = np.random.default_rng(31)
+    with open(path, "w") as f:
+        f.write("first sample: 5 3 5 9\n")
+        f.write("no colon here 1 2 3\n")
+        f.write("empty:\n")
+        f.write(": 7\n")
+        for i in range(40):
+            k = int(rng.integers(0, 3000))
+            f.write("s%d/x y.sig:" % i + "".join(" %d" % int(h) for h in rng.integers(0, 2 ** 64 - 1, k, dtype=np.uint64)) + "\n")
+        f.write("last: 18446744073709551615 0")                                     # no trailing newline
+
+
+def test_binary_hash_file_round_trip(tmp_path):
+    """pack: text -> batch -> binary file -> the same batch (names, offsets, payload order), in both parser modes, through
+    the library call and through `project_everything pack`."""
+    lib = mvs.load_library()
+    txt, binf = tmp_path / "h.txt", tmp_path / "h.u64"
+    _write_text_case(txt)
+    for named in (1, 0):
+        rc, want = _raw_batch(txt, named)
+        assert rc == 0
+        hb = C.POINTER(_lib.HashBatch)()
+        assert lib.mvs_parse_hash_file(str(txt).encode(), named, C.byref(hb)) == 0
+        assert lib.mvs_write_hash_batch(hb, str(binf).encode()) == 0
+        lib.mvs_free_hash_batch(hb)
+        raw = open(binf, "rb").read()
+        assert raw[:8] == b"MVSU64\x00\x01" and len(raw) % 8 == 0
+        n, nh, nb, pay = np.frombuffer(raw[8:40], dtype=np.uint64)
+        assert int(pay) % 4096 == 0 and len(raw) == int(pay) + 8 * int(nh) and int(n) == len(want[1]) - 1
+        assert np.array_equal(np.frombuffer(raw[int(pay):], dtype=np.uint64), want[2])   # the payload, verbatim
+        rc, got = _raw_batch(binf, named)
+        assert rc == 0 and got[0] == want[0] and np.array_equal(got[1], want[1]) and np.array_equal(got[2], want[2])
+        if named:                                     # a named file also serves the unnamed parser; not the reverse
+            rc, got0 = _raw_batch(binf, 0)
+            assert rc == 0 and got0[0] is None and np.array_equal(got0[2], want[2])
+        else:
+            assert _raw_batch(binf, 1)[0] == -1
+    pe = os.path.join(BIN, "project_everything")
+    if os.path.exists(pe):
+        out = tmp_path / "cli.u64"
+        r = subprocess.run([pe, "pack", str(txt), str(out)], capture_output=True, text=True)
+        assert r.returncode == 0 and "Packed 44 samples" in r.stdout
+        rc, want = _raw_batch(txt, 1)
+        rc2, got = _raw_batch(out, 1)
+        assert rc == 0 and rc2 == 0 and got[0] == want[0] and np.array_equal(got[1], want[1]) and np.array_equal(got[2], want[2])
+        r = subprocess.run([pe, "pack", str(tmp_path / "missing.txt"), str(out)], capture_output=True, text=True)
+        assert r.returncode == 2 and "pack:" in r.stderr
+
+
+def test_binary_hash_file_rejects_damaged_files(tmp_path):
+    lib = mvs.load_library()
+    txt, binf = tmp_path / "h.txt", tmp_path / "h.u64"
+    _write_text_case(txt)
+    hb = C.POINTER(_lib.HashBatch)()
+    assert lib.mvs_parse_hash_file(str(txt).encode(), 1, C.byref(hb)) == 0
+    assert lib.mvs_write_hash_batch(hb, str(binf).encode()) == 0
+    lib.mvs_free_hash_batch(hb)
+    good = bytearray(open(binf, "rb").read())
+    n = int(np.frombuffer(bytes(good[8:16]), dtype=np.uint64)[0])
+
+    def load(data):
+        p = tmp_path / "bad.u64"
+        open(p, "wb").write(bytes(data))
+        return _raw_batch(p, 1)[0]
+
+    assert load(good) == 0
+    assert load(good[:-8]) == -6                                                    # truncated payload
+    assert load(good + b"\0" * 8) == -6                                            # trailing bytes
+    assert load(good[:100]) == -6                                                   # header only
+    bad = bytearray(good); bad[16:24] = (10 ** 15).to_bytes(8, "little"); assert load(bad) == -6      # n_hashes lies
+    bad = bytearray(good); bad[8:16] = (n + 1).to_bytes(8, "little"); assert load(bad) == -6          # n_samples lies
+    bad = bytearray(good); bad[32:40] = (4097).to_bytes(8, "little"); assert load(bad) == -6          # payload offset
+    bad = bytearray(good)                                                           # offsets not monotone
+    bad[64 + 8 * 5:64 + 8 * 6] = (2 ** 40).to_bytes(8, "little")
+    assert load(bad) == -6
+    bad = bytearray(good)                                                           # names without terminators
+    nb = int(np.frombuffer(bytes(good[24:32]), dtype=np.uint64)[0])
+    at = 64 + 8 * (n + 1)
+    bad[at:at + nb] = b"x" * nb
+    assert load(bad) == -6
+
+
 @pytest.mark.parametrize("tag,i16", [("d2048", False), ("d2048_i16", True), ("d100", False)])
 @pytest.mark.parametrize("norms_from", ["ref_norms", "vec32"])
 def test_write_db_matches_reference_files(tmp_path, tag, i16, norms_from):

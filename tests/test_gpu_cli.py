@@ -113,6 +113,24 @@ def test_sketch_cli_readme_spelling_and_seed(tmp_path, toy_hash_file):
     assert r.returncode == 0 and "Error opening" in r.stderr            # reference returns 0 here
 
 
+def test_sketch_cli_from_binary_hash_file_writes_the_same_db(tmp_path, toy_hash_file):
+    """`pack` once, then sketch from the binary file (no text parse): the db is byte-identical to the one sketched from
+    the text file, at two dimensions, int16 and over two shards."""
+    packed = tmp_path / "toy.u64"
+    r = run([PE, "pack", toy_hash_file, str(packed)])
+    assert r.returncode == 0 and "Packed 61 samples, 261591 hashes" in r.stdout
+    for extra in (["-d", "2048"], ["-d", "100", "--int16"], ["--devices", "0,0"]):
+        a, b = tmp_path / "db_text", tmp_path / "db_bin"
+        ra = run([PE, "sketch", toy_hash_file, str(a), "--quiet"] + extra)
+        rb = run([PE, "sketch", str(packed), str(b), "--quiet"] + extra)
+        assert ra.returncode == 0 and rb.returncode == 0, (ra.stderr, rb.stderr)
+        assert "Loaded 61 hash sets from" in rb.stdout
+        for f in DB_FILES:
+            assert (a / f).read_bytes() == (b / f).read_bytes(), (extra, f)
+    ref = load_toy_ref("d2048")
+    assert hashlib.sha256((tmp_path / "db_bin" / "vectors.bin").read_bytes()).hexdigest() == ref["vectors_sha256"]
+
+
 def test_standalone_cli_matches_reference_stdout(tmp_path):
     for case in load_kat()["standalone"]:
         p = tmp_path / "q.hashes"
