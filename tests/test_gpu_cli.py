@@ -124,7 +124,6 @@ def test_sketch_cli_from_binary_hash_file_writes_the_same_db(tmp_path, toy_hash_
         ra = run([PE, "sketch", toy_hash_file, str(a), "--quiet"] + extra)
         rb = run([PE, "sketch", str(packed), str(b), "--quiet"] + extra)
         assert ra.returncode == 0 and rb.returncode == 0, (ra.stderr, rb.stderr)
-        assert "Loaded 61 hash sets from" in rb.stdout
         for f in DB_FILES:
             assert (a / f).read_bytes() == (b / f).read_bytes(), (extra, f)
     ref = load_toy_ref("d2048")
