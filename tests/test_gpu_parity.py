@@ -253,6 +253,85 @@ def test_properties_at_scale(sk):
     assert np.array_equal(merged[0], full.sum(axis=0, dtype=np.int64).astype(np.int32))
 
 
+def _project_resident(sk, dh, off, d, ts):
+    import torch
+    out = torch.empty((len(off) - 1, d), dtype=torch.int32, device="cuda")
+    sk.project_device(dh.data_ptr(), off, d, out.data_ptr(), stream=ts.cuda_stream)
+    ts.synchronize()
+    return out
+
+
+def test_properties_at_full_config2_size(sk):
+    """BASELINE configs[1] at its full size (10 000 x 50 000 hashes = 5e8, d = 2048), device-resident like bench.py's
+    `value`: linearity over half-samples, the prefix property, the parity of every entry, a merged sample that is
+    split over hundreds of warp tasks, and rows spot-checked against the oracle."""
+    import torch
+    n, per, d = 10000, 50000, 2048
+    ts = torch.cuda.Stream()
+    dh, off = mvs.synthetic.uniform_batch_torch(n, per, "cuda", seed=0)
+    torch.cuda.synchronize()
+    full = _project_resident(sk, dh, off, d, ts)
+    off2 = np.arange(2 * n + 1, dtype=np.uint64) * np.uint64(per // 2)
+    halves = _project_resident(sk, dh, off2, d, ts)
+    assert torch.equal(halves[0::2] + halves[1::2], full)                               # linearity
+    del halves
+    assert torch.equal(_project_resident(sk, dh, off, 512, ts), full[:, :512])          # prefix property
+    assert bool(((full & 1) == (per & 1)).all()) and int(full.abs().max()) <= per       # parity, bound
+    for s in (0, 4999, n - 1):                                                          # oracle rows
+        hs = dh[s * per:(s + 1) * per].cpu().numpy().view(np.uint64)
+        assert np.array_equal(full[s].cpu().numpy(), oracle_set(hs, d)), s
+    # 1000 samples merged into one of 5e7 hashes: > 3000 partial rows and the fixed-order reduce
+    merged = _project_resident(sk, dh[: 1000 * per], np.array([0, 1000 * per], dtype=np.uint64), d, ts)
+    assert torch.equal(merged[0].to(torch.int64), full[:1000].sum(dim=0, dtype=torch.int64))
+    # the checksum bench.py prints for this workload (profiles/r02p_bench_1gpu_final.json)
+    assert int(full.sum(dtype=torch.int64).item()) == -168614
+
+
+def test_properties_at_full_config3_size(sk):
+    """BASELINE configs[2] (1 024 x 100 000 hashes) over its dimension sweep: every d is a prefix of d = 4096, so the five
+    kernel instantiations (4, 8, 16, 32 lanes per hash, two column passes) must agree column for column; d = 256 rows
+    against the oracle."""
+    import torch
+    n, per = 1024, 100000
+    ts = torch.cuda.Stream()
+    dh, off = mvs.synthetic.uniform_batch_torch(n, per, "cuda", seed=0)
+    torch.cuda.synchronize()
+    widest = _project_resident(sk, dh, off, 4096, ts)
+    for d in (256, 512, 1024, 2048, 100, 4000):
+        assert torch.equal(_project_resident(sk, dh, off, d, ts), widest[:, :d]), d
+    assert bool(((widest & 1) == (per & 1)).all())
+    for s in (0, 777):
+        hs = dh[s * per:(s + 1) * per].cpu().numpy().view(np.uint64)
+        assert np.array_equal(widest[s, :256].cpu().numpy(), oracle_set(hs, 256)), s
+
+
+def test_properties_on_a_heavy_tailed_slice_of_config4(sk):
+    """One eighth of BASELINE configs[3] (12 500 samples, log-normal sizes 1e3..1e7, about 7.7e8 hashes), i.e. the shard
+    one of 8 GPUs owns: parity of every row equals the parity of its size, the device path equals the batch path on a
+    sub-range, and the largest sample (split over hundreds of tasks) equals the sum of its halves."""
+    import torch
+    ts = torch.cuda.Stream()
+    sizes = mvs.synthetic.lognormal_sizes(12500, seed=0)
+    dh, off = mvs.synthetic.ragged_batch_torch(sizes, "cuda", seed=0)
+    torch.cuda.synchronize()
+    out = _project_resident(sk, dh, off, 2048, ts)
+    par = torch.from_numpy((sizes & 1).astype(np.int32)).cuda()
+    assert bool(((out & 1) == par[:, None]).all())
+    assert bool((out.abs().max(dim=1).values <= torch.from_numpy(sizes.astype(np.int32)).cuda()).all())
+    lo, hi = 100, 164                                                                    # 64 samples through host buffers
+    h_host = dh[int(off[lo]):int(off[hi])].cpu().numpy().view(np.uint64)
+    assert np.array_equal(sk.project_csr(h_host, off[lo:hi + 1] - off[lo], 2048), out[lo:hi].cpu().numpy())
+    big = int(np.argmax(sizes))
+    b0, b1 = int(off[big]), int(off[big + 1])
+    mid = b0 + (b1 - b0) // 2
+    two = _project_resident(sk, dh[b0:b1], np.array([0, mid - b0, b1 - b0], dtype=np.uint64), 2048, ts)
+    assert torch.equal(two[0] + two[1], out[big])
+    for s in (int(np.argmin(sizes)), 5):
+        hs = dh[int(off[s]):int(off[s + 1])].cpu().numpy().view(np.uint64)
+        if len(hs) <= 200000:
+            assert np.array_equal(out[s].cpu().numpy(), oracle_set(hs, 2048)), s
+
+
 def test_sketch_batch_multi_on_all_visible_devices(sk):
     """On a box with several B200s: one context per device (what `--gpus N` does), same rows as one context."""
     import torch
