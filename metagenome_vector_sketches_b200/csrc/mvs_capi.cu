@@ -221,25 +221,34 @@ uint64_t count_tasks(const uint64_t* offsets, int64_t s0, int64_t s1, const Chun
 }
 
 // The per-launch task cap (hashes).  Large launches take the largest task the bit planes allow (fewest flushes and
-// partial rows).  Small launches are quantised by the machine: CTAs of kWarpsPerCta tasks are spread over the SMs, an
-// SM shares its issue slots evenly among its resident warps, so with equal tasks the launch lasts as long as the SM
-// that received the most CTAs -- time ~ ceil(CTAs / SMs) x (task + fixed cost per task).  Measured on config 3 at
-// d = 256 (1024 x 100 000 hashes, profiles/r02e_ab_kernel.jsonl): 3072 / 4096 / 7168 tasks = 6 / 7 / 13 CTAs on the
-// busiest SM run 0.60 / 0.52 / 0.53 ms, exactly this model.  So candidates on a geometric grid between 512 rounds and
-// the maximum are scored with it and the best one wins; launches with >= 64 CTAs per SM skip the search.
+// partial rows).  Small launches are scored with a three-term model of the machine and the best cap on a geometric grid
+// between 512 rounds and the maximum wins (launches with >= 64 CTAs per SM skip the search):
+//   * SM quantisation: CTAs of kWarpsPerCta tasks are spread over the SMs and an SM shares its issue slots among its
+//     resident warps, so with equal tasks the launch lasts as long as the SM that received the most CTAs:
+//     ceil(CTAs / SMs) / (CTAs / SMs).  Config 3 at d = 256 (1024 x 100 000 hashes): 7168 tasks = 12.1 CTAs per SM
+//     run 0.507 ms, 8192 tasks = 13.8 per SM 0.479 ms.
+//   * fixed cost per task (first tile's latency, flush): ~110 rounds.
+//   * tail: the last tasks of a launch run on nearly empty SMs, where a warp is no longer bound by issue slots but by
+//     the latency of its two-stage hash pipeline -- about 2.5 ns per hash of the task whatever d, i.e. 0.145 of the
+//     17.3 ns a warp round takes on a full sub-partition.  This is what makes 8192 tasks beat 4096 at d <= 1024
+//     (same quantisation, twice the fixed cost, half the tail).
+// Fitted on profiles/r02z_ksweep_c3.jsonl (config 3, k = 1..16 chunks per sample, d = 256..4096): the model's choice is the
+// measured optimum at d = 256 / 512 / 1024 and within 0.1 % of it at 2048 / 4096.
 uint64_t choose_cap(const uint64_t* offsets, int64_t s0, int64_t s1, const Geometry& g, int sm_count)
 {
     const uint64_t cap_max = g.cap;
     const uint64_t cap_min = std::min(cap_max, std::max<uint64_t>(512ull * g.S / g.quantum * g.quantum, g.quantum));
     const uint64_t total = offsets[s1] - offsets[s0];
     if (total == 0) return cap_max;
-    const double fixed = 96.0 * g.S;                                    // flush + start-up of a task, in hashes (~96 rounds)
+    const double fixed = 110.0 * g.S;                                   // flush + start-up of a task, in hashes (~110 rounds)
     const double sms = static_cast<double>(sm_count);
+    const double warp_rounds = static_cast<double>(total) * g.passes / g.S;          // of the whole launch
     auto score = [&](uint64_t cap, uint64_t tasks) {
         const double ctas = std::ceil(static_cast<double>(tasks) * g.passes / mvs::kWarpsPerCta);
         const double per_sm = ctas / sms;
         const double avg = static_cast<double>(total) / static_cast<double>(tasks);
-        return std::ceil(per_sm) / per_sm * (1.0 + fixed / avg);        // relative to perfectly divisible work
+        const double tail = 0.145 * avg * (4.0 * sms) / warp_rounds;    // one task at 2.5 ns per hash over the launch's time
+        return std::ceil(per_sm) / per_sm * (1.0 + fixed / avg) + tail; // relative to perfectly divisible work
     };
     Chunker ch{cap_max, g.quantum};
     const uint64_t tasks_max = count_tasks(offsets, s0, s1, ch);

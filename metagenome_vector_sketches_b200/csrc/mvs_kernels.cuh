@@ -129,16 +129,28 @@ __device__ __forceinline__ void mix_staged(ulonglong2 c, uint32_t off, uint32_t 
     eacc += static_cast<uint32_t>(__popc(t));
 }
 
-// tile pass: raw hash -> cooked record
-__device__ __forceinline__ ulonglong2 cook(uint64_t raw, uint64_t base, bool& risky)
+// tile pass: raw hash -> cooked record {hb, F, M} (see the header), stored as the two 8-byte halves of the 16-byte
+// record at shared address rec + OFF: {hb} and {F, M} are each produced in a register pair, so no moves into a register
+// quad are needed (a 16-byte store cost four IMAD.MOV per hash).  worst = max over the hashes of lo32(hb) << 2.
+template <int OFF>
+__device__ __forceinline__ void cook_store(uint32_t rec, uint64_t raw, uint64_t base, uint32_t& worst)
 {
     const uint64_t hb = raw + base;
     const uint32_t xl = static_cast<uint32_t>(hb);
     const uint32_t xh = static_cast<uint32_t>(hb >> 32);
-    risky |= (xl | 0xC0000000u) >= kCarryRisk;
+    worst = max(worst, xl << 2);                 // (xl mod 2^30) >= 2^30 - 2048  <=>  (xl << 2) >= 0xFFFFE000
     const uint32_t f = (xl >> 30) | (xh << 2);
     const uint32_t m = (xh ^ (xh >> 30)) * kK1lo;
-    return make_ulonglong2(hb, (static_cast<uint64_t>(m) << 32) | f);
+    asm volatile("st.shared.v2.u32 [%0 + %3], {%1, %2};" ::"r"(rec), "r"(xl), "r"(xh), "n"(OFF) : "memory");
+    asm volatile("st.shared.v2.u32 [%0 + %3], {%1, %2};" ::"r"(rec), "r"(f), "r"(m), "n"(OFF + 8) : "memory");
+}
+template <int I, int N>
+__device__ __forceinline__ void cook_rows(uint32_t rec, const uint64_t* __restrict__ st, uint64_t base, uint32_t& worst)
+{
+    if constexpr (I < N) {
+        cook_store<I * 512>(rec, st[I * 32], base, worst);               // rows of 32 lanes x 16 bytes
+        cook_rows<I + 1, N>(rec, st, base, worst);
+    }
 }
 
 // carry-save adder on 32 bit columns at once: s = a^b^c, c = maj(a,b,c)
@@ -287,6 +299,20 @@ __device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc, uint
     const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
 }
+// full copy with the same compile-time byte offset on both sides: one LDGSTS with immediate offsets, no address arithmetic
+template <int OFF>
+__device__ __forceinline__ void cp_async8_at(uint32_t smem_dst, const void* gsrc)
+{
+    asm volatile("cp.async.ca.shared.global [%0 + %2], [%1 + %2], 8;" ::"r"(smem_dst), "l"(gsrc), "n"(OFF) : "memory");
+}
+template <int I, int N>
+__device__ __forceinline__ void cp_async8_rows(uint32_t smem_dst, const void* gsrc)   // rows of 32 lanes x 8 bytes
+{
+    if constexpr (I < N) {
+        cp_async8_at<I * 256>(smem_dst, gsrc);
+        cp_async8_rows<I + 1, N>(smem_dst, gsrc);
+    }
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
@@ -344,6 +370,10 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
     auto issue_tile = [&](uint32_t t) {
         uint64_t* st = ring + (t & (kStages - 1)) * kTileHashes;
         const uint32_t base = t * kTileHashes;
+        if (base + kTileHashes <= count) {       // a full tile (all but the last of a task): no bounds, no zero-fill
+            cp_async8_rows<0, kTileHashes / 32>(static_cast<uint32_t>(__cvta_generic_to_shared(st + lane)), src + base + lane);
+            return;
+        }
 #pragma unroll
         for (int i = 0; i < kTileHashes / 32; ++i) {
             const uint32_t pos = base + i * 32 + lane;
@@ -361,10 +391,16 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
         __syncwarp();
         const uint64_t* st = ring + (t & (kStages - 1)) * kTileHashes;
         // tile pass: raw -> cooked records; vote whether any low word could reach bit 30 under + off
-        bool risky = false;
-#pragma unroll
-        for (int i = 0; i < kTileHashes / 32; ++i) cooked[i * 32 + lane] = cook(st[i * 32 + lane], base, risky);
-        const bool exact = __any_sync(0xffffffffu, risky);
+        uint32_t worst = 0;
+        {
+            // four rows (of 32 hashes) at a time: enough independent work to hide the LDS latency, few enough live
+            // register quads to stay at 6 CTAs per SM
+            uint32_t rec = static_cast<uint32_t>(__cvta_generic_to_shared(cooked + lane));
+            const uint64_t* raw = st + lane;
+#pragma unroll 1
+            for (int c = 0; c < kTileHashes / 128; ++c, rec += 4 * 512, raw += 4 * 32) cook_rows<0, 4>(rec, raw, base, worst);
+        }
+        const bool exact = __any_sync(0xffffffffu, worst >= (kCarryRisk << 2));
         __syncwarp();
         const uint32_t valid = min(count - t * kTileHashes, static_cast<uint32_t>(kTileHashes));
         const uint32_t rounds = (valid + S - 1) / S;

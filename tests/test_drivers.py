@@ -379,12 +379,15 @@ def test_planner_tasks_cover_every_hash_exactly_once_per_pass(d):
 
 
 def test_planner_avoids_a_nearly_empty_last_wave():
-    """BASELINE configs[2] at d = 256 (1024 x 100 000 hashes): round 1 cut 7168 tasks = 13 CTAs on the busiest of 148
-    SMs with the 13th almost alone; the SM-quantisation model picks 4096 (7 per SM), which is also what the GPU
-    measured as fastest (profiles/r02e_ab_kernel.jsonl).  Big launches keep the largest task the bit planes allow."""
+    """BASELINE configs[2] (1024 x 100 000 hashes): round 1 cut 7168 tasks at d = 256 = 12.1 CTAs per SM on 148 SMs, the
+    13th almost alone.  The planner's model (SM quantisation, fixed cost per task, latency-bound tail) picks 8192 tasks at
+    d <= 1024 and 16 384 (two column passes) at d = 4096, the measured optima of profiles/r02z_ksweep_c3.jsonl.  Big
+    launches keep the largest task the bit planes allow."""
     off = np.arange(1025, dtype=np.uint64) * np.uint64(100000)
-    cap, t, *_ = _plan(off, 256)
-    assert t == 4096
+    for d, want in ((256, 8192), (512, 8192), (1024, 8192), (4096, 16384)):
+        cap, t, *_ = _plan(off, d)
+        assert t == want, (d, t)
+    assert _plan(off, 2048)[1] in (8192, 15360)                        # equal within 0.1 % on the GPU
     off2 = np.arange(10001, dtype=np.uint64) * np.uint64(50000)        # configs[1]
     cap2, t2, *_ = _plan(off2, 2048)
     assert cap2 == 16320 and t2 == 40000
