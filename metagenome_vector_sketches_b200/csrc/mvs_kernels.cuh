@@ -215,9 +215,43 @@ __device__ __forceinline__ void group16(const ulonglong2* __restrict__ sp, uint3
 // at most 4).  With four groups per trip (d >= 1024) the carries of the groups meet inside the trip -- weight 16 pairwise
 // into weight 32, those into weight 64, rippled into planes 6.. -- so the loop carries no pending-carry state and has no
 // branch; shorter trips keep the pending words across trips (g = groups done so far, a multiple of TRIP).
-struct Pending { uint32_t c16lo, c16hi, c32lo, c32hi; };
+struct Pending { uint32_t c16lo, c16hi, c32lo, c32hi, c64lo, c64hi, c128lo, c128hi; };
 
-template <int S, bool EXACT, int TRIP>
+// A weight-64 carry (one per 64 rounds of the lane) joins the planes.  Rippling it through planes 6..13 at once costs
+// 32 LOP3 per 64 rounds (0.5 per round, 3.5 % of the loop's ALU-slot instructions); instead it is paired with the next
+// one by a carry-save adder on plane 6, those pairs on plane 7, and only the weight-256 carry is rippled (planes
+// 8..13): 0.14 LOP3 per round.  g = groups done before this trip (warp-uniform), so the branches do not diverge.
+// DEEP = false ripples at once: the one-group-per-trip instantiations (d <= 256) lose 1.3 % to the deeper branch nest
+// (config 3 at d = 256: 0.470 -> 0.477 ms), the others gain 1.1 % (config 2: 14.48 -> 14.32 ms).  All paths of one
+// instantiation (packed and plain 64-bit arithmetic) use the same scheme, because they share the pending words.
+template <bool DEEP>
+__device__ __forceinline__ void carry64(uint32_t (&Plo)[kPlanes], uint32_t (&Phi)[kPlanes], Pending& pend, uint32_t g,
+                                        uint32_t c64lo, uint32_t c64hi)
+{
+    if constexpr (!DEEP) {
+        ripple<6>(Plo, c64lo);
+        ripple<6>(Phi, c64hi);
+        return;
+    }
+    if ((g & 4u) == 0u) {
+        pend.c64lo = c64lo; pend.c64hi = c64hi;
+        return;
+    }
+    uint32_t c128lo, c128hi;
+    csa(c128lo, Plo[6], Plo[6], pend.c64lo, c64lo);
+    csa(c128hi, Phi[6], Phi[6], pend.c64hi, c64hi);
+    if ((g & 8u) == 0u) {
+        pend.c128lo = c128lo; pend.c128hi = c128hi;
+        return;
+    }
+    uint32_t c256lo, c256hi;
+    csa(c256lo, Plo[7], Plo[7], pend.c128lo, c128lo);
+    csa(c256hi, Phi[7], Phi[7], pend.c128hi, c128hi);
+    ripple<8>(Plo, c256lo);
+    ripple<8>(Phi, c256hi);
+}
+
+template <int S, bool EXACT, int TRIP, bool DEEP>
 __device__ __forceinline__ void trip_groups(const ulonglong2* __restrict__ sp, uint32_t off, uint32_t fold,
                                             uint32_t (&Plo)[kPlanes], uint32_t (&Phi)[kPlanes], Pending& pend, uint32_t g,
                                             uint32_t& eacc)
@@ -235,8 +269,7 @@ __device__ __forceinline__ void trip_groups(const ulonglong2* __restrict__ sp, u
         uint32_t c64lo, c64hi;
         csa(c64lo, Plo[5], Plo[5], c32lo[0], c32lo[1]);
         csa(c64hi, Phi[5], Phi[5], c32hi[0], c32hi[1]);
-        ripple<6>(Plo, c64lo);
-        ripple<6>(Phi, c64hi);
+        carry64<DEEP>(Plo, Phi, pend, g, c64lo, c64hi);
     } else if constexpr (TRIP == 2) {
         uint32_t alo, ahi, blo, bhi, c32lo, c32hi;
         group16<S, EXACT>(sp, off, fold, Plo, Phi, alo, ahi, eacc);
@@ -249,8 +282,7 @@ __device__ __forceinline__ void trip_groups(const ulonglong2* __restrict__ sp, u
             uint32_t c64lo, c64hi;
             csa(c64lo, Plo[5], Plo[5], pend.c32lo, c32lo);
             csa(c64hi, Phi[5], Phi[5], pend.c32hi, c32hi);
-            ripple<6>(Plo, c64lo);
-            ripple<6>(Phi, c64hi);
+            carry64<DEEP>(Plo, Phi, pend, g, c64lo, c64hi);
         }
     } else {
         uint32_t c16lo, c16hi;
@@ -267,8 +299,7 @@ __device__ __forceinline__ void trip_groups(const ulonglong2* __restrict__ sp, u
                 uint32_t c64lo, c64hi;
                 csa(c64lo, Plo[5], Plo[5], pend.c32lo, c32lo);
                 csa(c64hi, Phi[5], Phi[5], pend.c32hi, c32hi);
-                ripple<6>(Plo, c64lo);
-                ripple<6>(Phi, c64hi);
+                carry64<DEEP>(Plo, Phi, pend, g, c64lo, c64hi);
             }
         }
     }
@@ -339,6 +370,7 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
 #endif
     constexpr int kTrip = kGroupsPerTile >= 4 ? (MVS_TRIP_MAX < 4 ? MVS_TRIP_MAX : 4) : 1;
     static_assert(kGroupsPerTile % kTrip == 0, "a tile is a whole number of trips");
+    constexpr bool kDeep = kTrip >= 2;           // weight-64 carries deferred through two more adder levels (carry64)
 
     extern __shared__ __align__(16) uint64_t smem[];
     const int warp = threadIdx.x >> 5;
@@ -361,7 +393,7 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
     uint32_t Plo[kPlanes], Phi[kPlanes];
 #pragma unroll
     for (int p = 0; p < kPlanes; ++p) { Plo[p] = 0u; Phi[p] = 0u; }
-    Pending pend{0u, 0u, 0u, 0u};
+    Pending pend{0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
     uint32_t g = 0;                              // groups done (warp-uniform, a multiple of kTrip)
     uint32_t eacc = 0;                           // sum of popc(hi * fold) over this lane's hashes
 
@@ -407,17 +439,21 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
         const uint32_t ntrips = (rounds + 16 * kTrip - 1) / (16 * kTrip);   // the tile's tail is cooked zero padding
         if (!exact) {
             for (uint32_t ti = 0; ti < ntrips; ++ti, g += kTrip)
-                trip_groups<S, false, kTrip>(cooked + ti * (kTrip * 16 * S) + slot, off, fold, Plo, Phi, pend, g, eacc);
+                trip_groups<S, false, kTrip, kDeep>(cooked + ti * (kTrip * 16 * S) + slot, off, fold, Plo, Phi, pend, g, eacc);
         } else {                                 // 5e-4 of the tiles: plain 64-bit arithmetic, one group at a time (code size)
 #pragma unroll 1
             for (uint32_t gi = 0; gi < ntrips * kTrip; ++gi, ++g)
-                trip_groups<S, true, 1>(cooked + gi * (16 * S) + slot, off, fold, Plo, Phi, pend, g, eacc);
+                trip_groups<S, true, 1, kDeep>(cooked + gi * (16 * S) + slot, off, fold, Plo, Phi, pend, g, eacc);
         }
         __syncwarp();                            // stage and cooked tile may be overwritten next
     }
     // fold the pending carries (g = number of groups done)
     if (g & 1u) { ripple<4>(Plo, pend.c16lo); ripple<4>(Phi, pend.c16hi); }
     if (g & 2u) { ripple<5>(Plo, pend.c32lo); ripple<5>(Phi, pend.c32hi); }
+    if constexpr (kDeep) {
+        if (g & 4u) { ripple<6>(Plo, pend.c64lo); ripple<6>(Phi, pend.c64hi); }
+        if (g & 8u) { ripple<7>(Plo, pend.c128lo); ripple<7>(Phi, pend.c128hi); }
+    }
 
     // padding correction: this lane consumed 16*g hashes of which `mine` were real; the
     // others were zeros whose mixer output is the per-lane constant z.
