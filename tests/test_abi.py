@@ -30,6 +30,21 @@ def test_header_symbols_exported_and_bound():
     assert lib.mvs_abi_version() >= 1
 
 
+def test_every_entry_point_is_documented_for_integrators():
+    """INTEGRATION.md names the reference interface each entry point replaces (or says that it has none)."""
+    text = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    text = text.replace("`mvs_finalize(_device)`", "`mvs_finalize` `mvs_finalize_device`")
+    missing = [n for n in _declared_symbols() if n not in text]
+    assert not missing, missing
+    assert lib_status_texts_are_distinct()
+
+
+def lib_status_texts_are_distinct():
+    lib = mvs.load_library()
+    texts = [lib.mvs_strerror(c) for c in range(0, -8, -1)]
+    return len(set(texts)) == 8 and b"unknown" not in b" ".join(texts)
+
+
 def test_strerror_and_argument_checks_need_no_gpu():
     lib = mvs.load_library()
     assert lib.mvs_strerror(0) == b"ok"
