@@ -368,7 +368,10 @@ project_kernel(const uint64_t* __restrict__ hashes, const WarpTask* __restrict__
 #ifndef MVS_TRIP_MAX
 #define MVS_TRIP_MAX 2
 #endif
-    constexpr int kTrip = kGroupsPerTile >= 4 ? (MVS_TRIP_MAX < 4 ? MVS_TRIP_MAX : 4) : 1;
+#ifndef MVS_TRIP_MIN_GROUPS
+#define MVS_TRIP_MIN_GROUPS 4
+#endif
+    constexpr int kTrip = kGroupsPerTile >= MVS_TRIP_MIN_GROUPS ? (MVS_TRIP_MAX < 4 ? MVS_TRIP_MAX : 4) : 1;
     static_assert(kGroupsPerTile % kTrip == 0, "a tile is a whole number of trips");
     constexpr bool kDeep = kTrip >= 2;           // weight-64 carries deferred through two more adder levels (carry64)
 
