@@ -177,7 +177,10 @@ def test_carry_window_of_the_hoisted_add(sk):
     the exact path.  Build samples that sit in and around that window for every pass / seed."""
     golden = 0x9E3779B97F4A7C15
     rng = np.random.default_rng(77)
-    for d, seed in ((2048, 0), (2048, 12345), (4096, 0), (256, 0), (100, 2 ** 64 - 5), (5000, 7)):
+    # d = 512 / 1024: a tile is 4 / 8 Harley-Seal groups, so deferred weight-64 / weight-128 carries are pending when
+    # an exact tile follows a fast one (and the other way round)
+    for d, seed in ((2048, 0), (2048, 12345), (4096, 0), (256, 0), (100, 2 ** 64 - 5), (5000, 7), (512, 0), (1024, 3),
+                    (768, 11)):
         passes = (((d + 63) // 64) + 31) // 32
         sets = []
         for p in range(passes):
@@ -195,6 +198,11 @@ def test_carry_window_of_the_hoisted_add(sk):
             # a sparse mix: one risky hash hidden among ordinary ones (exercises exact and fast tiles)
             plain = rng.integers(0, 2 ** 63, 6000, dtype=np.uint64)
             plain[3333] = sets[-1][-7]
+            sets.append(np.unique(plain))
+            # several risky hashes spread over a long sample: exact tiles at many positions of the carry cycle
+            plain = np.sort(rng.integers(0, 2 ** 63, 40000, dtype=np.uint64))
+            risky = sets[-2][rng.integers(0, len(sets[-2]), 9)]
+            plain[[300, 700, 1100, 5000, 5300, 12345, 20000, 20300, 39000]] = risky
             sets.append(np.unique(plain))
         offsets = np.zeros(len(sets) + 1, dtype=np.uint64)
         offsets[1:] = np.cumsum([len(x) for x in sets])
