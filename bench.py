@@ -66,6 +66,16 @@ def load_kernel_profile(n, per, d):
     return prof, "cubin %s..., %s" % (key[:12], prof.get("source"))
 
 
+def balanced_relay_share(p0, g0, p1, g1):
+    """Share (percent) of a relaying rank's bytes that should take the relay, from two measured steps: g = (slowest
+    relaying rank's time - slowest direct rank's time) at shares p0 and p1.  The gap falls linearly with the share
+    (more relayed = relaying ranks faster, direct ranks slower); its root is where both groups finish together.  A gap
+    that does not move keeps p0; the result is clamped to [0, 100]."""
+    if abs(g1 - g0) <= 1e-3 or p1 == p0:
+        return int(p0)
+    return int(round(min(100.0, max(0.0, p0 - g0 * (p1 - p0) / (g1 - g0)))))
+
+
 def work_per_hash(d):
     """algorithmic int32 ops per hash, d sign-accumulates + 20 per splitmix64."""
     return d + 20 * ((d + 63) // 64)
@@ -358,9 +368,7 @@ def run_gpu(args):
         p0 = int(round(max(float(x.item()) for x in allp)))              # the same for every relaying rank up to probe noise
         p1 = min(100, p0 + 15) if p0 <= 85 else p0 - 15
         g0, g1 = one_step_gap(p0), one_step_gap(p1)
-        tuned = p0
-        if abs(g1 - g0) > 1e-3:
-            tuned = int(round(min(100.0, max(0.0, p0 - g0 * (p1 - p0) / (g1 - g0)))))
+        tuned = balanced_relay_share(p0, g0, p1, g1)
         if relay["via"] is not None:
             sk.set_option("relay_percent", tuned)
         relay["percent_probe"] = p0

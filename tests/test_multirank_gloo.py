@@ -50,3 +50,19 @@ def test_two_rank_sharding_reassembles():
         assert p.exitcode == 0
     assert ok and nrows == 10 and firsts[0] == 0 and 0 < firsts[1] < 10
     assert slowest == 11.0
+
+
+def test_bench_relay_share_root():
+    """bench.py's secant step for the relay share (8-GPU boxes with unequal PCIe roots): the measured gaps of
+    profiles/r02t_bench_8gpu_default.json give the share the run used; flat or degenerate inputs keep the probe's share;
+    the result stays inside [0, 100]."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_module", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    f = bench.balanced_relay_share
+    assert f(21, 14.33, 36, -9.38) == 30
+    assert f(21, 14.84, 36, -6.99) == 31
+    assert f(21, 5.0, 36, 5.0) == 21 and f(21, 5.0, 21, -5.0) == 21
+    assert f(90, 40.0, 75, 60.0) == 100                      # gap grows as the share falls: everything relayed
+    assert f(10, -30.0, 25, -50.0) == 0                      # relaying ranks already faster: nothing relayed
