@@ -50,6 +50,11 @@ def test_strerror_and_argument_checks_need_no_gpu():
     assert lib.mvs_strerror(0) == b"ok"
     assert b"no CPU fallback" in lib.mvs_strerror(-2)
     assert lib.mvs_create(None, 0) == -1
+    need = C.c_uint64(7)
+    assert lib.mvs_project_device_static(None, None, None, 0, 2048, C.c_uint64(0), None, None, C.byref(need)) == -1
+    assert need.value == 0                                   # cleared even when the call is refused
+    assert b"MVS_STATIC_SCRATCH_BYTES" in lib.mvs_strerror(-7)
+    assert lib.mvs_write_hash_batch(None, b"/nonexistent/x") == -1
     a = np.array([5, 3, 5, 1, 3], dtype=np.uint64)
     n = lib.mvs_sort_unique(a.ctypes.data, len(a))
     assert n == 3 and a[:3].tolist() == [1, 3, 5]
